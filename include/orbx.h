@@ -1,0 +1,165 @@
+/* orbx.h -- C ABI of the B200-native ORB front-end (liborbx.so).
+ *
+ * This is the drop-in boundary for the reference's feature front-end.  Every entry point
+ * is `extern "C"`, takes plain pointers and sizes, never throws and never aborts; the C++
+ * classes in include/Features/ and include/SlamTypes/ (same names and signatures as the
+ * reference) are thin host wrappers over these calls.  There is no CPU fallback: every
+ * compute entry runs hand-written sm_100a kernels and returns ORBX_ERR_CUDA if no device
+ * is usable.
+ *
+ * Reference interfaces replaced (paths relative to the reference checkout):
+ *   orbx_create / orbx_get_level_tables   ORBextractor::ORBextractor + accessors
+ *                                         Features/ORBextractor.hpp:68-108, .cpp:492-595
+ *   orbx_extract / orbx_extract_batch     ORBextractor::operator()      Features/ORBextractor.cpp:1531-1653
+ *   orbx_get_pyramid_level                public member mvImagePyramid  Features/ORBextractor.hpp:111
+ *   orbx_set_camera / orbx_frame_glue     Frame::Frame ctor glue        SlamTypes/Frame.cpp:40-161
+ *   orbx_features_in_area                 Frame::GetFeaturesInArea      SlamTypes/Frame.cpp:163-206
+ *   orbx_search_for_initialization        ORBmatcher::SearchForInitialization  Features/ORBmatcher.cpp:11-150
+ *   orbx_descriptor_distance              DBoW2::FORB::distance         Thirdparty/DBoW2/src/FORB.cpp:77-100
+ *   orbx_stream_*                         the demo's per-pair sequence  demo/demo_initialization.cpp:65-108
+ *                                         kept resident on the device (throughput path)
+ *
+ * Threading: an orbx_ctx is not thread-safe; distinct contexts are independent (one per
+ * host thread / GPU), each owning its stream and all of its device memory.
+ */
+#ifndef ORBX_H_
+#define ORBX_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* status codes (all entry points returning int) */
+#define ORBX_OK 0
+#define ORBX_ERR_ARG (-1)        /* null pointer, bad size, image shape differs from the context's */
+#define ORBX_ERR_EMPTY_IMAGE (-2)/* reference: `if (_image.empty()) return -1;`  ORBextractor.cpp:1536 */
+#define ORBX_ERR_CTOR (-3)       /* reference would exit(1): scaleFactor == 1 with nlevels > 1, .cpp:502-505 */
+#define ORBX_ERR_CUDA (-4)       /* CUDA runtime error; see orbx_last_error() */
+#define ORBX_ERR_CAPACITY (-5)   /* caller's output buffer or an internal table is too small */
+#define ORBX_ERR_ASPECT (-6)     /* level aspect ratio rounds to 0 roots (reference indexes an empty vector, .cpp:706) */
+#define ORBX_ERR_STATE (-7)      /* call order (e.g. glue before orbx_set_camera) */
+
+#define ORBX_MAX_LEVELS 16
+#define ORBX_GRID_COLS 64 /* FRAME_GRID_COLS, SlamTypes/Frame.hpp:16 */
+#define ORBX_GRID_ROWS 48 /* FRAME_GRID_ROWS, SlamTypes/Frame.hpp:15 */
+#define ORBX_GRID_CELLS (ORBX_GRID_COLS * ORBX_GRID_ROWS)
+
+/* Byte-compatible with cv::KeyPoint (28 bytes): pt.x, pt.y, size, angle, response, octave, class_id. */
+typedef struct orbx_keypoint {
+  float x, y, size, angle, response;
+  int32_t octave, class_id;
+} orbx_keypoint;
+
+/* A Frame as the matcher sees it (host memory, borrowed).  grid_offsets has
+ * ORBX_GRID_CELLS + 1 entries in cell order ix * ORBX_GRID_ROWS + iy; grid_indices lists the
+ * keypoint indices of each cell in ascending order (= mGrid[ix][iy], Frame.hpp:98). */
+typedef struct orbx_frame {
+  int32_t n;
+  const orbx_keypoint* keys_un; /* mvKeysUn */
+  const uint8_t* desc;          /* mDescriptors, n x 32, continuous */
+  const uint32_t* grid_offsets;
+  const uint32_t* grid_indices;
+} orbx_frame;
+
+typedef struct orbx_ctx orbx_ctx;
+
+/* ---- lifetime ------------------------------------------------------------------------ */
+/* One context = one extractor configuration on one image shape on one GPU.  max_batch is the
+ * number of frames processed per launch sequence (device memory is sized for it once).
+ * Returns NULL on failure; *status (may be NULL) receives the reason. */
+orbx_ctx* orbx_create(int device, int width, int height, int nfeatures, float scale_factor, int nlevels,
+                      int ini_th_fast, int min_th_fast, int max_batch, int* status);
+void orbx_destroy(orbx_ctx* ctx);
+const char* orbx_last_error(const orbx_ctx* ctx); /* never NULL */
+/* 0: (float)cos((double)a) [default, pinned by the oracle]; 1: cosf(a).  See DESIGN.md. */
+int orbx_set_trig_mode(orbx_ctx* ctx, int mode);
+
+/* ---- extractor tables (host arithmetic of the reference constructor) -------------------- */
+/* Any output pointer may be NULL.  Arrays have nlevels entries; umax has 16.  Returns nlevels. */
+int orbx_get_level_tables(const orbx_ctx* ctx, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                          int* n_per_level, int* umax16);
+int orbx_get_level_size(const orbx_ctx* ctx, int level, int* w, int* h);
+/* Same tables without a device (used by the C++ wrapper's accessors before the first image). */
+int orbx_compute_level_tables(int nfeatures, float scale_factor, int nlevels, float* scale, float* inv_scale,
+                              float* sigma2, float* inv_sigma2, int* n_per_level, int* umax16);
+
+/* ---- extraction ---------------------------------------------------------------------------- */
+/* img: 8-bit single channel, ctx's width x height, row stride `step` bytes (host memory).
+ * kps/desc: caller-owned, room for `cap` keypoints (cap >= nfeatures is always enough).
+ * lapping: vLappingArea {x0, x1} (NULL = {0, 0}).  *n_out = number of keypoints,
+ * *mono_index = the reference's return value (may be NULL). */
+int orbx_extract(orbx_ctx* ctx, const uint8_t* img, size_t step, const int lapping[2], orbx_keypoint* kps,
+                 uint8_t* desc, int cap, int* n_out, int* mono_index);
+/* n_img <= max_batch images; outputs are n_img consecutive blocks of `cap` keypoints. */
+int orbx_extract_batch(orbx_ctx* ctx, const uint8_t* const* imgs, size_t step, int n_img, const int lapping[2],
+                       orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_index);
+
+/* Inspection of the last batch (parity tests; mvImagePyramid).  slot = index in the batch.
+ * padded != 0: (w+38) x (h+38) including the 19-px BORDER_REFLECT_101 frame of
+ * ComputePyramid (.cpp:1689,1708); else w x h. */
+int orbx_get_pyramid_level(orbx_ctx* ctx, int slot, int level, int padded, uint8_t* dst, size_t dst_step);
+int orbx_get_blurred_level(orbx_ctx* ctx, int slot, int level, uint8_t* dst, size_t dst_step);
+/* FAST candidates of a level in the reference's order (cell row-major, then y, then x), as
+ * (x, y, response) float triples relative to (16, 16).  Returns the count (may exceed cap). */
+int orbx_get_candidates(orbx_ctx* ctx, int slot, int level, float* xyr, int cap);
+/* keypoints of one level after distribution + orientation (+ descriptors), level coordinates */
+int orbx_get_level_keypoints(orbx_ctx* ctx, int slot, int level, orbx_keypoint* kps, uint8_t* desc, int cap);
+
+/* ---- Frame glue ---------------------------------------------------------------------------- */
+/* K4 = fx, fy, cx, cy; dist4 = k1, k2, p1, p2 (float32, as the reference's CV_32F matrices).
+ * bounds = mnMinX, mnMaxX, mnMinY, mnMaxY or NULL to compute them as ComputeImageBounds does
+ * (Frame.cpp:101-134).  bounds_out (may be NULL) receives the values in use. */
+int orbx_set_camera(orbx_ctx* ctx, const float K4[4], const float dist4[4], const int bounds[4],
+                    int bounds_out[4]);
+/* UndistortKeyPoints + grid assignment (Frame.cpp:64-77) on the device. */
+int orbx_frame_glue(orbx_ctx* ctx, const orbx_keypoint* kps, int n, orbx_keypoint* kps_un,
+                    uint32_t* grid_offsets, uint32_t* grid_indices);
+/* GetFeaturesInArea on a host frame (device kernel).  Returns the count (may exceed cap). */
+int orbx_features_in_area(orbx_ctx* ctx, const orbx_frame* F, float x, float y, float r, int min_level,
+                          int max_level, int* out, int cap);
+
+/* ---- matcher ------------------------------------------------------------------------------- */
+/* matches12: F1->n ints (-1 = none).  *nmatches = the reference's return value (with its
+ * double-decrement quirk).  counters: rejected by distance, ratio, orientation (the three
+ * values the reference prints, ORBmatcher.cpp:144-147); may be NULL. */
+int orbx_search_for_initialization(orbx_ctx* ctx, const orbx_frame* F1, const orbx_frame* F2, float nnratio,
+                                   int check_orientation, int window_size, int* matches12, int* nmatches,
+                                   int counters[3]);
+/* 256-bit Hamming distance of two 32-byte descriptors (host utility, no device needed). */
+int orbx_descriptor_distance(const uint8_t a[32], const uint8_t b[32]);
+/* n distances a[i] vs b[i] on the device (32 bytes each). */
+int orbx_descriptor_distance_batch(orbx_ctx* ctx, const uint8_t* a, const uint8_t* b, int n, int* out);
+
+/* ---- device-resident stream (throughput path) ---------------------------------------------- */
+/* The frames of a batch stay in HBM from the image to the match list: extract -> glue ->
+ * SearchForInitialization on the pairs (2k, 2k+1).  orbx_set_camera must have been called. */
+/* copy n_img continuous width x height images (host, ideally pinned) into the batch slots */
+int orbx_stream_upload(orbx_ctx* ctx, const uint8_t* imgs, int n_img);
+/* enqueue the whole pipeline on the context's stream for the first n_img slots; asynchronous */
+int orbx_stream_run(orbx_ctx* ctx, int n_img, float nnratio, int check_orientation, int window_size);
+/* wait, then copy results to the host.  Any pointer may be NULL.  kps/kps_un/desc: blocks of
+ * `cap` per frame; matches12: blocks of `cap` per pair; nmatches/counters per pair. */
+int orbx_stream_download(orbx_ctx* ctx, int n_img, orbx_keypoint* kps, orbx_keypoint* kps_un, uint8_t* desc,
+                         int cap, int* n_out, int* matches12, int* nmatches, int* counters3);
+/* compact result of the e2e path: per pair nmatches + matches12 only */
+int orbx_stream_sync(orbx_ctx* ctx);
+/* CUDA-event timing on the context's stream: start/stop bracket enqueued work; elapsed in ms.
+ * which = 0: whole bracket; 1..: per-stage timers recorded inside orbx_stream_run when
+ * enabled with orbx_set_stage_timing(ctx, 1). */
+int orbx_timer_start(orbx_ctx* ctx);
+int orbx_timer_stop(orbx_ctx* ctx, float* ms);
+int orbx_set_stage_timing(orbx_ctx* ctx, int enable);
+/* stage names: "pyramid","fast","quadtree","blur","describe","pack","glue","match" */
+int orbx_get_stage_times(orbx_ctx* ctx, float* ms8);
+/* number of kernel launches issued by the last orbx_stream_run / orbx_extract_batch */
+int orbx_last_launch_count(const orbx_ctx* ctx);
+/* raw cudaStream_t of the context (for callers that record their own events) */
+void* orbx_get_stream(orbx_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ORBX_H_ */
