@@ -152,10 +152,13 @@ int orbx_stream_sync(orbx_ctx* ctx);
 int orbx_timer_start(orbx_ctx* ctx);
 int orbx_timer_stop(orbx_ctx* ctx, float* ms);
 int orbx_set_stage_timing(orbx_ctx* ctx, int enable);
-/* stage names: "pyramid","fast","quadtree","blur","describe","pack","glue","match" */
+/* 8 stages: pyramid, fast, quadtree, blur, describe+pack, (unused, 0), glue, match */
 int orbx_get_stage_times(orbx_ctx* ctx, float* ms8);
 /* number of kernel launches issued by the last orbx_stream_run / orbx_extract_batch */
 int orbx_last_launch_count(const orbx_ctx* ctx);
+/* page-locked host buffers for orbx_stream_upload / orbx_stream_download (NULL on failure) */
+void* orbx_host_alloc(size_t bytes);
+void orbx_host_free(void* p);
 /* raw cudaStream_t of the context (for callers that record their own events) */
 void* orbx_get_stream(orbx_ctx* ctx);
 

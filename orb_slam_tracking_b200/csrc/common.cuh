@@ -1,0 +1,151 @@
+// Shared definitions of the orbx kernels (sm_100a only).
+//
+// HBM layout of a context (one extractor configuration, `maxBatch` frame slots):
+//   pyr / blur   u8   [slot][slabBytes]       level l of a slot at +lv[l].imgOff, rows of lv[l].pitch bytes
+//   candKey      u64  [slot][candTotal]       (response << 32) | ~order   (order = reference emission order)
+//   candXY       u32  [slot][candTotal]       x | y << 16, relative to (16, 16) as in the reference
+//   candNode     u32  [slot][candTotal]       current quadtree node of the candidate
+//   candCount    u32  [slot][nlevels]
+//   node tables  per (slot, level), lv[l].nodeCap entries
+//   lvlKp*       per (slot, level) quota-sized slots: xy, response, angle, descriptor
+//   out*         per slot: packed cv::KeyPoint records + descriptors in the reference's order
+//   frame store  per slot: undistorted keys, 64x48 CSR grid
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/orbx.h"
+#include "stdsort_emul.cuh"
+
+namespace orbx {
+
+typedef unsigned char u8;
+typedef unsigned int u32;
+typedef unsigned long long u64;
+
+constexpr int kMaxLevels = ORBX_MAX_LEVELS;
+constexpr int kEdge = 19;       // EDGE_THRESHOLD, Features/ORBextractor.cpp:76
+constexpr int kHalfPatch = 15;  // HALF_PATCH_SIZE, :74
+constexpr int kPatch = 31;      // PATCH_SIZE, :72
+constexpr int kMinBorder = 16;  // EDGE_THRESHOLD - 3, :1056
+constexpr int kGridCols = ORBX_GRID_COLS, kGridRows = ORBX_GRID_ROWS, kGridCells = ORBX_GRID_CELLS;
+constexpr int kMaxCellDim = 80;  // cell ROI (wCell + 6) is < 76 for every image size
+
+struct LevelInfo {
+  int w, h, pitch;    // unpadded size, row pitch in bytes (multiple of 128)
+  u32 imgOff;         // byte offset of the level in a slot's slab
+  int nCols, nRows, wCell, hCell;  // FAST cell grid, :1066-1075
+  int cellBase;       // first entry of this level in the cell table
+  int quota;          // mnFeaturesPerLevel[l]
+  int candCap;        // capacity of the candidate arrays of this level
+  u32 candOff;        // first candidate of this level in a slot's candidate arrays
+  int nodeCap;        // capacity of the quadtree node tables
+  u32 nodeOff;
+  int nIni;           // number of root nodes, :706
+  u32 rootTabOff;     // x -> root index table (u8), precomputed with the reference's float expression
+  u32 rootEdgeOff;    // nIni + 1 root box edges (int)(hX * i), :719-724
+  int kpOff;          // first keypoint slot of this level (prefix sum of quotas)
+  float scale;        // mvScaleFactor[l]
+  float patchSize;    // (float)(int)(31 * mvScaleFactor[l]), :1165
+  int distW, distH;   // maxBorderX - minBorderX, maxBorderY - minBorderY
+};
+
+struct CellDesc {     // one FAST cell, Features/ORBextractor.cpp:1078-1141
+  short level, pad;
+  short x0, y0, x1, y1;   // ROI [x0,x1) x [y0,y1) in level coordinates
+  short sx, sy;           // j * wCell, i * hCell: shift applied to ROI-relative coordinates (:1134-1135)
+  int index;              // i * nCols + j
+};
+
+struct BlurTile {
+  short level, pad;
+  short x0, y0;
+};
+
+struct Params {
+  int W, H, nlevels, nfeatures, iniTh, minTh, maxBatch;
+  int kpStride;        // keypoint slots per frame = max(nfeatures, sum of quotas)
+  int trigMode;
+  int nCells, nBlurTiles;
+  u32 slabBytes, candTotal, nodeTotal;
+  int umax[16];
+  LevelInfo lv[kMaxLevels];
+  // device pointers
+  u8* pyr;
+  u8* blur;
+  u64* candKey;
+  u32* candXY;
+  u32* candNode;
+  u32* candCount;      // [slot][kMaxLevels]
+  const CellDesc* cells;
+  const BlurTile* blurTiles;
+  const u8* rootTab;
+  // quadtree node tables [slot][nodeTotal]
+  short4* nodeBox;     // ulx, uly, urx, bry
+  int* nodeCount;
+  int* nodeSlot;       // split slot of the node in the current pass, -1 if not being split
+  u64* nodeBest;
+  int* nodeAux;        // 4 ints per split slot: child counts, then child ids, of the current pass
+  int* nodeList;       // split list of the current pass (node ids in visiting order)
+  int* nodeScan;       // scan scratch
+  SortElem* nodeSort;  // (count, UL.x) pairs for the std::sort replay
+  const int* rootEdges;
+  // per-level keypoints [slot][nfeatures]
+  u32* lvlXY;          // x | y << 16, level coordinates
+  float* lvlResp;
+  float* lvlAngle;
+  u8* lvlDesc;         // 32 bytes each
+  int* lvlCount;       // [slot][kMaxLevels]
+  int* status;         // [slot]  sticky error flags of the slot (ORBX_ERR_*), 0 = ok
+  // packed outputs [slot][nfeatures]
+  orbx_keypoint* outKp;
+  u8* outDesc;
+  int* outN;           // [slot]
+  int* outMono;        // [slot]
+  // frame store [slot]
+  orbx_keypoint* keysUn;
+  u32* gridOff;        // [slot][kGridCells + 1]
+  u32* gridIdx;        // [slot][nfeatures]
+  // camera
+  float K4[4], D4[4];
+  int bounds[4];
+  float gridWInv, gridHInv;
+  int undistort;       // mDistCoef(0) != 0
+};
+
+__device__ __forceinline__ const u8* level_ptr(const u8* base, const Params& P, int slot, int l) {
+  return base + (size_t)slot * P.slabBytes + P.lv[l].imgOff;
+}
+__device__ __forceinline__ u8* level_ptr(u8* base, const Params& P, int slot, int l) {
+  return base + (size_t)slot * P.slabBytes + P.lv[l].imgOff;
+}
+__device__ __forceinline__ int reflect101(int i, int len) {
+  // BORDER_REFLECT_101, single reflection is enough for |overhang| < len
+  if (i < 0) i = -i;
+  if (i >= len) i = 2 * (len - 1) - i;
+  return i;
+}
+
+// launchers (one per .cu file); all enqueue on `st` and return the number of kernel launches
+int launch_pyramid(const Params& P, const int* const* dTabs, int nSlots, cudaStream_t st);
+int launch_blur(const Params& P, int nSlots, cudaStream_t st);
+int launch_fast(const Params& P, int nSlots, cudaStream_t st);
+int launch_quadtree(const Params& P, int nSlots, cudaStream_t st);
+int launch_describe(const Params& P, int nSlots, int lap0, int lap1, cudaStream_t st);
+int launch_glue(const Params& P, int nSlots, cudaStream_t st);
+struct MatchArgs {
+  const orbx_keypoint* keysUn;  // [slot][nfeatures]
+  const u8* desc;
+  const u32* gridOff;
+  const u32* gridIdx;
+  const int* n;                 // [slot]
+  int stride;                   // nfeatures
+  int* matches12;               // [pair][stride]
+  int* nmatches;                // [pair]
+  int* counters;                // [pair][3]
+  int* scratch;                 // [pair][2*stride + ...]
+};
+int launch_match(const Params& P, const MatchArgs& A, int nPairs, int pairStep, float nnratio, int checkOri,
+                 int window, cudaStream_t st);
+
+}  // namespace orbx

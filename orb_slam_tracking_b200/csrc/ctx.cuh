@@ -1,0 +1,62 @@
+// Host-side context of liborbx.so: owns the stream, every device allocation and the host tables.
+#pragma once
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+namespace orbx {
+void launch_hamming(const u8* a, const u8* b, int n, int* out, cudaStream_t st);
+
+// ORBextractor::ORBextractor host arithmetic (Features/ORBextractor.cpp:492-595)
+struct HostTables {
+  std::vector<float> scale, invScale, sigma2, invSigma2;
+  std::vector<int> perLevel;
+  int umax[16];
+};
+int compute_tables(int nfeatures, float scaleFactor, int nlevels, HostTables& t);
+}  // namespace orbx
+
+#define CU(ctx, call)                                                                       \
+  do {                                                                                      \
+    cudaError_t e_ = (call);                                                                \
+    if (e_ != cudaSuccess) {                                                                \
+      (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                      \
+      return ORBX_ERR_CUDA;                                                                 \
+    }                                                                                       \
+  } while (0)
+
+struct orbx_ctx {
+  orbx::Params P;
+  orbx::HostTables T;
+  int device;
+  cudaStream_t stream;
+  std::vector<void*> allocs;       // every cudaMalloc, freed in orbx_destroy
+  std::vector<int*> dResizeTabs;   // per level (entry 0 unused)
+  const int** hTabPtrs;            // host array of device pointers for launch_pyramid
+  std::string err;
+  int launches;
+  int cameraSet;
+  int lastBatch;
+  // matcher outputs for the stream path [pair]
+  int* dMatches12;
+  int* dNMatches;
+  int* dCounters;
+  int* dMatchScratch;
+  // staging store for host-frame calls (2 frames): keysUn, desc, gridOff, gridIdx, n
+  orbx_keypoint* hfKeys;
+  orbx::u8* hfDesc;
+  orbx::u32* hfGridOff;
+  orbx::u32* hfGridIdx;
+  int* hfN;
+  int* hfMatches;   // matches12 + nmatches + counters + scratch
+  int* hfNMatches;
+  int* hfCounters;
+  int* hfScratch;
+  int hfCap;
+  // timing
+  cudaEvent_t evStart, evStop;
+  int stageTiming;
+  cudaEvent_t evStage[10];
+  float stageMs[8];
+};

@@ -1,0 +1,177 @@
+// Orientation, steered BRIEF and output packing.
+//   IC_Angle               Features/ORBextractor.cpp:103-159   (on the UNBLURRED level, :1184-1188)
+//   computeOrbDescriptor   Features/ORBextractor.cpp:169-228   (on the blurred level, :1613)
+//   output packing         Features/ORBextractor.cpp:1558-1652 (level-major, pt *= scale, lapping split)
+// One warp per keypoint.  Moments are integer sums (order-independent, so a shuffle reduction is
+// exact); cv::fastAtan2 is replayed in float32 with explicit round-to-nearest multiplies and adds
+// (this file is also compiled with -fmad=false); the rotated sample coordinates use the same
+// separate float multiply/add roundings and round-half-even as cvRound on x86-64.
+#include "common.cuh"
+
+namespace orbx {
+
+__constant__ signed char c_pattern[256 * 4] = {
+#include "orb_pattern.inc"
+};
+
+// cv::fastAtan2 (degrees), SURVEY.md appendix A4
+__device__ __forceinline__ float fast_atan2_deg(float y, float x) {
+  const float scale = (float)(180.0 / 3.1415926535897932384626433832795);
+  const float p1 = 0.9997878412794807f * scale, p3 = -0.3258083974640975f * scale;
+  const float p5 = 0.1555786518463281f * scale, p7 = -0.04432655554792128f * scale;
+  const float eps = 2.2204460492503131e-16f;  // (float)DBL_EPSILON
+  const float ax = fabsf(x), ay = fabsf(y);
+  float a, c, c2;
+  if (ax >= ay) {
+    c = __fdiv_rn(ay, __fadd_rn(ax, eps));
+    c2 = __fmul_rn(c, c);
+    a = __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c);
+  } else {
+    c = __fdiv_rn(ax, __fadd_rn(ay, eps));
+    c2 = __fmul_rn(c, c);
+    a = __fsub_rn(90.f, __fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(__fadd_rn(__fmul_rn(p7, c2), p5), c2), p3), c2), p1), c));
+  }
+  if (x < 0) a = __fsub_rn(180.f, a);
+  if (y < 0) a = __fsub_rn(360.f, a);
+  return a;
+}
+
+constexpr int kWarpsPerCta = 8;
+
+__global__ void __launch_bounds__(kWarpsPerCta * 32) k_describe(const __grid_constant__ Params P) {
+  __shared__ char4 sPat[256];  // [i * 32 + byte]: conflict-free for lane = byte
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  {
+    const int b = tid & 31, i = tid >> 5;  // 256 threads: pair (b, i) -> pattern row 8b + i
+    const signed char* p = c_pattern + 4 * (8 * b + i);
+    sPat[i * 32 + b] = make_char4(p[0], p[1], p[2], p[3]);
+  }
+  __syncthreads();
+  const int slot = blockIdx.y;
+  const int g = blockIdx.x * kWarpsPerCta + warp;  // keypoint slot in [0, nfeatures)
+  if (g >= P.kpStride) return;
+  int l = 0;
+  while (l + 1 < P.nlevels && g >= P.lv[l + 1].kpOff) ++l;
+  const LevelInfo& L = P.lv[l];
+  const int p = g - L.kpOff;
+  if (p >= P.lvlCount[(size_t)slot * kMaxLevels + l]) return;
+  const size_t ko = (size_t)slot * P.kpStride + g;
+  const u32 xy = P.lvlXY[ko];
+  const int x = (int)(xy & 0xffff), y = (int)(xy >> 16);
+
+  // ---- IC_Angle: lane = patch row v in [-15, 15] ----
+  const u8* __restrict__ img = level_ptr((const u8*)P.pyr, P, slot, l);
+  int m10 = 0, m01 = 0;
+  if (lane < 31) {
+    const int v = lane - kHalfPatch;
+    const int d = P.umax[v < 0 ? -v : v];
+    const u8* row = img + (size_t)(y + v) * L.pitch + x;
+    int si = 0, su = 0;
+    for (int u = -d; u <= d; ++u) {
+      const int I = __ldg(row + u);
+      si += I;
+      su += u * I;
+    }
+    m10 = su;
+    m01 = v * si;
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+    m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+  }
+  const float angle = fast_atan2_deg((float)m01, (float)m10);
+
+  // ---- steered BRIEF: lane = descriptor byte ----
+  const float a = __fmul_rn(angle, (float)(3.1415926535897932384626433832795 / 180.f));
+  float co, si;
+  if (P.trigMode == 0) { co = (float)cos((double)a); si = (float)sin((double)a); }
+  else { co = cosf(a); si = sinf(a); }
+  const u8* __restrict__ bl = level_ptr((const u8*)P.blur, P, slot, l) + (size_t)y * L.pitch + x;
+  u32 val = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const char4 q = sPat[i * 32 + lane];
+    const float x0 = (float)q.x, y0 = (float)q.y, x1 = (float)q.z, y1 = (float)q.w;
+    const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, si), __fmul_rn(y0, co)));
+    const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, co), __fmul_rn(y0, si)));
+    const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, si), __fmul_rn(y1, co)));
+    const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, co), __fmul_rn(y1, si)));
+    const int t0 = __ldg(bl + r0 * L.pitch + c0), t1 = __ldg(bl + r1 * L.pitch + c1);
+    val |= (u32)(t0 < t1) << i;
+  }
+  P.lvlDesc[ko * 32 + lane] = (u8)val;
+  if (lane == 0) P.lvlAngle[ko] = angle;
+}
+
+// ---- output packing: one CTA per slot ----
+constexpr int PK = 256;
+__global__ void __launch_bounds__(PK) k_pack(const __grid_constant__ Params P, int lap0, int lap1) {
+  __shared__ int sPart[PK];
+  __shared__ int sOff[kMaxLevels + 1];
+  const int slot = blockIdx.x, tid = threadIdx.x;
+  if (tid == 0) {
+    int s = 0;
+    for (int l = 0; l < P.nlevels; ++l) { sOff[l] = s; s += P.lvlCount[(size_t)slot * kMaxLevels + l]; }
+    sOff[P.nlevels] = s;
+  }
+  __syncthreads();
+  const int total = sOff[P.nlevels];
+  const int chunk = (total + PK - 1) / PK;
+  const int b = min(tid * chunk, total), e = min(b + chunk, total);
+  const size_t base = (size_t)slot * P.kpStride;
+  const float fl0 = (float)lap0, fl1 = (float)lap1;
+  // pass 1: lapping keypoints in my chunk
+  int nl = 0;
+  {
+    int l = 0;
+    for (int i = b; i < e; ++i) {
+      while (i >= sOff[l + 1]) ++l;
+      const u32 xy = P.lvlXY[base + P.lv[l].kpOff + (i - sOff[l])];
+      float x = (float)(xy & 0xffff);
+      if (l != 0) x = __fmul_rn(x, P.lv[l].scale);
+      nl += (x >= fl0 && x <= fl1);
+    }
+  }
+  sPart[tid] = nl;
+  __syncthreads();
+  for (int off = 1; off < PK; off <<= 1) {
+    const int v = tid >= off ? sPart[tid - off] : 0;
+    __syncthreads();
+    sPart[tid] += v;
+    __syncthreads();
+  }
+  int lapBefore = tid ? sPart[tid - 1] : 0;
+  const int nLap = sPart[PK - 1];
+  // pass 2: write
+  {
+    int l = 0;
+    for (int i = b; i < e; ++i) {
+      while (i >= sOff[l + 1]) ++l;
+      const size_t src = base + P.lv[l].kpOff + (i - sOff[l]);
+      const u32 xy = P.lvlXY[src];
+      float x = (float)(xy & 0xffff), y = (float)(xy >> 16);
+      if (l != 0) { x = __fmul_rn(x, P.lv[l].scale); y = __fmul_rn(y, P.lv[l].scale); }
+      const bool lap = (x >= fl0 && x <= fl1);
+      const int dst = lap ? total - 1 - lapBefore : i - lapBefore;
+      lapBefore += lap;
+      orbx_keypoint k;
+      k.x = x; k.y = y; k.size = P.lv[l].patchSize; k.angle = P.lvlAngle[src]; k.response = P.lvlResp[src];
+      k.octave = l; k.class_id = -1;
+      P.outKp[base + dst] = k;
+      const uint4* d = reinterpret_cast<const uint4*>(P.lvlDesc + src * 32);
+      uint4* o = reinterpret_cast<uint4*>(P.outDesc + (base + dst) * 32);
+      o[0] = d[0]; o[1] = d[1];
+    }
+  }
+  if (tid == 0) { P.outN[slot] = total; P.outMono[slot] = total - nLap; }
+}
+
+int launch_describe(const Params& P, int nSlots, int lap0, int lap1, cudaStream_t st) {
+  dim3 grid((P.kpStride + kWarpsPerCta - 1) / kWarpsPerCta, nSlots);
+  k_describe<<<grid, kWarpsPerCta * 32, 0, st>>>(P);
+  k_pack<<<nSlots, PK, 0, st>>>(P, lap0, lap1);
+  return 2;
+}
+
+}  // namespace orbx

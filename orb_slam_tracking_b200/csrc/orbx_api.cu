@@ -1,0 +1,212 @@
+// C ABI of liborbx.so (include/orbx.h): context lifetime, host<->device plumbing, launch sequence.
+// No algorithm lives here; each stage is a kernel in pyramid/fast/quadtree/blur/describe/glue/match.cu.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <new>
+
+#include "ctx.cuh"
+
+namespace orbx {
+void build_resize_tab(int sw, int sh, int dw, int dh, std::vector<int>& tab);
+int build_geometry(Params& P, const HostTables& T, std::vector<CellDesc>& cells, std::vector<BlurTile>& tiles,
+                   std::vector<u8>& rootTab, std::vector<int>& rootEdges);
+}
+using namespace orbx;
+
+template <typename T>
+static int dalloc(orbx_ctx* c, T** p, size_t n) {
+  void* q = nullptr;
+  if (n == 0) n = 1;
+  CU(c, cudaMalloc(&q, n * sizeof(T)));
+  c->allocs.push_back(q);
+  *p = (T*)q;
+  return ORBX_OK;
+}
+template <typename T>
+static int dupload(orbx_ctx* c, T** p, const std::vector<T>& v) {
+  int rc = dalloc(c, p, v.size());
+  if (rc) return rc;
+  if (!v.empty()) CU(c, cudaMemcpy(*p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return ORBX_OK;
+}
+
+static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeatures, float scaleFactor,
+                       int nlevels, int iniTh, int minTh, int maxBatch) {
+  if (width <= 0 || height <= 0 || nfeatures <= 0 || maxBatch <= 0) return ORBX_ERR_ARG;
+  int rc = compute_tables(nfeatures, scaleFactor, nlevels, c->T);
+  if (rc) return rc;
+  Params& P = c->P;
+  std::memset(&P, 0, sizeof(P));
+  P.W = width; P.H = height; P.nlevels = nlevels; P.nfeatures = nfeatures;
+  P.iniTh = iniTh; P.minTh = minTh; P.maxBatch = maxBatch; P.trigMode = 0;
+  std::memcpy(P.umax, c->T.umax, sizeof(P.umax));
+  std::vector<CellDesc> cells;
+  std::vector<BlurTile> tiles;
+  std::vector<u8> rootTab;
+  std::vector<int> rootEdges;
+  rc = build_geometry(P, c->T, cells, tiles, rootTab, rootEdges);
+  if (rc) return rc;
+  int kp = 0;
+  for (int l = 0; l < nlevels; ++l) kp += P.lv[l].quota;
+  P.kpStride = std::max(kp, nfeatures);
+
+  int ndev = 0;
+  CU(c, cudaGetDeviceCount(&ndev));
+  if (device < 0 || device >= ndev) { c->err = "no such CUDA device"; return ORBX_ERR_CUDA; }
+  c->device = device;
+  CU(c, cudaSetDevice(device));
+  CU(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CU(c, cudaEventCreate(&c->evStart));
+  CU(c, cudaEventCreate(&c->evStop));
+  for (int i = 0; i < 10; ++i) CU(c, cudaEventCreate(&c->evStage[i]));
+
+  const size_t B = (size_t)maxBatch;
+  CellDesc* dCells; BlurTile* dTiles; u8* dRootTab; int* dRootEdges;
+  if ((rc = dupload(c, &dCells, cells))) return rc;
+  if ((rc = dupload(c, &dTiles, tiles))) return rc;
+  if ((rc = dupload(c, &dRootTab, rootTab))) return rc;
+  if ((rc = dupload(c, &dRootEdges, rootEdges))) return rc;
+  P.cells = dCells; P.blurTiles = dTiles; P.rootTab = dRootTab; P.rootEdges = dRootEdges;
+  c->dResizeTabs.assign(nlevels, nullptr);
+  c->hTabPtrs = new const int*[nlevels];
+  c->hTabPtrs[0] = nullptr;
+  for (int l = 1; l < nlevels; ++l) {
+    std::vector<int> tab;
+    build_resize_tab(P.lv[l - 1].w, P.lv[l - 1].h, P.lv[l].w, P.lv[l].h, tab);
+    if ((rc = dupload(c, &c->dResizeTabs[l], tab))) return rc;
+    c->hTabPtrs[l] = c->dResizeTabs[l];
+  }
+  if ((rc = dalloc(c, &P.pyr, B * P.slabBytes))) return rc;
+  if ((rc = dalloc(c, &P.blur, B * P.slabBytes))) return rc;
+  if ((rc = dalloc(c, &P.candKey, B * P.candTotal))) return rc;
+  if ((rc = dalloc(c, &P.candXY, B * P.candTotal))) return rc;
+  if ((rc = dalloc(c, &P.candNode, B * P.candTotal))) return rc;
+  if ((rc = dalloc(c, &P.candCount, B * kMaxLevels))) return rc;
+  if ((rc = dalloc(c, &P.nodeBox, B * P.nodeTotal))) return rc;
+  if ((rc = dalloc(c, &P.nodeCount, B * P.nodeTotal))) return rc;
+  if ((rc = dalloc(c, &P.nodeSlot, B * P.nodeTotal))) return rc;
+  if ((rc = dalloc(c, &P.nodeBest, B * P.nodeTotal))) return rc;
+  if ((rc = dalloc(c, &P.nodeAux, 4 * B * P.nodeTotal))) return rc;
+  if ((rc = dalloc(c, &P.nodeList, B * P.nodeTotal))) return rc;
+  if ((rc = dalloc(c, &P.nodeScan, B * P.nodeTotal))) return rc;
+  if ((rc = dalloc(c, &P.nodeSort, B * P.nodeTotal))) return rc;
+  const size_t K = B * (size_t)P.kpStride;
+  if ((rc = dalloc(c, &P.lvlXY, K))) return rc;
+  if ((rc = dalloc(c, &P.lvlResp, K))) return rc;
+  if ((rc = dalloc(c, &P.lvlAngle, K))) return rc;
+  if ((rc = dalloc(c, &P.lvlDesc, K * 32))) return rc;
+  if ((rc = dalloc(c, &P.lvlCount, B * kMaxLevels))) return rc;
+  if ((rc = dalloc(c, &P.status, B))) return rc;
+  if ((rc = dalloc(c, &P.outKp, K))) return rc;
+  if ((rc = dalloc(c, &P.outDesc, K * 32))) return rc;
+  if ((rc = dalloc(c, &P.outN, B))) return rc;
+  if ((rc = dalloc(c, &P.outMono, B))) return rc;
+  if ((rc = dalloc(c, &P.keysUn, K))) return rc;
+  if ((rc = dalloc(c, &P.gridOff, B * (kGridCells + 1)))) return rc;
+  if ((rc = dalloc(c, &P.gridIdx, K))) return rc;
+  const size_t nPairs = (B + 1) / 2;
+  if ((rc = dalloc(c, &c->dMatches12, nPairs * P.kpStride))) return rc;
+  if ((rc = dalloc(c, &c->dNMatches, nPairs))) return rc;
+  if ((rc = dalloc(c, &c->dCounters, nPairs * 3))) return rc;
+  if ((rc = dalloc(c, &c->dMatchScratch, nPairs * 3 * P.kpStride))) return rc;
+  // host-frame staging (2 frames)
+  c->hfCap = P.kpStride;
+  if ((rc = dalloc(c, &c->hfKeys, 2 * (size_t)c->hfCap))) return rc;
+  if ((rc = dalloc(c, &c->hfDesc, 2 * (size_t)c->hfCap * 32))) return rc;
+  if ((rc = dalloc(c, &c->hfGridOff, 2 * (size_t)(kGridCells + 1)))) return rc;
+  if ((rc = dalloc(c, &c->hfGridIdx, 2 * (size_t)c->hfCap))) return rc;
+  if ((rc = dalloc(c, &c->hfN, 2))) return rc;
+  if ((rc = dalloc(c, &c->hfMatches, (size_t)c->hfCap))) return rc;
+  if ((rc = dalloc(c, &c->hfNMatches, 1))) return rc;
+  if ((rc = dalloc(c, &c->hfCounters, 3))) return rc;
+  if ((rc = dalloc(c, &c->hfScratch, 3 * (size_t)c->hfCap))) return rc;
+  CU(c, cudaMemset(P.status, 0, B * sizeof(int)));
+  CU(c, cudaMemset(P.outN, 0, B * sizeof(int)));
+  CU(c, cudaMemset(P.pyr, 0, B * P.slabBytes));
+  CU(c, cudaMemset(P.blur, 0, B * P.slabBytes));
+  CU(c, cudaDeviceSynchronize());
+  return ORBX_OK;
+}
+
+extern "C" orbx_ctx* orbx_create(int device, int width, int height, int nfeatures, float scale_factor, int nlevels,
+                                 int ini_th_fast, int min_th_fast, int max_batch, int* status) {
+  orbx_ctx* c = new (std::nothrow) orbx_ctx();
+  if (!c) { if (status) *status = ORBX_ERR_ARG; return nullptr; }
+  c->stream = nullptr; c->hTabPtrs = nullptr; c->launches = 0; c->cameraSet = 0; c->lastBatch = 0;
+  c->stageTiming = 0; c->evStart = c->evStop = nullptr;
+  for (int i = 0; i < 10; ++i) c->evStage[i] = nullptr;
+  std::memset(c->stageMs, 0, sizeof(c->stageMs));
+  int rc = create_impl(c, device, width, height, nfeatures, scale_factor, nlevels, ini_th_fast, min_th_fast, max_batch);
+  if (status) *status = rc;
+  if (rc != ORBX_OK) {
+    if (rc == ORBX_ERR_CUDA) std::fprintf(stderr, "orbx_create: %s\n", c->err.c_str());
+    orbx_destroy(c);
+    return nullptr;
+  }
+  return c;
+}
+
+extern "C" void orbx_destroy(orbx_ctx* c) {
+  if (!c) return;
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  for (void* p : c->allocs) cudaFree(p);
+  if (c->evStart) cudaEventDestroy(c->evStart);
+  if (c->evStop) cudaEventDestroy(c->evStop);
+  for (int i = 0; i < 10; ++i) if (c->evStage[i]) cudaEventDestroy(c->evStage[i]);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete[] c->hTabPtrs;
+  delete c;
+}
+
+extern "C" const char* orbx_last_error(const orbx_ctx* c) { return c ? c->err.c_str() : "null context"; }
+extern "C" int orbx_set_trig_mode(orbx_ctx* c, int mode) {
+  if (!c || (mode != 0 && mode != 1)) return ORBX_ERR_ARG;
+  c->P.trigMode = mode;
+  return ORBX_OK;
+}
+extern "C" void* orbx_get_stream(orbx_ctx* c) { return c ? (void*)c->stream : nullptr; }
+extern "C" int orbx_last_launch_count(const orbx_ctx* c) { return c ? c->launches : 0; }
+
+static int copy_tables(const HostTables& T, int nlevels, float* scale, float* inv, float* s2, float* is2, int* npl,
+                       int* umax16) {
+  for (int i = 0; i < nlevels; ++i) {
+    if (scale) scale[i] = T.scale[i];
+    if (inv) inv[i] = T.invScale[i];
+    if (s2) s2[i] = T.sigma2[i];
+    if (is2) is2[i] = T.invSigma2[i];
+    if (npl) npl[i] = T.perLevel[i];
+  }
+  if (umax16) std::memcpy(umax16, T.umax, 16 * sizeof(int));
+  return nlevels;
+}
+extern "C" int orbx_get_level_tables(const orbx_ctx* c, float* scale, float* inv_scale, float* sigma2,
+                                     float* inv_sigma2, int* n_per_level, int* umax16) {
+  if (!c) return ORBX_ERR_ARG;
+  return copy_tables(c->T, c->P.nlevels, scale, inv_scale, sigma2, inv_sigma2, n_per_level, umax16);
+}
+extern "C" int orbx_compute_level_tables(int nfeatures, float scale_factor, int nlevels, float* scale,
+                                         float* inv_scale, float* sigma2, float* inv_sigma2, int* n_per_level,
+                                         int* umax16) {
+  HostTables T;
+  int rc = compute_tables(nfeatures, scale_factor, nlevels, T);
+  if (rc) return rc;
+  return copy_tables(T, nlevels, scale, inv_scale, sigma2, inv_sigma2, n_per_level, umax16);
+}
+extern "C" int orbx_get_level_size(const orbx_ctx* c, int level, int* w, int* h) {
+  if (!c || level < 0 || level >= c->P.nlevels) return ORBX_ERR_ARG;
+  if (w) *w = c->P.lv[level].w;
+  if (h) *h = c->P.lv[level].h;
+  return ORBX_OK;
+}
+
+// DBoW2::FORB::distance (Thirdparty/DBoW2/src/FORB.cpp:77-100): 4 x 64-bit XOR + popcount.
+extern "C" int orbx_descriptor_distance(const uint8_t a[32], const uint8_t b[32]) {
+  uint64_t x[4], y[4];
+  std::memcpy(x, a, 32);
+  std::memcpy(y, b, 32);
+  int d = 0;
+  for (int i = 0; i < 4; ++i) d += __builtin_popcountll(x[i] ^ y[i]);
+  return d;
+}

@@ -1,0 +1,173 @@
+// C ABI, part 3: camera / Frame glue / matcher entry points on host frames, and the
+// device-resident stream path (extract -> glue -> SearchForInitialization without leaving HBM).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "ctx.cuh"
+
+using namespace orbx;
+
+namespace orbx {
+void launch_features_in_area(const Params& P, const orbx_keypoint* kun, const u32* gOff, const u32* gIdx, float x,
+                             float y, float r, int minLevel, int maxLevel, int* out, int cap, int* count,
+                             cudaStream_t st);
+}
+
+// cv::undistortPoints for the four image corners (ComputeImageBounds, SlamTypes/Frame.cpp:101-134).
+// Runs once per context on the host: it is constructor arithmetic like the level tables, and its
+// float -> int truncation decides the grid geometry, so it is evaluated exactly as the CPU does.
+static void undistort_host(float u, float v, const float K[4], const float D[4], float* ou, float* ov) {
+  const double fx = K[0], fy = K[1], cx = K[2], cy = K[3], k1 = D[0], k2 = D[1], p1 = D[2], p2 = D[3];
+  const double ifx = 1. / fx, ify = 1. / fy;
+  double x = ((double)u - cx) * ifx, y = ((double)v - cy) * ify;
+  const double x0 = x, y0 = y;
+  for (int j = 0; j < 5; ++j) {
+    const double r2 = x * x + y * y;
+    const double icdist = 1. / (1 + ((0 * r2 + k2) * r2 + k1) * r2);
+    const double dx = 2 * p1 * x * y + p2 * (r2 + 2 * x * x);
+    const double dy = p1 * (r2 + 2 * y * y) + 2 * p2 * x * y;
+    x = (x0 - dx) * icdist;
+    y = (y0 - dy) * icdist;
+  }
+  *ou = (float)(x * fx + cx);
+  *ov = (float)(y * fy + cy);
+}
+
+extern "C" int orbx_set_camera(orbx_ctx* c, const float K4[4], const float dist4[4], const int bounds[4],
+                               int bounds_out[4]) {
+  if (!c || !K4 || !dist4) return ORBX_ERR_ARG;
+  Params& P = c->P;
+  std::memcpy(P.K4, K4, sizeof(P.K4));
+  std::memcpy(P.D4, dist4, sizeof(P.D4));
+  P.undistort = dist4[0] != 0.0f;  // :138, :103
+  if (bounds) {
+    std::memcpy(P.bounds, bounds, sizeof(P.bounds));
+  } else if (P.undistort) {
+    const float cs[4][2] = {{0.f, 0.f}, {(float)P.W, 0.f}, {0.f, (float)P.H}, {(float)P.W, (float)P.H}};
+    float u[4][2];
+    for (int i = 0; i < 4; ++i) undistort_host(cs[i][0], cs[i][1], K4, dist4, &u[i][0], &u[i][1]);
+    P.bounds[0] = (int)std::min(u[0][0], u[2][0]);
+    P.bounds[1] = (int)std::max(u[1][0], u[3][0]);
+    P.bounds[2] = (int)std::min(u[0][1], u[1][1]);
+    P.bounds[3] = (int)std::max(u[2][1], u[3][1]);
+  } else {
+    P.bounds[0] = 0; P.bounds[1] = P.W; P.bounds[2] = 0; P.bounds[3] = P.H;
+  }
+  if (P.bounds[1] <= P.bounds[0] || P.bounds[3] <= P.bounds[2]) return ORBX_ERR_ARG;
+  P.gridWInv = (float)kGridCols / (float)(P.bounds[1] - P.bounds[0]);  // :46-47
+  P.gridHInv = (float)kGridRows / (float)(P.bounds[3] - P.bounds[2]);
+  if (bounds_out) std::memcpy(bounds_out, P.bounds, sizeof(P.bounds));
+  c->cameraSet = 1;
+  return ORBX_OK;
+}
+
+extern "C" int orbx_frame_glue(orbx_ctx* c, const orbx_keypoint* kps, int n, orbx_keypoint* kps_un,
+                               uint32_t* grid_offsets, uint32_t* grid_indices) {
+  if (!c || n < 0 || (n > 0 && !kps)) return ORBX_ERR_ARG;
+  if (!c->cameraSet) return ORBX_ERR_STATE;
+  const Params& P = c->P;
+  if (n > P.kpStride) return ORBX_ERR_CAPACITY;
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  // slot 0 of the frame store is the staging area of this call
+  if (n) CU(c, cudaMemcpyAsync(P.outKp, kps, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, st));
+  CU(c, cudaMemcpyAsync(P.outN, &n, sizeof(int), cudaMemcpyHostToDevice, st));
+  c->launches = launch_glue(P, 1, st);
+  CU(c, cudaGetLastError());
+  if (kps_un && n) CU(c, cudaMemcpyAsync(kps_un, P.keysUn, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, st));
+  if (grid_offsets)
+    CU(c, cudaMemcpyAsync(grid_offsets, P.gridOff, (kGridCells + 1) * sizeof(u32), cudaMemcpyDeviceToHost, st));
+  if (grid_indices && n) CU(c, cudaMemcpyAsync(grid_indices, P.gridIdx, (size_t)n * sizeof(u32), cudaMemcpyDeviceToHost, st));
+  CU(c, cudaStreamSynchronize(st));
+  return ORBX_OK;
+}
+
+// copies a host frame into staging slot s (0 or 1)
+static int stage_frame(orbx_ctx* c, const orbx_frame* F, int s) {
+  if (!F || F->n < 0) return ORBX_ERR_ARG;
+  if (F->n > c->hfCap) return ORBX_ERR_CAPACITY;
+  if (F->n > 0 && (!F->keys_un || !F->desc || !F->grid_indices)) return ORBX_ERR_ARG;
+  if (!F->grid_offsets) return ORBX_ERR_ARG;
+  cudaStream_t st = c->stream;
+  const size_t cap = (size_t)c->hfCap;
+  if (F->n) {
+    CU(c, cudaMemcpyAsync(c->hfKeys + s * cap, F->keys_un, (size_t)F->n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, st));
+    CU(c, cudaMemcpyAsync(c->hfDesc + s * cap * 32, F->desc, (size_t)F->n * 32, cudaMemcpyHostToDevice, st));
+    const u32 nIdx = F->grid_offsets[kGridCells];
+    if (nIdx > (u32)F->n) return ORBX_ERR_ARG;
+    if (nIdx) CU(c, cudaMemcpyAsync(c->hfGridIdx + s * cap, F->grid_indices, nIdx * sizeof(u32), cudaMemcpyHostToDevice, st));
+  }
+  CU(c, cudaMemcpyAsync(c->hfGridOff + (size_t)s * (kGridCells + 1), F->grid_offsets, (kGridCells + 1) * sizeof(u32),
+                        cudaMemcpyHostToDevice, st));
+  CU(c, cudaMemcpyAsync(c->hfN + s, &F->n, sizeof(int), cudaMemcpyHostToDevice, st));
+  return ORBX_OK;
+}
+
+extern "C" int orbx_features_in_area(orbx_ctx* c, const orbx_frame* F, float x, float y, float r, int min_level,
+                                     int max_level, int* out, int cap) {
+  if (!c || !F || cap < 0 || (cap > 0 && !out)) return ORBX_ERR_ARG;
+  if (!c->cameraSet) return ORBX_ERR_STATE;
+  CU(c, cudaSetDevice(c->device));
+  int rc = stage_frame(c, F, 0);
+  if (rc) return rc;
+  const int dcap = std::min(cap, c->hfCap);
+  launch_features_in_area(c->P, c->hfKeys, c->hfGridOff, c->hfGridIdx, x, y, r, min_level, max_level, c->hfMatches,
+                          dcap, c->hfNMatches, c->stream);
+  CU(c, cudaGetLastError());
+  int n = 0;
+  CU(c, cudaMemcpyAsync(&n, c->hfNMatches, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  const int m = std::min(n, dcap);
+  if (m > 0) CU(c, cudaMemcpy(out, c->hfMatches, (size_t)m * sizeof(int), cudaMemcpyDeviceToHost));
+  return n;
+}
+
+extern "C" int orbx_search_for_initialization(orbx_ctx* c, const orbx_frame* F1, const orbx_frame* F2, float nnratio,
+                                              int check_orientation, int window_size, int* matches12, int* nmatches,
+                                              int counters[3]) {
+  if (!c || !F1 || !F2) return ORBX_ERR_ARG;
+  if (!c->cameraSet) return ORBX_ERR_STATE;
+  CU(c, cudaSetDevice(c->device));
+  int rc = stage_frame(c, F1, 0);
+  if (rc) return rc;
+  if ((rc = stage_frame(c, F2, 1))) return rc;
+  MatchArgs A;
+  A.keysUn = c->hfKeys; A.desc = c->hfDesc; A.gridOff = c->hfGridOff; A.gridIdx = c->hfGridIdx; A.n = c->hfN;
+  A.stride = c->hfCap; A.matches12 = c->hfMatches; A.nmatches = c->hfNMatches; A.counters = c->hfCounters;
+  A.scratch = c->hfScratch;
+  c->launches = launch_match(c->P, A, 1, 2, nnratio, check_orientation, window_size, c->stream);
+  CU(c, cudaGetLastError());
+  int nm = 0, cnt[3] = {0, 0, 0};
+  if (matches12 && F1->n)
+    CU(c, cudaMemcpyAsync(matches12, c->hfMatches, (size_t)F1->n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaMemcpyAsync(&nm, c->hfNMatches, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaMemcpyAsync(cnt, c->hfCounters, 3 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  if (nmatches) *nmatches = nm;
+  if (counters) std::memcpy(counters, cnt, sizeof(cnt));
+  return ORBX_OK;
+}
+
+extern "C" int orbx_descriptor_distance_batch(orbx_ctx* c, const uint8_t* a, const uint8_t* b, int n, int* out) {
+  if (!c || n < 0 || (n > 0 && (!a || !b || !out))) return ORBX_ERR_ARG;
+  if (n == 0) return ORBX_OK;
+  CU(c, cudaSetDevice(c->device));
+  u8 *da = nullptr, *db = nullptr;
+  int* dout = nullptr;
+  CU(c, cudaMalloc(&da, (size_t)n * 32));
+  cudaError_t e1 = cudaMalloc(&db, (size_t)n * 32), e2 = cudaMalloc(&dout, (size_t)n * sizeof(int));
+  int rc = ORBX_OK;
+  if (e1 == cudaSuccess && e2 == cudaSuccess) {
+    cudaMemcpyAsync(da, a, (size_t)n * 32, cudaMemcpyHostToDevice, c->stream);
+    cudaMemcpyAsync(db, b, (size_t)n * 32, cudaMemcpyHostToDevice, c->stream);
+    launch_hamming(da, db, n, dout, c->stream);
+    cudaMemcpyAsync(out, dout, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, c->stream);
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) { c->err = cudaGetErrorString(e); rc = ORBX_ERR_CUDA; }
+  } else {
+    c->err = "cudaMalloc failed"; rc = ORBX_ERR_CUDA;
+  }
+  cudaFree(da); cudaFree(db); cudaFree(dout);
+  return rc;
+}

@@ -1,0 +1,236 @@
+// ORBextractor::DistributeOctTree (Features/ORBextractor.cpp:698-1011) + ExtractorNode::DivideNode
+// (:617-676) + the post-distribution fix-up (:1159-1179), one CTA per (level, slot).
+//
+// The reference keeps a std::list of nodes and push_front()s children; this kernel keeps the same
+// information in flat tables and reproduces the list ORDER arithmetically:
+//  * every node gets an index in creation (push) order; push_front means the list, front to
+//    back, is "alive nodes by DESCENDING index" (root i is stored at index nIni-1-i so that the
+//    rule also holds for the push_back'ed roots);
+//  * a pass visits the nodes to split in list order (phase 1) or in reverse std::sort order
+//    (phase 2), so child indices are a prefix sum over the visiting order;
+//  * node boxes depend only on geometry, and a key's child is a pure function of its position
+//    and its node's box, so keys are never moved: each key carries its current node id, child
+//    populations are counted with atomics, and the per-node "first strict maximum of response in
+//    input order" (:984-1007) is an atomicMax over (response, ~emission order) keys;
+//  * the tie order of std::sort (unstable, observable -- SURVEY.md 7.3-1) is replayed by one thread
+//    with stdsort_emul(); everything else in a pass is CTA-parallel.
+#include "common.cuh"
+
+namespace orbx {
+
+constexpr int QT = 512;
+
+struct QtS {
+  int nNodes, size, gen0, gen1, nS, nProc, nToExpand, cut;
+  int part[QT];
+};
+
+// In-place inclusive scan of a[0..n) by the whole CTA.  Returns the total to every thread.
+__device__ int cta_scan(int* a, int n, int* part) {
+  const int tid = threadIdx.x;
+  const int chunk = (n + QT - 1) / QT;
+  const int b = min(tid * chunk, n), e = min(b + chunk, n);
+  int s = 0;
+  for (int i = b; i < e; ++i) s += a[i];
+  part[tid] = s;
+  __syncthreads();
+  for (int off = 1; off < QT; off <<= 1) {
+    const int v = tid >= off ? part[tid - off] : 0;
+    __syncthreads();
+    part[tid] += v;
+    __syncthreads();
+  }
+  int run = tid ? part[tid - 1] : 0;
+  for (int i = b; i < e; ++i) { run += a[i]; a[i] = run; }
+  const int total = part[QT - 1];
+  __syncthreads();
+  return total;
+}
+
+__device__ __forceinline__ int quadrant(const short4 b, const u32 xy) {
+  const int x = (int)(xy & 0xffff), y = (int)(xy >> 16);
+  const int midx = b.x + ((b.z - b.x + 1) >> 1);  // UL.x + ceil(w / 2)
+  const int midy = b.y + ((b.w - b.y + 1) >> 1);
+  return (x >= midx ? 1 : 0) + (y >= midy ? 2 : 0);  // n1, n2, n3, n4
+}
+
+__global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params P) {
+  __shared__ QtS S;
+  const int l = blockIdx.x, slot = blockIdx.y, tid = threadIdx.x;
+  const LevelInfo& L = P.lv[l];
+  const int N = L.quota;
+  int* lvlCount = P.lvlCount + (size_t)slot * kMaxLevels + l;
+  const int M = min((int)P.candCount[(size_t)slot * kMaxLevels + l], L.candCap);
+  if (M == 0 || L.nIni < 1) {
+    if (tid == 0) {
+      *lvlCount = 0;
+      if (L.nIni < 1) atomicMin(P.status + slot, ORBX_ERR_ASPECT);
+    }
+    return;
+  }
+  const size_t co = (size_t)slot * P.candTotal + L.candOff;
+  const u64* cKey = P.candKey + co;
+  const u32* cXY = P.candXY + co;
+  u32* cNode = P.candNode + co;
+  const size_t no = (size_t)slot * P.nodeTotal + L.nodeOff;
+  short4* nBox = P.nodeBox + no;
+  int* nCount = P.nodeCount + no;
+  int* nSlot = P.nodeSlot + no;
+  u64* nBest = P.nodeBest + no;
+  int* aux = P.nodeAux + 4 * no;
+  int* list = P.nodeList + no;
+  int* scan = P.nodeScan + no;
+  SortElem* srt = P.nodeSort + no;
+  const int* edges = P.rootEdges + L.rootEdgeOff;
+
+  // roots (:706-768)
+  for (int i = tid; i < L.nIni; i += QT) {
+    const int r = L.nIni - 1 - i;  // root r stored at index i
+    nBox[i] = make_short4((short)edges[r], 0, (short)edges[r + 1], (short)L.distH);
+    nCount[i] = 0;
+    nSlot[i] = -1;
+  }
+  __syncthreads();
+  for (int k = tid; k < M; k += QT) atomicAdd(nCount + cNode[k], 1);
+  __syncthreads();
+  if (tid == 0) {
+    int s = 0;
+    for (int i = 0; i < L.nIni; ++i) s += nCount[i] > 0;
+    S.size = s; S.nNodes = L.nIni; S.gen0 = 0; S.gen1 = L.nIni;
+  }
+  __syncthreads();
+
+  bool phase2 = false;
+  for (;;) {
+    const int prevSize = S.size, gen0 = S.gen0, gen1 = S.gen1, G = gen1 - gen0, nNodes = S.nNodes;
+    // ---- A. nodes to split, in visiting order ----
+    int nS;
+    if (!phase2) {
+      for (int j = tid; j < G; j += QT) scan[j] = nCount[gen1 - 1 - j] > 1;
+      __syncthreads();
+      nS = cta_scan(scan, G, S.part);
+      for (int j = tid; j < G; j += QT) {
+        const int node = gen1 - 1 - j;
+        if (nCount[node] > 1) list[scan[j] - 1] = node;
+      }
+    } else {
+      for (int j = tid; j < G; j += QT) scan[j] = nCount[gen0 + j] > 1;
+      __syncthreads();
+      nS = cta_scan(scan, G, S.part);
+      for (int j = tid; j < G; j += QT) {
+        const int node = gen0 + j, c = nCount[node];
+        if (c > 1) {
+          SortElem e;
+          e.key = ((u64)(u32)c << 32) | (u64)(u32)(int)nBox[node].x;
+          e.id = (u32)node; e.pad = 0;
+          srt[scan[j] - 1] = e;
+        }
+      }
+      __syncthreads();
+      if (tid == 0) stdsort_emul(srt, nS);
+      __syncthreads();
+      for (int s = tid; s < nS; s += QT) list[s] = (int)srt[nS - 1 - s].id;
+    }
+    __syncthreads();
+    if (nS == 0) break;  // nothing divisible: |L| == prevSize
+    // ---- B/C. child populations ----
+    for (int s = tid; s < nS; s += QT) nSlot[list[s]] = s;
+    for (int i = tid; i < 4 * nS; i += QT) aux[i] = 0;
+    __syncthreads();
+    for (int k = tid; k < M; k += QT) {
+      const int nd = (int)cNode[k], s = nSlot[nd];
+      if (s >= 0) atomicAdd(aux + 4 * s + quadrant(nBox[nd], cXY[k]), 1);
+    }
+    __syncthreads();
+    // ---- D. child indices = prefix sum over the visiting order; phase 2 stops at |L| >= N ----
+    for (int s = tid; s < nS; s += QT)
+      scan[s] = (aux[4 * s] > 0) + (aux[4 * s + 1] > 0) + (aux[4 * s + 2] > 0) + (aux[4 * s + 3] > 0);
+    if (tid == 0) { S.cut = nS - 1; S.nToExpand = 0; }
+    __syncthreads();
+    cta_scan(scan, nS, S.part);
+    if (phase2) {
+      for (int s = tid; s < nS; s += QT)
+        if (prevSize + scan[s] - (s + 1) >= N) atomicMin(&S.cut, s);
+      __syncthreads();
+    }
+    const int nProc = S.cut + 1;
+    const int nNew = scan[nProc - 1];
+    if (nNodes + nNew > L.nodeCap) {
+      if (tid == 0) { atomicMin(P.status + slot, ORBX_ERR_CAPACITY); *lvlCount = 0; }
+      return;
+    }
+    // ---- E. create the children (n1..n4 order), erase the parents ----
+    for (int s = tid; s < nS; s += QT) {
+      const int node = list[s];
+      if (s >= nProc) { nSlot[node] = -1; continue; }
+      const short4 b = nBox[node];
+      const int hx = (b.z - b.x + 1) >> 1, hy = (b.w - b.y + 1) >> 1;
+      const int mx = b.x + hx, my = b.y + hy;
+      int id = nNodes + (s ? scan[s - 1] : 0);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int c = aux[4 * s + q];
+        if (c > 0) {
+          nBox[id] = make_short4((short)((q & 1) ? mx : b.x), (short)((q & 2) ? my : b.y),
+                                 (short)((q & 1) ? b.z : mx), (short)((q & 2) ? b.w : my));
+          nCount[id] = c;
+          nSlot[id] = -1;
+          if (c > 1) atomicAdd(&S.nToExpand, 1);
+          aux[4 * s + q] = id++;
+        }
+      }
+      nCount[node] = 0;
+    }
+    __syncthreads();
+    // ---- F. move the keys of the split nodes to their child ----
+    for (int k = tid; k < M; k += QT) {
+      const int nd = (int)cNode[k], s = nSlot[nd];
+      if (s >= 0) cNode[k] = (u32)aux[4 * s + quadrant(nBox[nd], cXY[k])];
+    }
+    __syncthreads();
+    if (tid == 0) {
+      S.size = prevSize + nNew - nProc;
+      S.gen0 = nNodes; S.gen1 = nNodes + nNew; S.nNodes = nNodes + nNew;
+    }
+    __syncthreads();
+    const int size = S.size;
+    if (size >= N || size == prevSize) break;                         // :887-888 / :966-967
+    if (!phase2 && size + 3 * S.nToExpand > N) phase2 = true;         // :897
+    __syncthreads();
+  }
+  __syncthreads();
+  // ---- best key per node (:984-1007), list order = descending node index, truncation (:1159-1161) ----
+  const int nNodes = S.nNodes;
+  for (int i = tid; i < nNodes; i += QT) nBest[i] = 0ull;
+  __syncthreads();
+  for (int k = tid; k < M; k += QT) atomicMax(nBest + cNode[k], cKey[k]);
+  for (int j = tid; j < nNodes; j += QT) scan[j] = nCount[nNodes - 1 - j] > 0;
+  __syncthreads();
+  const int alive = cta_scan(scan, nNodes, S.part);
+  const size_t ko = (size_t)slot * P.kpStride + L.kpOff;
+  for (int j = tid; j < nNodes; j += QT) {
+    const int node = nNodes - 1 - j;
+    if (nCount[node] > 0) {
+      const int p = scan[j] - 1;
+      if (p < N) {
+        const u64 best = nBest[node];
+        const u32 order = ~(u32)(best & 0xffffffffull);
+        const int cell = (int)(order >> 14), yin = (int)((order >> 7) & 127), xin = (int)(order & 127);
+        const int ci = cell / L.nCols, cj = cell - ci * L.nCols;
+        // candidate coordinates are relative to (16,16); the reference adds minBorder back (:1171-1173)
+        const int x = xin + cj * L.wCell + kMinBorder, y = yin + ci * L.hCell + kMinBorder;
+        P.lvlXY[ko + p] = (u32)x | ((u32)y << 16);
+        P.lvlResp[ko + p] = (float)(u32)(best >> 32);
+      }
+    }
+  }
+  if (tid == 0) *lvlCount = min(alive, N);
+}
+
+int launch_quadtree(const Params& P, int nSlots, cudaStream_t st) {
+  dim3 grid(P.nlevels, nSlots);
+  k_quadtree<<<grid, QT, 0, st>>>(P);
+  return 1;
+}
+
+}  // namespace orbx

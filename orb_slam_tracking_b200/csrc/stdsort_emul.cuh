@@ -1,0 +1,162 @@
+// Reproduces the PERMUTATION that libstdc++'s std::sort produces (GCC 13 bits/stl_algo.h,
+// bits/stl_heap.h: median-of-3 introsort down to runs of 16, heap-sort fallback at depth
+// 2*floor(log2 n), then the final insertion sort).  The reference sorts the quadtree's
+// (key count, UL.x) pairs with std::sort and a comparator that ties
+// (Features/ORBextractor.cpp:684-696, 912-913); the order of tied elements decides which nodes are
+// split before DistributeOctTree's `break`, so a device sort "by key" is not parity-safe -- the
+// algorithm itself has to be replayed.  Host+device so the CPU suite can check it against the
+// real std::sort (tests/test_stdsort_emul.py).
+#pragma once
+#include <stdint.h>
+
+#ifdef __CUDACC__
+#define ORBX_HD __host__ __device__ __forceinline__
+#else
+#define ORBX_HD inline
+#endif
+
+namespace orbx {
+
+struct SortElem {
+  unsigned long long key;  // compared with <
+  unsigned int id;         // payload
+  unsigned int pad;
+};
+
+namespace ss {
+
+ORBX_HD bool lt(const SortElem& a, const SortElem& b) { return a.key < b.key; }
+ORBX_HD void swp(SortElem& a, SortElem& b) { SortElem t = a; a = b; b = t; }
+
+ORBX_HD void push_heap(SortElem* f, long hole, long top, SortElem v) {
+  long parent = (hole - 1) / 2;
+  while (hole > top && lt(f[parent], v)) {
+    f[hole] = f[parent];
+    hole = parent;
+    parent = (hole - 1) / 2;
+  }
+  f[hole] = v;
+}
+
+ORBX_HD void adjust_heap(SortElem* f, long hole, long len, SortElem v) {
+  const long top = hole;
+  long child = hole;
+  while (child < (len - 1) / 2) {
+    child = 2 * (child + 1);
+    if (lt(f[child], f[child - 1])) child--;
+    f[hole] = f[child];
+    hole = child;
+  }
+  if ((len & 1) == 0 && child == (len - 2) / 2) {
+    child = 2 * (child + 1);
+    f[hole] = f[child - 1];
+    hole = child - 1;
+  }
+  push_heap(f, hole, top, v);
+}
+
+// std::__partial_sort(first, last, last): make_heap + sort_heap (the heap_select loop is empty)
+ORBX_HD void heap_sort(SortElem* f, long len) {
+  if (len >= 2) {
+    long parent = (len - 2) / 2;
+    for (;;) {
+      SortElem v = f[parent];
+      adjust_heap(f, parent, len, v);
+      if (parent == 0) break;
+      parent--;
+    }
+  }
+  long last = len;
+  while (last > 1) {
+    --last;
+    SortElem v = f[last];
+    f[last] = f[0];
+    adjust_heap(f, 0, last, v);
+  }
+}
+
+ORBX_HD void unguarded_linear_insert(SortElem* f, long last) {
+  SortElem v = f[last];
+  long next = last - 1;
+  while (lt(v, f[next])) {
+    f[last] = f[next];
+    last = next;
+    --next;
+  }
+  f[last] = v;
+}
+
+ORBX_HD void insertion_sort(SortElem* f, long first, long last) {
+  if (first == last) return;
+  for (long i = first + 1; i != last; ++i) {
+    if (lt(f[i], f[first])) {
+      SortElem v = f[i];
+      for (long j = i; j > first; --j) f[j] = f[j - 1];
+      f[first] = v;
+    } else {
+      unguarded_linear_insert(f, i);
+    }
+  }
+}
+
+}  // namespace ss
+
+// Sorts f[0..n) exactly as std::sort(f, f + n, [](a, b){ return a.key < b.key; }) does.
+ORBX_HD void stdsort_emul(SortElem* f, long n) {
+  using namespace ss;
+  if (n <= 0) return;
+  // __introsort_loop with an explicit stack of (first, last, depth) for the right-hand recursions
+  long stF[64], stL[64];
+  int stD[64];
+  int sp = 0;
+  int lg = 0;
+  for (long t = n; t > 1; t >>= 1) ++lg;
+  long first = 0, last = n;
+  int depth = 2 * lg;
+  for (;;) {
+    while (last - first > 16) {
+      if (depth == 0) {
+        heap_sort(f + first, last - first);
+        break;
+      }
+      --depth;
+      // __move_median_to_first(first, first+1, mid, last-1)
+      const long a = first + 1, b = first + (last - first) / 2, c = last - 1;
+      if (lt(f[a], f[b])) {
+        if (lt(f[b], f[c])) swp(f[first], f[b]);
+        else if (lt(f[a], f[c])) swp(f[first], f[c]);
+        else swp(f[first], f[a]);
+      } else if (lt(f[a], f[c])) swp(f[first], f[a]);
+      else if (lt(f[b], f[c])) swp(f[first], f[c]);
+      else swp(f[first], f[b]);
+      // __unguarded_partition(first+1, last, first)
+      long lo = first + 1, hi = last;
+      for (;;) {
+        while (lt(f[lo], f[first])) ++lo;
+        --hi;
+        while (lt(f[first], f[hi])) --hi;
+        if (!(lo < hi)) break;
+        swp(f[lo], f[hi]);
+        ++lo;
+      }
+      // recurse on [lo, last) first (depth-first, exactly as the recursive call would), then
+      // continue with [first, lo): the right part must be fully processed before the left.
+      // The recursion is tail-structured: right call runs to completion, then the loop
+      // continues on the left.  Emulate by pushing the LEFT continuation and looping on the right.
+      stF[sp] = first; stL[sp] = lo; stD[sp] = depth; ++sp;
+      first = lo;
+    }
+    if (sp == 0) break;
+    --sp;
+    first = stF[sp]; last = stL[sp]; depth = stD[sp];
+  }
+  // __final_insertion_sort
+  if (n > 16) {
+    insertion_sort(f, 0, 16);
+    for (long i = 16; i < n; ++i) unguarded_linear_insert(f, i);
+  } else {
+    insertion_sort(f, 0, n);
+  }
+}
+
+}  // namespace orbx

@@ -1,0 +1,178 @@
+// Host tables of a context: every float -> int decision the reference makes on the CPU (level
+// sizes, resize coefficients, per-level quotas, umax, cell geometry, quadtree roots) is made here
+// once, on the host, with the reference's own expressions, and uploaded as integers.  The GPU
+// never re-derives them.
+#include <cmath>
+#include <cstring>
+
+#include "ctx.cuh"
+
+namespace orbx {
+
+static inline int cv_round_f(float v) { return (int)lrintf(v); }    // cvRound: half-to-even
+static inline int cv_round_d(double v) { return (int)lrint(v); }
+static inline int cv_floor_f(float v) { int i = (int)v; return i - (i > v); }
+static inline int cv_ceil_f(float v) { int i = (int)v; return i + (i < v); }
+
+// ORBextractor::ORBextractor, Features/ORBextractor.cpp:492-595.  Returns ORBX_ERR_CTOR where the
+// reference calls exit(1).
+int compute_tables(int nfeatures, float scaleFactorF, int nlevels, HostTables& t) {
+  const double scaleFactor = scaleFactorF;  // the member is a double holding the float (hpp:142)
+  if (nlevels < 1 || nlevels > kMaxLevels) return ORBX_ERR_ARG;
+  if (scaleFactor == 1.0 && nlevels > 1) return ORBX_ERR_CTOR;  // :502-505
+  t.scale.assign(nlevels, 1.0f);
+  t.sigma2.assign(nlevels, 1.0f);
+  for (int i = 1; i < nlevels; ++i) {
+    t.scale[i] = (float)(t.scale[i - 1] * scaleFactor);  // :512
+    t.sigma2[i] = t.scale[i] * t.scale[i];                // :513
+  }
+  t.invScale.resize(nlevels);
+  t.invSigma2.resize(nlevels);
+  for (int i = 0; i < nlevels; ++i) {
+    t.invScale[i] = 1.0f / t.scale[i];
+    t.invSigma2[i] = 1.0f / t.sigma2[i];
+  }
+  // quotas: geometric series in float, cvRound per level, remainder to the last level (:529-548)
+  t.perLevel.assign(nlevels, 0);
+  const float factor = (float)(1.0f / scaleFactor);
+  float want = nfeatures * (1 - factor) / (1 - (float)std::pow((double)factor, (double)(float)nlevels));
+  int sum = 0;
+  for (int l = 0; l < nlevels - 1; ++l) {
+    t.perLevel[l] = cv_round_f(want);
+    sum += t.perLevel[l];
+    want *= factor;
+  }
+  t.perLevel[nlevels - 1] = nfeatures - sum > 0 ? nfeatures - sum : 0;
+  // umax (:562-594)
+  std::memset(t.umax, 0, sizeof(t.umax));
+  const int vmax = cv_floor_f(kHalfPatch * std::sqrt(2.f) / 2 + 1);
+  const int vmin = cv_ceil_f(kHalfPatch * std::sqrt(2.f) / 2);
+  const double hp2 = kHalfPatch * kHalfPatch;
+  for (int v = 0; v <= vmax; ++v) t.umax[v] = cv_round_d(std::sqrt(hp2 - v * v));
+  for (int v = kHalfPatch, v0 = 0; v >= vmin; --v) {
+    while (t.umax[v0] == t.umax[v0 + 1]) ++v0;
+    t.umax[v] = v0;
+    ++v0;
+  }
+  return ORBX_OK;
+}
+
+// cv::resize INTER_LINEAR 8U coefficient tables.  Layout: xofs | xcoef | yofs | ycoef.
+void build_resize_tab(int sw, int sh, int dw, int dh, std::vector<int>& tab) {
+  tab.assign(2 * (size_t)dw + 2 * (size_t)dh, 0);
+  const double sxs = 1. / ((double)dw / sw), sys = 1. / ((double)dh / sh);
+  for (int d = 0; d < dw; ++d) {
+    float f = (float)((d + 0.5) * sxs - 0.5);
+    int s = cv_floor_f(f);
+    f -= s;
+    if (s < 0) { f = 0; s = 0; }
+    if (s >= sw - 1) { f = 0; s = sw - 1; }
+    const int a0 = cv_round_f((1.f - f) * 2048.f), a1 = cv_round_f(f * 2048.f);
+    tab[d] = s;
+    tab[dw + d] = (a0 & 0xffff) | (a1 << 16);
+  }
+  for (int d = 0; d < dh; ++d) {
+    float f = (float)((d + 0.5) * sys - 0.5);
+    const int s = cv_floor_f(f);
+    f -= s;
+    const int b0 = cv_round_f((1.f - f) * 2048.f), b1 = cv_round_f(f * 2048.f);
+    tab[2 * dw + d] = s;  // clipped to [0, sh-1] at use, like OpenCV's row loop
+    tab[2 * dw + dh + d] = (b0 & 0xffff) | (b1 << 16);
+  }
+}
+
+static inline u32 align_up(u32 v, u32 a) { return (v + a - 1) / a * a; }
+
+// Fills P.lv[], the cell table, the blur tile table and the quadtree root tables.
+// Returns ORBX_ERR_ARG for shapes on which the reference itself is undefined (a level narrower
+// than 67 px gives nCols == 0 and a division by zero at :1073) and ORBX_ERR_ASPECT where
+// DistributeOctTree would index an empty root vector (:706, aspect ratio rounding to 0).
+int build_geometry(Params& P, const HostTables& T, std::vector<CellDesc>& cells, std::vector<BlurTile>& tiles,
+                   std::vector<u8>& rootTab, std::vector<int>& rootEdges) {
+  u32 imgOff = 0, candOff = 0, nodeOff = 0;
+  int kpOff = 0;
+  cells.clear(); tiles.clear(); rootTab.clear(); rootEdges.clear();
+  for (int l = 0; l < P.nlevels; ++l) {
+    LevelInfo& L = P.lv[l];
+    L.w = cv_round_f((float)P.W * T.invScale[l]);  // :1662-1663
+    L.h = cv_round_f((float)P.H * T.invScale[l]);
+    L.pitch = (int)align_up((u32)L.w, 128);
+    L.imgOff = imgOff;
+    imgOff += align_up((u32)L.pitch * (u32)L.h, 256);
+    L.scale = T.scale[l];
+    L.patchSize = (float)(int)(kPatch * T.scale[l]);  // :1165
+    L.quota = T.perLevel[l];
+    L.kpOff = kpOff;
+    kpOff += L.quota;
+    // cell grid, :1056-1075
+    const int minBX = kMinBorder, minBY = kMinBorder;
+    const int maxBX = L.w - kEdge + 3, maxBY = L.h - kEdge + 3;
+    const float width = (float)(maxBX - minBX), height = (float)(maxBY - minBY);
+    L.distW = maxBX - minBX;
+    L.distH = maxBY - minBY;
+    L.nCols = (int)(width / 35.f);
+    L.nRows = (int)(height / 35.f);
+    if (L.nCols < 1 || L.nRows < 1 || L.w > 32000 || L.h > 32000) return ORBX_ERR_ARG;
+    L.wCell = (int)std::ceil(width / L.nCols);
+    L.hCell = (int)std::ceil(height / L.nRows);
+    if (L.wCell + 6 > kMaxCellDim || L.hCell + 6 > kMaxCellDim) return ORBX_ERR_ARG;
+    L.cellBase = (int)cells.size();
+    int cap = 0;
+    for (int i = 0; i < L.nRows; ++i) {
+      const float iniY = (float)(minBY + i * L.hCell);
+      float maxY = iniY + L.hCell + 6;
+      if (iniY >= maxBY - 3) continue;  // :1088
+      if (maxY > maxBY) maxY = (float)maxBY;
+      for (int j = 0; j < L.nCols; ++j) {
+        const float iniX = (float)(minBX + j * L.wCell);
+        float maxX = iniX + L.wCell + 6;
+        if (iniX >= maxBX - 6) continue;  // :1101
+        if (maxX > maxBX) maxX = (float)maxBX;
+        CellDesc c;
+        c.level = (short)l; c.pad = 0;
+        c.x0 = (short)iniX; c.y0 = (short)iniY; c.x1 = (short)maxX; c.y1 = (short)maxY;
+        c.sx = (short)(j * L.wCell); c.sy = (short)(i * L.hCell);
+        c.index = i * L.nCols + j;
+        const int iw = c.x1 - c.x0 - 6, ih = c.y1 - c.y0 - 6;
+        if (iw < 1 || ih < 1) continue;  // cv::FAST yields nothing for ROIs under 7 px
+        cells.push_back(c);
+        cap += ((iw + 1) / 2) * ((ih + 1) / 2);  // NMS survivors are never 8-adjacent
+      }
+    }
+    if ((u32)(L.nCols * L.nRows) >= (1u << 18)) return ORBX_ERR_ARG;  // order key has 18 cell bits
+    L.candCap = cap > 0 ? cap : 1;
+    L.candOff = candOff;
+    candOff += align_up((u32)L.candCap, 32);
+    // quadtree roots, :706-739, and the key -> root map, :743-748
+    L.nIni = (int)std::round((float)(maxBX - minBX) / (maxBY - minBY));
+    if (L.nIni < 1) return ORBX_ERR_ASPECT;
+    if (L.nIni > 255) return ORBX_ERR_ARG;
+    const float hX = (float)(maxBX - minBX) / L.nIni;
+    L.rootEdgeOff = (u32)rootEdges.size();
+    for (int i = 0; i <= L.nIni; ++i) rootEdges.push_back((int)(hX * (float)i));
+    L.rootTabOff = (u32)rootTab.size();
+    for (int x = 0; x <= L.distW; ++x) {
+      int r = (int)((float)x / hX);
+      if (r >= L.nIni) r = L.nIni - 1;  // unreachable for real candidates (x < distW - 3)
+      rootTab.push_back((u8)r);
+    }
+    L.nodeCap = 8 * L.quota + 64 + 4 * L.nIni;
+    L.nodeOff = nodeOff;
+    nodeOff += align_up((u32)L.nodeCap, 32);
+    // blur tiles of 128 x 32
+    for (int y = 0; y < L.h; y += 32)
+      for (int x = 0; x < L.w; x += 128) {
+        BlurTile t;
+        t.level = (short)l; t.pad = 0; t.x0 = (short)x; t.y0 = (short)y;
+        tiles.push_back(t);
+      }
+  }
+  P.slabBytes = imgOff;
+  P.candTotal = candOff;
+  P.nodeTotal = nodeOff;
+  P.nCells = (int)cells.size();
+  P.nBlurTiles = (int)tiles.size();
+  return ORBX_OK;
+}
+
+}  // namespace orbx
