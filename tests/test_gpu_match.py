@@ -1,0 +1,146 @@
+"""Frame glue (undistort + 64x48 grid), GetFeaturesInArea, SearchForInitialization and the
+device-resident stream path against the oracle (reference: SlamTypes/Frame.cpp:40-206,
+Features/ORBmatcher.cpp:11-183).  Bit-exact: undistorted coordinates, grid lists, candidate order,
+vnMatches12, the returned count (with its double-decrement quirk) and the three printed counters."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def fe():
+    from orb_slam_tracking_b200 import frontend
+    return frontend
+
+
+@pytest.fixture(scope="module")
+def synth():
+    from orb_slam_tracking_b200 import synth
+    return synth
+
+
+def _pair(fe, oracle, synth, W, H, nf, ini, mn, pair_index, K4=None, D4=None):
+    if K4 is None:
+        K4, D4 = synth.camera_for(W, H)
+    E = fe.ORBextractor(nf, 1.2, 8, ini, mn, W, H)
+    bounds = E.set_camera(K4, D4)
+    assert np.array_equal(bounds, oracle.image_bounds(W, H, K4, D4))
+    R = oracle.Extractor(nf, 1.2, 8, ini, mn)
+    imgs = synth.frame_pair(pair_index, W, H)
+    G, O = [], []
+    for im in imgs:
+        G.append(fe.Frame(E, im))
+        k, d, _ = R(im)
+        O.append(oracle.Frame(k, d, K4, D4, bounds))
+    return E, G, O
+
+
+@pytest.mark.parametrize("shape", [(752, 480, 1200), (640, 480, 1000), (1241, 376, 2000)])
+def test_frame_glue(fe, oracle, synth, shape):
+    W, H, nf = shape
+    E, G, O = _pair(fe, oracle, synth, W, H, nf, 20, 7, 21)
+    for g, o in zip(G, O):
+        ku = o.keys_un()
+        assert g.N == o.N
+        for f in ku.dtype.names:
+            assert np.array_equal(g.mvKeysUn[f].view(np.uint32), ku[f].view(np.uint32)), f
+        off, idx = o.grid()
+        assert np.array_equal(g.grid_offsets, off)
+        assert np.array_equal(g.grid_indices, idx)
+    E.close()
+
+
+def test_features_in_area(fe, oracle, synth):
+    E, G, O = _pair(fe, oracle, synth, 752, 480, 1200, 20, 7, 22)
+    rng = np.random.default_rng(1)
+    g, o = G[1], O[1]
+    qs = [(float(x), float(y), float(r), lv) for x, y, r, lv in
+          zip(rng.uniform(-100, 900, 60), rng.uniform(-100, 600, 60), rng.uniform(5, 300, 60), rng.integers(-1, 4, 60))]
+    qs += [(376.0, 240.0, 8192.0, 0), (0.0, 0.0, 100.0, -1), (5000.0, 5000.0, 10.0, 0), (-5000.0, 0.0, 10.0, 0)]
+    for x, y, r, lv in qs:
+        a = g.GetFeaturesInArea(x, y, r, int(lv), int(lv))
+        b = o.features_in_area(x, y, r, int(lv), int(lv))
+        assert np.array_equal(a, b), (x, y, r, lv)
+    E.close()
+
+
+@pytest.mark.parametrize("cfg", [(640, 480, 1000, 20, 7), (752, 480, 2000, 0, 0), (752, 480, 1200, 20, 7),
+                                 (1241, 376, 2000, 20, 7)])
+def test_search_for_initialization(fe, oracle, synth, cfg):
+    W, H, nf, ini, mn = cfg
+    for pair_index in (30, 31):
+        E, G, O = _pair(fe, oracle, synth, W, H, nf, ini, mn, pair_index)
+        for nnratio, ori, window in ((0.9, True, 100), (0.6, True, 100), (0.9, False, 50), (0.9, True, 8192)):
+            n, m12, cnt = fe.ORBmatcher(nnratio, ori).SearchForInitialization(G[0], G[1], window)
+            rn, rm12, rcnt = oracle.search_for_initialization(O[0], O[1], nnratio, ori, window)
+            assert np.array_equal(m12, rm12), (nnratio, ori, window, int((m12 != rm12).sum()))
+            assert n == rn and np.array_equal(cnt, rcnt), (n, rn, cnt, rcnt)
+        # identical frames: every level-0 key finds itself at distance 0
+        n, m12, _ = fe.ORBmatcher(0.9, True).SearchForInitialization(G[0], G[0], 100)
+        rn, rm12, _ = oracle.search_for_initialization(O[0], O[0], 0.9, True, 100)
+        assert n == rn and np.array_equal(m12, rm12)
+        E.close()
+
+
+def test_empty_frames(fe, oracle):
+    W, H = 640, 480
+    E = fe.ORBextractor(1000, 1.2, 8, 20, 7, W, H)
+    E.set_camera(np.array([500, 500, 320, 240], np.float32), np.zeros(4, np.float32))
+    flat = np.full((H, W), 50, np.uint8)
+    F = fe.Frame(E, flat)
+    assert F.N == 0 and F.grid_offsets[-1] == 0
+    n, m12, cnt = fe.ORBmatcher(0.9, True).SearchForInitialization(F, F, 100)
+    assert n == 0 and len(m12) == 0 and not cnt.any()
+    E.close()
+
+
+def test_descriptor_distance(fe, oracle):
+    rng = np.random.default_rng(3)
+    a = rng.integers(0, 256, (500, 32), dtype=np.uint8)
+    b = rng.integers(0, 256, (500, 32), dtype=np.uint8)
+    b[:50] = a[:50]
+    ref = np.array([oracle.descriptor_distance(x, y) for x, y in zip(a, b)])
+    host = np.array([fe.ORBmatcher.DescriptorDistance(x, y) for x, y in zip(a, b)])
+    assert np.array_equal(ref, host)
+    from orb_slam_tracking_b200.capi import lib, ptr, check
+    E = fe.ORBextractor(100, 1.2, 2, 20, 7, 640, 480)
+    out = np.zeros(500, np.int32)
+    check(lib().orbx_descriptor_distance_batch(E._h, ptr(a), ptr(b), 500, ptr(out)), E._h)
+    assert np.array_equal(out, ref)
+    E.close()
+
+
+@pytest.mark.parametrize("cfg", [(640, 480, 1000, 20, 7, 8), (752, 480, 1200, 20, 7, 6)])
+def test_stream_path(fe, oracle, synth, cfg):
+    W, H, nf, ini, mn, B = cfg
+    K4, D4 = synth.camera_for(W, H)
+    E = fe.ORBextractor(nf, 1.2, 8, ini, mn, W, H, max_batch=B)
+    bounds = E.set_camera(K4, D4)
+    R = oracle.Extractor(nf, 1.2, 8, ini, mn)
+    imgs = synth.frames(B, W, H, first_pair=40)
+    S = fe.Stream(E, 0.9, True, 100)
+    S.upload(imgs)
+    S.run(B)
+    out = S.download(B)
+    frames = []
+    for i in range(B):
+        k, d, _ = R(imgs[i])
+        n = out["n"][i]
+        assert n == len(k)
+        assert np.array_equal(out["kps"][i, :n].view(np.uint8), k.view(np.uint8)), i
+        assert np.array_equal(out["desc"][i, :n], d), i
+        F = oracle.Frame(k, d, K4, D4, bounds)
+        assert np.array_equal(out["kps_un"][i, :n].view(np.uint8), F.keys_un().view(np.uint8)), i
+        frames.append(F)
+    for p in range(B // 2):
+        rn, rm12, rcnt = oracle.search_for_initialization(frames[2 * p], frames[2 * p + 1], 0.9, True, 100)
+        assert out["nmatches"][p] == rn, p
+        assert np.array_equal(out["matches12"][p, :len(rm12)], rm12), p
+        assert np.array_equal(out["counters"][p], rcnt), p
+    # size-independent property at full batch: re-running the same batch is idempotent
+    S.run(B)
+    out2 = S.download(B)
+    for k in out:
+        assert np.array_equal(out[k].view(np.uint8), out2[k].view(np.uint8)), k
+    E.close()
