@@ -1,0 +1,308 @@
+#!/usr/bin/env python
+"""ORB front-end throughput: frames/s of extract + Frame glue + SearchForInitialization.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--batch B] [--workload tum]
+
+A "step" is one pass of the whole hot path over one batch of B synthetic frames (B/2 frame
+pairs).  `value` is measured with the batch already resident in HBM; `e2e` goes through the
+same C ABI calls with host buffers (pinned H2D of the images, D2H of keypoints, descriptors and
+matches inside the timed region).  N > 1: one process per GPU (torchrun), frame pairs sharded per
+rank, no collective on the data path (weak scaling); the barrier and max-over-ranks timing use
+torch.distributed.  --impl reference times the CPU restatement of the reference (oracle/) on the
+host cores.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+WORKLOADS = {
+    # BASELINE.json configs[1..4]; configs[0] (demo pair) is a parity-test case
+    "tum": dict(W=640, H=480, nfeatures=1000, ini=20, mn=7, batch=512, desc="synthetic TUM-shape 640x480, 1000 kp"),
+    "euroc": dict(W=752, H=480, nfeatures=1200, ini=20, mn=7, batch=512, desc="synthetic EuRoC-shape 752x480, 1200 kp"),
+    "kitti": dict(W=1241, H=376, nfeatures=2000, ini=20, mn=7, batch=256, desc="synthetic KITTI-shape 1241x376, 2000 kp"),
+    "uhd": dict(W=3840, H=2160, nfeatures=8000, ini=20, mn=7, batch=16, desc="synthetic 3840x2160, 8000 kp"),
+}
+METRIC = "ORB frames/s (extract+match, 640x480, 1k kp)"
+UNIT = "frames/s"
+NNRATIO, WINDOW = 0.9, 100
+STAGES = ["pyramid", "fast", "quadtree", "blur", "describe", "pack", "glue", "match"]
+
+
+def level_sizes(W, H, nlevels=8, sf=1.2):
+    s, out = np.float32(1.0), []
+    for l in range(nlevels):
+        inv = np.float32(1.0) / s
+        out.append((int(np.rint(np.float32(W) * inv)), int(np.rint(np.float32(H) * inv))))
+        s = np.float32(np.float64(s) * np.float64(np.float32(sf)))
+    return out
+
+
+def algorithmic_bytes(W, H, K):
+    """per-frame algorithmic bytes of each stage (u8 images, no pads)."""
+    P = [w * h for w, h in level_sizes(W, H)]
+    S = sum(P)
+    return {"pyramid": 2 * S - P[0] - P[-1], "fast": S, "blur": 2 * S, "describe": K * (749 + 512), "pack": K * 60,
+            "frame": 5 * S - P[0] - P[-1] + 1321 * K}
+
+
+class ClockSampler:
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.rows, self.proc = device, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.QUERY,
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm = [float(r[1]) for r in self.rows if len(r) >= 9 and r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if len(r) >= 9 and r[2].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            if len(r) >= 9:
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        return float(json.loads(p.read_text())["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+def host_threads():
+    return len(os.sched_getaffinity(0))
+
+
+def cpu_baseline(wl, n_frames, threads, repeats=1):
+    """Oracle (CPU restatement of the reference path) on a bounded sample of the same workload.
+    Only the processing is timed (images are generated before)."""
+    from oracle import orb_oracle as O
+    from orb_slam_tracking_b200 import synth
+    imgs = synth.tile_frames(n_frames, wl["W"], wl["H"], unique_pairs=min(8, n_frames // 2))
+    K4, D4 = synth.camera_for(wl["W"], wl["H"])
+    a = (wl["nfeatures"], 1.2, 8, wl["ini"], wl["mn"], K4, D4, WINDOW, NNRATIO, threads)
+    O.run_stream(imgs[:2 * threads], *a)  # warm-up
+    t = time.perf_counter()
+    for _ in range(repeats):
+        O.run_stream(imgs, *a)
+    dt = time.perf_counter() - t
+    return repeats * n_frames / dt, dt
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+def run_reference(args, wl):
+    """The reference's CPU path (oracle restatement: the reference itself needs OpenCV C++ and
+    does not build here) on all host threads; rank 0 only."""
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    threads = host_threads()
+    per_step = max(8 * threads, 32) if wl["W"] * wl["H"] < 2_000_000 else 2 * threads
+    fps, dt = cpu_baseline(wl, per_step, threads, repeats=args.steps)
+    sample = "%d frames (%d pairs) of %s per step, %d host threads" % (per_step, per_step // 2, wl["desc"], threads)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": wl["desc"], "frames_per_step": per_step, "nnratio": NNRATIO, "window": WINDOW},
+        "cpu_baseline": {"value": fps, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }), flush=True)
+
+
+def run_ours(args, wl):
+    import ctypes as C
+    import torch
+    from orb_slam_tracking_b200 import capi, frontend as fe, synth
+    rank, world, local = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    use_dist = world > 1
+    torch.cuda.set_device(local)
+    if use_dist:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    B = args.batch or wl["batch"]
+    B -= B % 2
+    W, H, nf = wl["W"], wl["H"], wl["nfeatures"]
+    L = capi.lib()
+    E = fe.ORBextractor(nf, 1.2, 8, wl["ini"], wl["mn"], W, H, max_batch=B, device=local)
+    K4, D4 = synth.camera_for(W, H)
+    E.set_camera(K4, D4)
+    S = fe.Stream(E, NNRATIO, True, WINDOW)
+    # synthetic frames: 16 distinct pairs per rank, tiled to the batch (every slot is processed independently)
+    imgs = synth.tile_frames(B, W, H, unique_pairs=min(16, B // 2), first_pair=1000 * rank)
+    nbytes_in = imgs.nbytes
+    hp = L.orbx_host_alloc(nbytes_in)
+    assert hp, "pinned allocation failed"
+    pinned = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_ubyte)), shape=(nbytes_in,)).reshape(imgs.shape)
+    pinned[...] = imgs
+    cap = E.cap
+    # pinned result buffers for the e2e path
+    sizes = {"kps": B * cap * 28, "kps_un": B * cap * 28, "desc": B * cap * 32, "n": B * 4, "m12": (B // 2) * cap * 4,
+             "nm": (B // 2) * 4, "cnt": (B // 2) * 12}
+    res = {k: L.orbx_host_alloc(v) for k, v in sizes.items()}
+    nbytes_out = sum(sizes.values())
+
+    def barrier():
+        if use_dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident():
+        capi.check(L.orbx_stream_run(E._h, B, NNRATIO, 1, WINDOW), E._h)
+
+    def step_e2e():
+        capi.check(L.orbx_stream_upload(E._h, hp, B), E._h)
+        capi.check(L.orbx_stream_run(E._h, B, NNRATIO, 1, WINDOW), E._h)
+        capi.check(L.orbx_stream_download(E._h, B, res["kps"], res["kps_un"], res["desc"], cap, res["n"], res["m12"],
+                                          res["nm"], res["cnt"]), E._h)
+
+    def timed(fn, steps):
+        """K steps bracketed by barrier + synchronize; device time from CUDA events on the
+        context's own stream (max over ranks)."""
+        barrier()
+        ms = C.c_float(0)
+        capi.check(L.orbx_timer_start(E._h), E._h)
+        for _ in range(steps):
+            fn()
+        capi.check(L.orbx_timer_stop(E._h, C.byref(ms)), E._h)
+        barrier()
+        t = torch.tensor([ms.value], device="cuda", dtype=torch.float64)
+        if use_dist:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    capi.check(L.orbx_stream_upload(E._h, hp, B), E._h)
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    S.sync()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ms = timed(step_resident, args.steps)
+    launches = L.orbx_last_launch_count(E._h) * args.steps
+    clocks = sampler.stop() if rank == 0 else None
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, args.steps)
+    # per-stage device times (separate pass: the stage events are not in the timed region above)
+    L.orbx_set_stage_timing(E._h, 1)
+    acc = np.zeros(8)
+    reps = max(3, min(args.steps, 10))
+    for _ in range(reps):
+        step_resident()
+        S.sync()
+        st = np.zeros(8, np.float32)
+        L.orbx_get_stage_times(E._h, capi.ptr(st))
+        acc += st
+    L.orbx_set_stage_timing(E._h, 0)
+    stage_ms = acc / reps
+    # sanity of the work done: every frame produced keypoints and pairs produced matches
+    n_out = np.ctypeslib.as_array(C.cast(res["n"], C.POINTER(C.c_int32)), shape=(B,)).copy()
+    nm = np.ctypeslib.as_array(C.cast(res["nm"], C.POINTER(C.c_int32)), shape=(B // 2,)).copy()
+    assert n_out.min() > 0 and nm.sum() > 0, "pipeline produced no features / matches"
+
+    if rank == 0:
+        fps = world * B * args.steps / (ms * 1e-3)
+        fps_e2e = world * B * args.steps / (ms_e2e * 1e-3)
+        ab = algorithmic_bytes(W, H, float(n_out.mean()))
+        peak, how = measured_peak()
+        hbm_stages = {"pyramid": 0, "fast": 1, "blur": 3}
+        dom = max(hbm_stages, key=lambda s: stage_ms[hbm_stages[s]])
+        dom_ms = float(stage_ms[hbm_stages[dom]])
+        n_launch_dom = 7 if dom == "pyramid" else 1
+        achieved = ab[dom] * B / (dom_ms * 1e-3) / 1e9
+        line = {
+            "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic",
+            "config": {"workload": wl["desc"], "frames_per_step_per_gpu": B, "pairs_per_step_per_gpu": B // 2,
+                       "nlevels": 8, "scale": 1.2, "fast_th": [wl["ini"], wl["mn"]], "nnratio": NNRATIO, "window": WINDOW,
+                       "l2": "batch working set (%.0f MB of pyramids) exceeds the 126 MB L2; no flush" % (2 * B * 1.25 * W * H / 307200),
+                       "sharding": "independent frame pairs per rank, no collective"},
+            "e2e": {"value": fps_e2e, "unit": UNIT, "h2d_bytes_per_step": int(nbytes_in), "d2h_bytes_per_step": int(nbytes_out),
+                    "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "stage_ms_per_step": {STAGES[i]: round(float(stage_ms[i]), 4) for i in range(8) if i != 5},
+            "pipeline_hbm": {"algorithmic_GBps": ab["frame"] * fps / world / 1e9, "frac_of_peak": ab["frame"] * fps / world / 1e9 / peak,
+                             "bytes_per_frame": ab["frame"]},
+            "roofline": {"kernel": {"pyramid": "k_resize (7 launches)", "fast": "k_fast", "blur": "k_blur"}[dom],
+                         "bound": "hbm", "achieved": achieved, "peak": peak, "peak_source": how, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": None, "launches_per_step": n_launch_dom,
+                         "ms_per_step": dom_ms, "algorithmic_bytes_per_step": int(ab[dom] * B)},
+        }
+        if world == 1 and not args.no_cpu:
+            threads = host_threads()
+            n_cpu = max(16 * threads, 64) if W * H < 2_000_000 else 2 * threads
+            v, dt = cpu_baseline(wl, n_cpu, threads)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": "%d frames (%d pairs) of the same workload, %.1f s" % (n_cpu, n_cpu // 2, dt)}
+        print(json.dumps(line), flush=True)
+    for p in list(res.values()) + [hp]:
+        L.orbx_host_free(p)
+    E.close()
+    if use_dist:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="tum", choices=sorted(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, wl)
+    else:
+        run_ours(args, wl)
+
+
+if __name__ == "__main__":
+    main()

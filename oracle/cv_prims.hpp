@@ -22,6 +22,9 @@
 // the float formulas here rely on separate multiply/add roundings.
 #pragma once
 #include <cfloat>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -32,8 +35,13 @@ namespace orc {
 typedef unsigned char u8;
 
 // ---- rounding helpers (OpenCV fast_math.hpp semantics on x86-64 SSE2) -------------
-static inline int cv_round(double v) { return (int)std::lrint(v); }   // cvtsd2si: half-to-even
-static inline int cv_round(float v) { return (int)std::lrintf(v); }   // cvtss2si
+#if defined(__SSE2__)
+static inline int cv_round(double v) { return _mm_cvtsd_si32(_mm_set_sd(v)); }  // as OpenCV: cvtsd2si, half-to-even
+static inline int cv_round(float v) { return _mm_cvtss_si32(_mm_set_ss(v)); }   // cvtss2si
+#else
+static inline int cv_round(double v) { return (int)std::lrint(v); }
+static inline int cv_round(float v) { return (int)std::lrintf(v); }
+#endif
 static inline int cv_floor(float v) { int i = (int)v; return i - (i > v); }
 static inline int cv_floor(double v) { int i = (int)v; return i - (i > v); }
 static inline int cv_ceil(float v) { int i = (int)v; return i + (i < v); }
@@ -139,11 +147,13 @@ static const int kRingDy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1,
 static inline int fast_arc_value(const u8* p, const ptrdiff_t* ofs, int t) {
   int d[32];
   const int v = p[0];
-  for (int k = 0; k < 16; ++k) d[k] = v - p[ofs[k]];
   // a 9-arc contains one pixel of every opposing pair: if for some pair both |d| <= t, m <= t
-  for (int k = 0; k < 8; ++k) {
-    int a = d[k], b = d[k + 8];
+  static const int order[8] = {0, 4, 2, 6, 1, 3, 5, 7};
+  for (int i = 0; i < 8; ++i) {
+    const int k = order[i];
+    const int a = v - p[ofs[k]], b = v - p[ofs[k + 8]];
     if (a <= t && a >= -t && b <= t && b >= -t) return 0;
+    d[k] = a; d[k + 8] = b;
   }
   for (int k = 16; k < 32; ++k) d[k] = d[k - 16];
   int mn2[24], mx2[24], mn4[20], mx4[20];
@@ -233,22 +243,25 @@ static inline float fast_atan2(float y, float x) {
 // Fixed-point separable kernel {18,34,48,56,48,34,18}/256 (8.8 horizontal, 8.16 total).
 static inline void gaussian_blur7_u8(const u8* src, int w, int h, size_t sstep, u8* dst,
                                      size_t dstep) {
-  static const int k[7] = {18, 34, 48, 56, 48, 34, 18};
-  std::vector<unsigned> hbuf((size_t)w * h);
+  // row pass into a ring of 7 u16 rows (reflected source rows), column pass out of it
+  std::vector<u8> prow((size_t)w + 6);
+  std::vector<unsigned short> ring((size_t)7 * w);
+  auto hrow = [&](int y, unsigned short* out) {
+    const u8* s = src + (size_t)reflect101(y, h) * sstep;
+    for (int x = -3; x < w + 3; ++x) prow[(size_t)(x + 3)] = s[reflect101(x, w)];
+    const u8* p = prow.data();
+    for (int x = 0; x < w; ++x)
+      out[x] = (unsigned short)(18 * (p[x] + p[x + 6]) + 34 * (p[x + 1] + p[x + 5]) + 48 * (p[x + 2] + p[x + 4]) +
+                                56 * p[x + 3]);
+  };
+  for (int y = -3; y < 3; ++y) hrow(y, &ring[(size_t)((y + 7) % 7) * w]);
   for (int y = 0; y < h; ++y) {
-    const u8* s = src + (size_t)y * sstep;
-    for (int x = 0; x < w; ++x) {
-      unsigned acc = 0;
-      for (int i = 0; i < 7; ++i) acc += (unsigned)k[i] * s[reflect101(x + i - 3, w)];
-      hbuf[(size_t)y * w + x] = acc;
-    }
-  }
-  for (int y = 0; y < h; ++y) {
+    hrow(y + 3, &ring[(size_t)((y + 3) % 7) * w]);
+    const unsigned short* r[7];
+    for (int i = 0; i < 7; ++i) r[i] = &ring[(size_t)((y + i - 3 + 7) % 7) * w];
     u8* d = dst + (size_t)y * dstep;
     for (int x = 0; x < w; ++x) {
-      unsigned acc = 0;
-      for (int i = 0; i < 7; ++i)
-        acc += (unsigned)k[i] * hbuf[(size_t)reflect101(y + i - 3, h) * w + x];
+      unsigned acc = 18u * (r[0][x] + r[6][x]) + 34u * (r[1][x] + r[5][x]) + 48u * (r[2][x] + r[4][x]) + 56u * r[3][x];
       d[x] = (u8)((acc + 32768u) >> 16);
     }
   }
