@@ -10,6 +10,11 @@
 // CTA computes the peaks once and then applies the reference's rule: keep the peaks with
 // m > iniTh, or, if the cell has none, the peaks with m > minTh.
 //
+// Pass 1 is the hot loop: the opposing-pair rejection (every arc of 9 contains one pixel of each
+// opposing ring pair, so a pair with both |d| <= t proves m <= t) runs on FOUR pixels per thread
+// with byte-SWAR arithmetic on 32-bit words of the staged ROI; only the few surviving pixels get
+// the exact arc value.
+//
 // Survivors are appended to the level's candidate list with an atomic cursor; each carries its
 // position in the reference's emission order (cell row-major, then y, then x) inside its key, which
 // is all the quadtree needs ("first strict maximum" == max response, then min order).
@@ -17,7 +22,9 @@
 
 namespace orbx {
 
-constexpr int kStride = kMaxCellDim;
+constexpr int kSB = 96;          // staged row stride in bytes; byte b of a row <-> level column xb - 4 + b
+constexpr int kSW = kSB / 4;     // ... in words
+constexpr int kMaxRows = 76;     // hCell + 6 < 76
 
 __device__ __forceinline__ int arc_value(const int (&d)[16]) {
   // max over 16 arcs of min over 9 consecutive ring differences, and the same for -d
@@ -38,61 +45,87 @@ __device__ __forceinline__ int arc_value(const int (&d)[16]) {
   return max(A, B);
 }
 
+// bit 0 of each byte of the result = (that byte of a) > t, with K = (255 - t) * 0x00010001
+__device__ __forceinline__ u32 bytes_gt(u32 a, u32 K) {
+  const u32 e = (a & 0x00ff00ffu) + K, o = ((a >> 8) & 0x00ff00ffu) + K;
+  return ((e >> 8) & 0x00010001u) | (o & 0x01000100u);
+}
+// 4 bytes starting at byte offset 4g + dx (dx in [-3, 3]) of a staged row
+template <int DX>
+__device__ __forceinline__ u32 word_at(const u32* row, int g) {
+  if (DX == 0) return row[g];
+  if (DX > 0) return __funnelshift_r(row[g], row[g + 1], 8 * DX);
+  return __funnelshift_r(row[g - 1], row[g], 32 + 8 * DX);
+}
+
 __global__ void __launch_bounds__(256) k_fast(const __grid_constant__ Params P) {
-  __shared__ u8 sImg[kStride * kStride];
-  __shared__ u8 sM[kStride * kStride];          // m-map of the interior, 1-px zero frame
-  __shared__ unsigned short sList[kStride * kStride];
+  __shared__ u32 sImgW[kMaxRows * kSW];
+  __shared__ u32 sMW[kMaxRows * kSW];            // m-map, same geometry, zero outside the interior
+  __shared__ unsigned short sList[kMaxRows * kSB];
   __shared__ int sN, sPeaks, sIni, sMin, sBase, sCursor;
+  u8* const sImg = reinterpret_cast<u8*>(sImgW);
+  u8* const sM = reinterpret_cast<u8*>(sMW);
 
   const CellDesc c = P.cells[blockIdx.x];
   const int slot = blockIdx.y;
   const LevelInfo& L = P.lv[c.level];
   const int cw = c.x1 - c.x0, ch = c.y1 - c.y0;
   if (cw < 7 || ch < 7) return;  // cv::FAST returns nothing for such ROIs
-  const int iw = cw - 6, ih = ch - 6;
   const int tid = threadIdx.x;
-  const u8* __restrict__ img = level_ptr((const u8*)P.pyr, P, slot, c.level) + (size_t)c.y0 * L.pitch + c.x0;
+  const int a = c.x0 & 3, xb = c.x0 - a;       // aligned base column; ROI column rx <-> byte rx + 4 + a
+  const int nW = (a + cw + 3) >> 2;             // words per row holding ROI bytes (staged words 1 .. nW)
+  const u8* __restrict__ img = level_ptr((const u8*)P.pyr, P, slot, c.level) + (size_t)c.y0 * L.pitch + xb;
 
-  for (int i = tid; i < cw * ch; i += 256) {
-    const int r = i / cw, x = i - r * cw;
-    sImg[r * kStride + x] = __ldg(img + (size_t)r * L.pitch + x);
+  for (int i = tid; i < ch * kSW; i += 256) {
+    const int r = i / kSW, k = i - r * kSW;
+    u32 v = 0;
+    if (k >= 1 && k <= nW) v = __ldg(reinterpret_cast<const u32*>(img + (size_t)r * L.pitch) + (k - 1));
+    sImgW[i] = v;
+    sMW[i] = 0;
   }
-  for (int i = tid; i < (ih + 2) * kStride; i += 256) sM[i] = 0;
   if (tid == 0) { sN = 0; sPeaks = 0; sIni = 0; sMin = 0; sCursor = 0; }
   __syncthreads();
 
   const int tIni = min(max(P.iniTh, 0), 255), tMin = min(max(P.minTh, 0), 255);
   const int tq = min(tIni, tMin);
-  // ring offsets in shared-memory units, cv::FAST order
-  constexpr int o0 = 3 * kStride, o1 = 3 * kStride + 1, o2 = 2 * kStride + 2, o3 = kStride + 3, o4 = 3,
-                o5 = -kStride + 3, o6 = -2 * kStride + 2, o7 = -3 * kStride + 1, o8 = -3 * kStride,
-                o9 = -3 * kStride - 1, o10 = -2 * kStride - 2, o11 = -kStride - 3, o12 = -3,
-                o13 = kStride - 3, o14 = 2 * kStride - 2, o15 = 3 * kStride - 1;
+  const u32 K = (u32)(255 - tq) * 0x00010001u;
+  const int bLo = a + 4 + 3, bHi = a + 4 + cw - 3;  // interior bytes [bLo, bHi)
+  const int g0 = bLo >> 2, g1 = (bHi - 1) >> 2;
 
-  // pass 1: opposing-pair rejection (every arc of 9 contains one pixel of each opposing pair)
-  for (int i = tid; i < iw * ih; i += 256) {
-    const int yy = i / iw, xx = i - yy * iw;
-    const u8* p = sImg + (yy + 3) * kStride + xx + 3;
-    const int v = p[0];
-    const int lo = v - tq, hi = v + tq;
-    bool pass = true;
-#define ORBX_PAIR(a, b)                                              \
-  {                                                                  \
-    const int pa = p[a], pb = p[b];                                  \
-    if (pa >= lo && pa <= hi && pb >= lo && pb <= hi) pass = false;  \
+  // pass 1: opposing-pair rejection on 4 pixels at a time
+  for (int ry = 3 + (tid >> 4); ry < ch - 3; ry += 16) {
+    const u32* r0 = sImgW + ry * kSW;
+    for (int g = g0 + (tid & 15); g <= g1; g += 16) {
+      // bit 0 of byte j set <=> pixel 4g + j is in the interior and not yet rejected
+      u32 alive = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) alive |= (u32)((4 * g + j) >= bLo && (4 * g + j) < bHi) << (8 * j);
+      const u32 v = r0[g];
+#define ORBX_PAIR(DY, DX)                                                                    \
+  if (alive) {                                                                                \
+    const u32 pa = word_at<DX>(r0 + (DY) * kSW, g), pb = word_at<-(DX)>(r0 - (DY) * kSW, g); \
+    alive &= bytes_gt(__vabsdiffu4(v, pa), K) | bytes_gt(__vabsdiffu4(v, pb), K);            \
   }
-    ORBX_PAIR(o0, o8) ORBX_PAIR(o4, o12)
-    if (pass) { ORBX_PAIR(o2, o10) ORBX_PAIR(o6, o14) }
-    if (pass) { ORBX_PAIR(o1, o9) ORBX_PAIR(o3, o11) ORBX_PAIR(o5, o13) ORBX_PAIR(o7, o15) }
+      ORBX_PAIR(3, 0) ORBX_PAIR(0, 3) ORBX_PAIR(2, 2) ORBX_PAIR(-2, 2)
+      ORBX_PAIR(3, 1) ORBX_PAIR(1, 3) ORBX_PAIR(-1, 3) ORBX_PAIR(-3, 1)
 #undef ORBX_PAIR
-    if (pass) sList[atomicAdd(&sN, 1)] = (unsigned short)((yy << 8) | xx);
+      while (alive) {
+        const int j = (__ffs((int)alive) - 1) >> 3;
+        alive &= ~(1u << (8 * j));
+        sList[atomicAdd(&sN, 1)] = (unsigned short)((ry << 8) | (4 * g + j));
+      }
+    }
   }
   __syncthreads();
   const int n = sN;
+  // ring offsets in staged bytes, cv::FAST order
+  constexpr int o0 = 3 * kSB, o1 = 3 * kSB + 1, o2 = 2 * kSB + 2, o3 = kSB + 3, o4 = 3, o5 = -kSB + 3,
+                o6 = -2 * kSB + 2, o7 = -3 * kSB + 1, o8 = -3 * kSB, o9 = -3 * kSB - 1, o10 = -2 * kSB - 2,
+                o11 = -kSB - 3, o12 = -3, o13 = kSB - 3, o14 = 2 * kSB - 2, o15 = 3 * kSB - 1;
   // pass 2: exact segment-test value of the surviving pixels
   for (int i = tid; i < n; i += 256) {
-    const int e = sList[i], yy = e >> 8, xx = e & 255;
-    const u8* p = sImg + (yy + 3) * kStride + xx + 3;
+    const int e = sList[i], ry = e >> 8, b = e & 255;
+    const u8* p = sImg + ry * kSB + b;
     const int v = p[0];
     int d[16];
     d[0] = v - p[o0]; d[1] = v - p[o1]; d[2] = v - p[o2]; d[3] = v - p[o3];
@@ -100,19 +133,17 @@ __global__ void __launch_bounds__(256) k_fast(const __grid_constant__ Params P) 
     d[8] = v - p[o8]; d[9] = v - p[o9]; d[10] = v - p[o10]; d[11] = v - p[o11];
     d[12] = v - p[o12]; d[13] = v - p[o13]; d[14] = v - p[o14]; d[15] = v - p[o15];
     const int m = arc_value(d);
-    if (m > tq) sM[(yy + 1) * kStride + xx + 1] = (u8)m;
+    if (m > tq) sM[ry * kSB + b] = (u8)m;
   }
   __syncthreads();
-  // pass 3: strict 3x3 maxima with m >= 2; compact them to the front of sList (as index | m is
-  // re-read from sM).  Reuse of sList is safe: every thread finishes reading entry i before any
-  // thread can overwrite it only if writes go to a second region, so peaks are written behind n.
-  unsigned short* sPk = sList + n;  // n + peaks <= 2 * (iw*ih) / ... bounded below
+  // pass 3: strict 3x3 maxima with m >= 2, written behind the pass-1 list
+  unsigned short* sPk = sList + n;
   for (int i = tid; i < n; i += 256) {
-    const int e = sList[i], yy = e >> 8, xx = e & 255;
-    const u8* q = sM + (yy + 1) * kStride + xx + 1;
+    const int e = sList[i], ry = e >> 8, b = e & 255;
+    const u8* q = sM + ry * kSB + b;
     const int m = q[0];
-    if (m >= 2 && m > q[-1] && m > q[1] && m > q[-kStride - 1] && m > q[-kStride] && m > q[-kStride + 1] &&
-        m > q[kStride - 1] && m > q[kStride] && m > q[kStride + 1]) {
+    if (m >= 2 && m > q[-1] && m > q[1] && m > q[-kSB - 1] && m > q[-kSB] && m > q[-kSB + 1] &&
+        m > q[kSB - 1] && m > q[kSB] && m > q[kSB + 1]) {
       sPk[atomicAdd(&sPeaks, 1)] = (unsigned short)e;
       if (m > tIni) atomicAdd(&sIni, 1);
       if (m > tMin) atomicAdd(&sMin, 1);
@@ -134,13 +165,13 @@ __global__ void __launch_bounds__(256) k_fast(const __grid_constant__ Params P) 
   const u8* rootTab = P.rootTab + L.rootTabOff;
   const int np = sPeaks;
   for (int i = tid; i < np; i += 256) {
-    const int e = sPk[i], yy = e >> 8, xx = e & 255;
-    const int m = sM[(yy + 1) * kStride + xx + 1];
+    const int e = sPk[i], ry = e >> 8, b = e & 255;
+    const int m = sM[ry * kSB + b];
     if (m > th) {
       const int k = atomicAdd(&sCursor, 1);
-      // ROI-relative (xx + 3, yy + 3), shifted by the cell origin: coordinates relative to (16,16)
-      const int x = xx + 3 + c.sx, y = yy + 3 + c.sy;
-      const u32 order = ((u32)c.index << 14) | ((u32)(yy + 3) << 7) | (u32)(xx + 3);
+      const int rx = b - 4 - a;  // ROI-relative column; the reference shifts by the cell origin (:1134-1135)
+      const int x = rx + c.sx, y = ry + c.sy;  // relative to (16,16)
+      const u32 order = ((u32)c.index << 14) | ((u32)ry << 7) | (u32)rx;
       P.candKey[off + k] = ((u64)(u32)(m - 1) << 32) | (u64)(~order);
       P.candXY[off + k] = (u32)x | ((u32)y << 16);
       P.candNode[off + k] = (u32)(L.nIni - 1 - __ldg(rootTab + x));  // root i lives at node nIni-1-i

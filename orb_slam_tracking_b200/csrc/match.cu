@@ -24,35 +24,28 @@ __device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const 
          __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
 }
 
-struct Best {
-  int d, pos, idx, d2;  // best distance, its visiting position, its keypoint index; second best
-};
-__device__ __forceinline__ Best merge(const Best a, const Best b) {
-  const bool aFirst = (a.d < b.d) || (a.d == b.d && a.pos < b.pos);
-  Best r;
-  r.d = aFirst ? a.d : b.d;
-  r.pos = aFirst ? a.pos : b.pos;
-  r.idx = aFirst ? a.idx : b.idx;
-  r.d2 = min(min(a.d2, b.d2), aFirst ? b.d : a.d);
-  return r;
-}
-
+// One warp per pair.  Per query: the <= 64 grid columns of the search window are spread over the
+// lanes (their CSR ranges are loaded in parallel and prefix-summed), then the flattened candidate
+// list is walked 32 at a time; each lane keeps its two smallest distances and the visiting position
+// of its smallest, and two redux.sync min-reductions give the reference's best / second best.
 __global__ void __launch_bounds__(32) k_match(const __grid_constant__ Params P, const MatchArgs A, int pairStep,
                                               float nnratio, int checkOri, int window) {
   const int pair = blockIdx.x, lane = threadIdx.x;
   const int s1 = pair * pairStep, s2 = s1 + 1;
   const int n1 = A.n[s1], n2 = A.n[s2];
-  const orbx_keypoint* k1 = A.keysUn + (size_t)s1 * A.stride;
-  const orbx_keypoint* k2 = A.keysUn + (size_t)s2 * A.stride;
-  const u8* d1 = A.desc + (size_t)s1 * A.stride * 32;
-  const u8* d2 = A.desc + (size_t)s2 * A.stride * 32;
-  const u32* gOff = A.gridOff + (size_t)s2 * (kGridCells + 1);
-  const u32* gIdx = A.gridIdx + (size_t)s2 * A.stride;
+  const orbx_keypoint* __restrict__ k1 = A.keysUn + (size_t)s1 * A.stride;
+  const orbx_keypoint* __restrict__ k2 = A.keysUn + (size_t)s2 * A.stride;
+  const u8* __restrict__ d1 = A.desc + (size_t)s1 * A.stride * 32;
+  const u8* __restrict__ d2 = A.desc + (size_t)s2 * A.stride * 32;
+  const u32* __restrict__ gOff = A.gridOff + (size_t)s2 * (kGridCells + 1);
+  const u32* __restrict__ gIdx = A.gridIdx + (size_t)s2 * A.stride;
   int* m12 = A.matches12 + (size_t)pair * A.stride;
   int* matchedDist = A.scratch + (size_t)pair * 3 * A.stride;
   int* m21 = matchedDist + A.stride;
   int* binOf = m21 + A.stride;
   __shared__ int sHist[HISTO_LENGTH];
+  __shared__ int sStart[kGridCols + 1];  // exclusive prefix of the column range sizes
+  __shared__ int sBeg[kGridCols];        // CSR start of each column range
 
   for (int i = lane; i < n1; i += 32) { m12[i] = -1; binOf[i] = -1; }
   for (int i = lane; i < n2; i += 32) { matchedDist[i] = INT_MAX; m21[i] = -1; }
@@ -63,6 +56,7 @@ __global__ void __launch_bounds__(32) k_match(const __grid_constant__ Params P, 
   const float minX = (float)P.bounds[0], minY = (float)P.bounds[2];
   const float factor = (float)HISTO_LENGTH / 360.0f;
   int nmatches = 0, badDist = 0, badRatio = 0;
+  constexpr u32 kNone = 0xffffffffu;
 
   for (int i1 = 0; i1 < n1; ++i1) {
     const orbx_keypoint kp1 = k1[i1];
@@ -77,46 +71,75 @@ __global__ void __launch_bounds__(32) k_match(const __grid_constant__ Params P, 
     if (minCY >= kGridRows) continue;
     const int maxCY = min(kGridRows - 1, (int)ceilf(__fmul_rn(y - minY + r, P.gridHInv)));
     if (maxCY < 0) continue;
+    const int nCols = maxCX - minCX + 1;
+    if (nCols <= 0) continue;
+    // column ranges, two per lane
+    int b0 = 0, c0 = 0, b1 = 0, c1 = 0;
+    if (lane < nCols) {
+      const int cell = (minCX + lane) * kGridRows;
+      b0 = (int)gOff[cell + minCY];
+      c0 = (int)gOff[cell + maxCY + 1] - b0;
+    }
+    if (lane + 32 < nCols) {
+      const int cell = (minCX + lane + 32) * kGridRows;
+      b1 = (int)gOff[cell + minCY];
+      c1 = (int)gOff[cell + maxCY + 1] - b1;
+    }
+    int p0 = c0, p1 = c1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t0 = __shfl_up_sync(0xffffffffu, p0, o), t1 = __shfl_up_sync(0xffffffffu, p1, o);
+      if (lane >= o) { p0 += t0; p1 += t1; }
+    }
+    const int tot0 = __shfl_sync(0xffffffffu, p0, 31);
+    const int total = tot0 + __shfl_sync(0xffffffffu, p1, 31);
+    if (total == 0) continue;  // vIndices2.empty(), :46
+    sStart[lane] = p0 - c0; sBeg[lane] = b0;
+    sStart[lane + 32] = tot0 + p1 - c1; sBeg[lane + 32] = b1;
+    if (lane == 0) sStart[kGridCols] = total;
+    __syncwarp();
     const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i1 * 32));
     const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i1 * 32) + 1);
-    Best b;
-    b.d = INT_MAX; b.pos = INT_MAX; b.idx = -1; b.d2 = INT_MAX;
-    int posBase = 0, found = 0;
-    for (int ix = minCX; ix <= maxCX; ++ix) {
-      const int beg = (int)gOff[ix * kGridRows + minCY], end = (int)gOff[ix * kGridRows + maxCY + 1];
-      for (int t = beg + lane; t < end; t += 32) {
-        const int i2 = (int)gIdx[t];
-        const orbx_keypoint kp2 = k2[i2];
-        if (kp2.octave != kp1.octave) continue;  // level filter [level1, level1]
-        const float dx = kp2.x - x, dy = kp2.y - y;
-        if (!(fabsf(dx) < r && fabsf(dy) < r)) continue;
-        found = 1;
-        const int dist = hamming256(a0, a1, d2 + (size_t)i2 * 32);
-        if (matchedDist[i2] <= dist) continue;  // :67
-        const int pos = posBase + (t - beg);
-        if (dist < b.d) { b.d2 = b.d; b.d = dist; b.pos = pos; b.idx = i2; }
-        else if (dist < b.d2) b.d2 = dist;
-      }
-      posBase += end - beg;
-    }
-    if (!__any_sync(0xffffffffu, found)) continue;  // vIndices2.empty(), :46
+    u32 key = kNone;          // (best distance << 20) | visiting position
+    int bidx = -1, bd2 = INT_MAX, found = 0;
+    for (int t = lane; t < total; t += 32) {
+      // column of flattened position t: last c with sStart[c] <= t
+      int lo = 0, hi = kGridCols;
 #pragma unroll
-    for (int o = 16; o; o >>= 1) {
-      Best q;
-      q.d = __shfl_xor_sync(0xffffffffu, b.d, o);
-      q.pos = __shfl_xor_sync(0xffffffffu, b.pos, o);
-      q.idx = __shfl_xor_sync(0xffffffffu, b.idx, o);
-      q.d2 = __shfl_xor_sync(0xffffffffu, b.d2, o);
-      b = merge(b, q);
+      for (int s = 0; s < 6; ++s) {
+        const int mid = (lo + hi) >> 1;
+        if (sStart[mid] <= t) lo = mid; else hi = mid;
+      }
+      const int i2 = (int)gIdx[sBeg[lo] + (t - sStart[lo])];
+      const orbx_keypoint kp2 = k2[i2];
+      if (kp2.octave != kp1.octave) continue;  // level filter [level1, level1]
+      const float dx = kp2.x - x, dy = kp2.y - y;
+      if (!(fabsf(dx) < r && fabsf(dy) < r)) continue;
+      found = 1;
+      const int dist = hamming256(a0, a1, d2 + (size_t)i2 * 32);
+      if (matchedDist[i2] <= dist) continue;  // :67
+      const u32 k = ((u32)dist << 20) | (u32)t;
+      if (k < key) {  // lane-local positions ascend, so "dist < best" and "k < key" agree
+        if (key != kNone) bd2 = (int)(key >> 20);
+        key = k; bidx = i2;
+      } else if (dist < bd2) bd2 = dist;
     }
-    if (b.d > TH_LOW) { ++badDist; continue; }                             // :82
-    if ((float)b.d > __fmul_rn(nnratio, (float)b.d2)) { ++badRatio; continue; }  // :87
-    const int prev = m21[b.idx];
+    __syncwarp();
+    if (!__any_sync(0xffffffffu, found)) continue;  // no candidate passed the window test
+    const u32 best = __reduce_min_sync(0xffffffffu, key);
+    const int winner = __ffs((int)__ballot_sync(0xffffffffu, key == best)) - 1;
+    const int bestDist = best == kNone ? INT_MAX : (int)(best >> 20);
+    const int mine2 = (lane == winner) ? bd2 : (key == kNone ? INT_MAX : (int)(key >> 20));
+    const int bestDist2 = (int)__reduce_min_sync(0xffffffffu, (u32)mine2);
+    const int bestIdx = __shfl_sync(0xffffffffu, bidx, winner);
+    if (bestDist > TH_LOW) { ++badDist; continue; }                                  // :82
+    if ((float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) { ++badRatio; continue; }  // :87
+    const int prev = m21[bestIdx];
     if (prev >= 0) --nmatches;  // :95-98
     ++nmatches;
     int bin = -1;
     if (checkOri) {
-      float rot = kp1.angle - k2[b.idx].angle;
+      float rot = kp1.angle - k2[bestIdx].angle;
       if (rot < 0.0f) rot = rot + 360.0f;
       bin = (int)roundf(__fmul_rn(rot, factor));
       if (bin == HISTO_LENGTH) bin = 0;
@@ -124,9 +147,9 @@ __global__ void __launch_bounds__(32) k_match(const __grid_constant__ Params P, 
     __syncwarp();
     if (lane == 0) {
       if (prev >= 0) m12[prev] = -1;
-      m12[i1] = b.idx;
-      m21[b.idx] = i1;
-      matchedDist[b.idx] = b.d;
+      m12[i1] = bestIdx;
+      m21[bestIdx] = i1;
+      matchedDist[bestIdx] = bestDist;
       if (bin >= 0) { binOf[i1] = bin; sHist[bin] += 1; }
     }
     __syncwarp();
