@@ -1,0 +1,50 @@
+#!/usr/bin/env python
+"""Writes profiles/<tag>_summary.md from gpurun_out/<tag>_launches.csv (launch list),
+gpurun_out/<tag>_full.ncu-rep (one --set full capture) and gpurun_out/<tag>_bench.json."""
+import csv, io, json, subprocess, sys, shutil
+from collections import OrderedDict
+from pathlib import Path
+tag = sys.argv[1]
+note = sys.argv[2] if len(sys.argv) > 2 else ""
+G, P = Path("gpurun_out"), Path("profiles")
+rows = [r for r in csv.reader(open(G / f"{tag}_launches.csv")) if len(r) > 10 and r[0].isdigit()]
+agg = OrderedDict()
+for r in rows:
+    k = r[4].split("(")[0]
+    a = agg.setdefault(k, [0, 0.0]); a[0] += 1; a[1] += float(r[-1]) / 1e3
+tot = sum(a[1] for a in agg.values())
+out = [f"# {tag}: {note}", "", "## launch list (ncu --metrics gpu__time_duration.sum --clock-control none; `bench.py --steps 2 --warmup 1 --no-cpu`)", "",
+       "| kernel | launches | total us | mean us | share |", "|---|---|---|---|---|"]
+for k, a in sorted(agg.items(), key=lambda x: -x[1][1]):
+    out.append(f"| {k} | {a[0]} | {a[1]:.1f} | {a[1]/a[0]:.1f} | {100*a[1]/tot:.1f}% |")
+b = G / f"{tag}_bench.json"
+if b.exists():
+    line = json.loads([l for l in b.read_text().splitlines() if l.startswith("{")][-1])
+    st = line["stage_ms_per_step"]; s = sum(st.values())
+    out += ["", "## bench.py line of the same build (no profiler): value %.0f frames/s resident, e2e %.0f frames/s, cpu_baseline %s" %
+            (line["value"], line["e2e"]["value"], json.dumps(line.get("cpu_baseline"))), "",
+            "CUDA-event stage times (ms per step of %d frames): " % line["config"]["frames_per_step_per_gpu"] +
+            ", ".join(f"{k} {v:.3f} ({100*v/s:.0f}%)" for k, v in st.items()), "",
+            "roofline: " + json.dumps(line["roofline"]), "", "clocks: " + json.dumps(line["clocks"])]
+    shutil.copy(b, P / f"{tag}_bench.json")
+rep = G / f"{tag}_full.ncu-rep"
+if rep.exists():
+    raw = subprocess.run(["ncu", "-i", str(rep), "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rr = list(csv.reader(io.StringIO(raw))); hdr = rr[0]
+    cols = [("Kernel Name", "kernel"), ("gpu__time_duration.sum", "ms"), ("dram__bytes_read.sum", "dram rd MB"), ("dram__bytes_write.sum", "dram wr MB"),
+            ("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "dram %"), ("sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm %"),
+            ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue %"), ("l1tex__throughput.avg.pct_of_peak_sustained_active", "l1 %"),
+            ("sm__warps_active.avg.pct_of_peak_sustained_active", "warps act %"), ("launch__registers_per_thread", "regs"),
+            ("smsp__inst_executed.sum", "warp instr"), ("launch__grid_size", "grid"), ("l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "smem conflicts")]
+    idx = [(hdr.index(c), n) for c, n in cols if c in hdr]
+    out += ["", "## ncu --set full (one launch each)", "", "| " + " | ".join(n for _, n in idx) + " |", "|" + "---|" * len(idx)]
+    seen = {}
+    for r in rr[2:]:
+        k = r[idx[0][0]].split("(")[0]
+        seen[k] = seen.get(k, 0) + 1
+        if seen[k] > (7 if k == "k_resize" else 1): continue
+        vals = [k] + [("%.4g" % float(r[i])) if r[i].replace(".", "").replace("e+", "").replace("-", "").isdigit() else r[i] for i, _ in idx[1:]]
+        out.append("| " + " | ".join(vals) + " |")
+shutil.copy(G / f"{tag}_launches.csv", P / f"{tag}_launches.csv")
+(P / f"{tag}_summary.md").write_text("\n".join(out) + "\n")
+print("\n".join(out))
