@@ -1,0 +1,16 @@
+#!/bin/bash
+# TEST INFRASTRUCTURE.  Compiles the reference's own hot-path sources, from where they lie under
+# /root/reference, against oracle/refshim (a stand-in for the OpenCV/Eigen headers that are not
+# installed here; its primitives come from oracle/cv_prims.hpp) into oracle/_ref/libref_orb.so.
+# Flags as the reference's Release build (-O3 -DNDEBUG would drop its asserts; keep them on).
+set -e
+HERE="$(cd "$(dirname "$0")" && pwd)"
+REF="${REFERENCE_ROOT:-/root/reference}"
+[ -f "$REF/Features/ORBextractor.cpp" ] || { echo "build_ref.sh: no reference checkout at $REF"; exit 0; }
+mkdir -p "$HERE/_ref"
+g++ -O2 -std=c++17 -fPIC -shared -ffp-contract=off -w \
+  -I"$HERE/refshim" -I"$REF" -I"$REF/Thirdparty/DBoW2/include" -I"$REF/Thirdparty/DBoW2/include/DBoW2" \
+  "$REF/Features/ORBextractor.cpp" "$REF/Features/ORBmatcher.cpp" "$REF/SlamTypes/Frame.cpp" \
+  "$REF/Thirdparty/DBoW2/src/FORB.cpp" "$REF/Thirdparty/DBoW2/src/BowVector.cpp" "$REF/Thirdparty/DBoW2/src/FeatureVector.cpp" \
+  "$HERE/ref_driver.cpp" -o "$HERE/_ref/libref_orb.so"
+echo "built $HERE/_ref/libref_orb.so"

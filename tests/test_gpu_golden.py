@@ -1,0 +1,64 @@
+"""The CUDA path (through the C ABI) against the golden vectors in tests/golden/: outputs of the
+reference's own sources on the reference's bundled images (tools/gen_golden.py).  Bit-exact:
+level tables, keypoint records, descriptors, lapping split, undistorted keys, image bounds, the
+64x48 grid, vnMatches12 and the returned count -- host-buffer calls and the device-resident stream."""
+import numpy as np
+import pytest
+
+from golden_util import CASES, Case, same_records
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_cuda_matches_reference_outputs(name):
+    from orb_slam_tracking_b200 import frontend as fe
+    c = Case(name)
+    H, W = c.imgs[0].shape
+    E = fe.ORBextractor(c.nf, 1.2, 8, c.ini, c.mn, W, H, max_batch=c.n_frames)
+    z = c.z
+    assert np.array_equal(E.GetScaleFactors(), z["tab_scale"]) and np.array_equal(E.GetInverseScaleFactors(), z["tab_inv_scale"])
+    assert np.array_equal(E.GetScaleSigmaSquares(), z["tab_sigma2"])
+    assert np.array_equal(E.GetInverseScaleSigmaSquares(), z["tab_inv_sigma2"])
+    assert np.array_equal(E.GetNumFeaturesPerLevel(), z["tab_per_level"])
+    assert np.array_equal(E.set_camera(c.K4, c.D4), c.bounds)
+    F = []
+    for i, im in enumerate(c.imgs):
+        gk, gd, gku, goff, gidx = c.frame(i)
+        k, d, mono = E(im)
+        assert same_records(k, gk), "keypoints of frame %d" % i
+        assert np.array_equal(d, gd), "descriptors of frame %d" % i
+        assert mono == len(gk)
+        if i == 0:
+            for l in (1, 7):
+                assert int(E.pyramid_level(l, padded=True).astype(np.int64).sum()) == int(z["level%d_crc" % l])
+        f = fe.Frame(E, kps=k, desc=d)
+        assert same_records(f.mvKeysUn, gku)
+        assert np.array_equal(f.grid_offsets, goff) and np.array_equal(f.grid_indices, gidx)
+        if c.lapping != (0, 0):
+            k2, d2, mono2 = E(im, vLappingArea=c.lapping)
+            assert same_records(k2, z["lap_kps%d" % i]) and np.array_equal(d2, z["lap_desc%d" % i])
+            assert mono2 == int(z["lap_mono%d" % i])
+        F.append(f)
+    M = fe.ORBmatcher(0.9, True)
+    for a in c.pairs():
+        for w in c.windows:
+            n, m12, _ = M.SearchForInitialization(F[a], F[a + 1], w)
+            gn, gm = c.matches(a, w)
+            assert n == gn and np.array_equal(m12, gm), "pair %d window %d" % (a, w)
+    # the device-resident stream: images in, match lists out
+    for w in c.windows:
+        S = fe.Stream(E, 0.9, True, w)
+        nfr = c.n_frames - c.n_frames % 2
+        S.upload(np.stack(c.imgs[:nfr]))
+        S.run(nfr)
+        out = S.download(nfr)
+        for i in range(nfr):
+            gk, gd, gku, _, _ = c.frame(i)
+            n = int(out["n"][i])
+            assert same_records(out["kps"][i, :n], gk) and np.array_equal(out["desc"][i, :n], gd)
+            assert same_records(out["kps_un"][i, :n], gku)
+        for a in c.pairs():
+            gn, gm = c.matches(a, w)
+            assert int(out["nmatches"][a // 2]) == gn and np.array_equal(out["matches12"][a // 2, :len(gm)], gm)
+    E.close()
