@@ -8,7 +8,7 @@ HERE="$(cd "$(dirname "$0")" && pwd)"
 REF="${REFERENCE_ROOT:-/root/reference}"
 [ -f "$REF/Features/ORBextractor.cpp" ] || { echo "build_ref.sh: no reference checkout at $REF"; exit 0; }
 mkdir -p "$HERE/_ref"
-g++ -O2 -std=c++17 -fPIC -shared -ffp-contract=off -w \
+g++ -O3 -std=c++17 -fPIC -shared -pthread -ffp-contract=off -w \
   -I"$HERE/refshim" -I"$REF" -I"$REF/Thirdparty/DBoW2/include" -I"$REF/Thirdparty/DBoW2/include/DBoW2" \
   "$REF/Features/ORBextractor.cpp" "$REF/Features/ORBmatcher.cpp" "$REF/SlamTypes/Frame.cpp" \
   "$REF/Thirdparty/DBoW2/src/FORB.cpp" "$REF/Thirdparty/DBoW2/src/BowVector.cpp" "$REF/Thirdparty/DBoW2/src/FeatureVector.cpp" \

@@ -6,6 +6,8 @@
 // the restatement in oracle/orb_oracle.cpp; never by the product path.
 #include <cstdio>
 #include <cstring>
+#include <atomic>
+#include <thread>
 #include <vector>
 
 #include "Features/ORBextractor.hpp"
@@ -119,5 +121,48 @@ int ref_search_for_initialization(void* f1, void* f2, float nnratio, int checkOr
 double ref_forb_distance(const unsigned char* a, const unsigned char* b) {
   cv::Mat A(1, 32, CV_8U, (void*)a), B(1, 32, CV_8U, (void*)b);
   return DBoW2::FORB::distance(A, B);
+}
+
+// CPU baseline: the reference's own Frame construction + SearchForInitialization over a stream of
+// frames, pairs (2k, 2k+1) sharded over `threads` host threads (one ORBextractor per thread: the
+// reference's extractor is not re-entrant).  Returns the total number of matches; *totalKp = keypoints.
+long long ref_run_stream(const unsigned char* imgs, int n, int w, int h, int nfeatures, float scaleFactor, int nlevels, int iniTh,
+                         int minTh, const float K4[4], const float D4[4], int window, float nnratio, int threads,
+                         long long* totalKp) {
+  Quiet q;
+  cv::Mat K = cv::Mat::zeros(3, 3, CV_32F);
+  K.at<float>(0, 0) = K4[0]; K.at<float>(1, 1) = K4[1]; K.at<float>(0, 2) = K4[2]; K.at<float>(1, 2) = K4[3]; K.at<float>(2, 2) = 1.f;
+  cv::Mat D(4, 1, CV_32F);
+  for (int i = 0; i < 4; ++i) D.at<float>(i) = D4[i];
+  {  // the once-per-process statics (Frame.cpp:44-55), before any thread starts
+    ORBextractor e(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+    cv::Mat im(h, w, CV_8UC1, (void*)imgs, (size_t)w);
+    Frame::mbInitialComputations = true;
+    Frame f(im, 0.0, &e, nullptr, K, D);
+  }
+  const int nPairs = n / 2;
+  std::atomic<int> next(0);
+  std::atomic<long long> matches(0), kps(0);
+  auto work = [&]() {
+    ORBextractor e(nfeatures, scaleFactor, nlevels, iniTh, minTh);
+    ORBmatcher m(nnratio, true);
+    for (;;) {
+      const int p = next.fetch_add(1);
+      if (p >= nPairs) break;
+      cv::Mat a(h, w, CV_8UC1, (void*)(imgs + (size_t)(2 * p) * w * h), (size_t)w);
+      cv::Mat b(h, w, CV_8UC1, (void*)(imgs + (size_t)(2 * p + 1) * w * h), (size_t)w);
+      cv::Mat Ka = K, Da = D;
+      Frame f1(a, 0.0, &e, nullptr, Ka, Da), f2(b, 1.0, &e, nullptr, Ka, Da);
+      std::vector<int> v;
+      matches += m.SearchForInitialization(f1, f2, v, window);
+      kps += f1.N + f2.N;
+    }
+  };
+  std::vector<std::thread> T;
+  for (int t = 1; t < threads; ++t) T.emplace_back(work);
+  work();
+  for (auto& t : T) t.join();
+  if (totalKp) *totalKp = kps.load();
+  return matches.load();
 }
 }

@@ -53,6 +53,8 @@ def lib():
         L.ref_search_for_initialization.argtypes = [vp, vp, cf, ci, ci, vp]
         L.ref_forb_distance.restype = C.c_double
         L.ref_forb_distance.argtypes = [vp, vp]
+        L.ref_run_stream.restype = C.c_longlong
+        L.ref_run_stream.argtypes = [vp, ci, ci, ci, ci, cf, ci, ci, ci, vp, vp, ci, cf, ci, vp]
         _LIB = L
     return _LIB
 
@@ -145,3 +147,15 @@ def search_for_initialization(F1, F2, nnratio=0.9, check_ori=True, window=100):
 def forb_distance(a, b):
     a, b = np.ascontiguousarray(a, np.uint8), np.ascontiguousarray(b, np.uint8)
     return lib().ref_forb_distance(_p(a), _p(b))
+
+
+def run_stream(imgs, nfeatures, scale_factor, nlevels, ini_th, min_th, K4, D4, window=100, nnratio=0.9, threads=1):
+    """CPU baseline on the reference's own code: Frame x 2 + SearchForInitialization per pair. -> (matches, keypoints)"""
+    imgs = np.ascontiguousarray(imgs, np.uint8)
+    n, H, W = imgs.shape
+    K4 = np.ascontiguousarray(K4, np.float32)
+    D4 = np.ascontiguousarray(D4, np.float32)
+    tot = C.c_longlong(0)
+    m = lib().ref_run_stream(_p(imgs), n, W, H, nfeatures, scale_factor, nlevels, ini_th, min_th, _p(K4), _p(D4), window, nnratio,
+                             threads, C.byref(tot))
+    return int(m), int(tot.value)
