@@ -11,6 +11,7 @@
 //   out*         per slot: packed cv::KeyPoint records + descriptors in the reference's order
 //   frame store  per slot: undistorted keys, 64x48 CSR grid
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -62,11 +63,18 @@ struct BlurTile {
   short x0, y0;
 };
 
+// TMA descriptors (cuTensorMapEncodeTiled, built once in orbx_create): level l of the pyramid slab as a
+// u8 tensor {x: w, y: h, slot: maxBatch} with strides {pitch, slabBytes}; box = fastBoxW x fastBoxH x 1.
+struct TmaMaps {
+  CUtensorMap lvl[kMaxLevels];
+};
+
 struct Params {
   int W, H, nlevels, nfeatures, iniTh, minTh, maxBatch;
   int kpStride;        // keypoint slots per frame = max(nfeatures, sum of quotas)
   int trigMode;
   int nCells, nBlurTiles;
+  int fastBoxW, fastBoxH;  // TMA box of k_fast: bytes per staged row (multiple of 16, >= widest cell ROI + 8), rows
   u32 slabBytes, candTotal, nodeTotal;
   int umax[16];
   LevelInfo lv[kMaxLevels];
@@ -129,7 +137,7 @@ __device__ __forceinline__ int reflect101(int i, int len) {
 // launchers (one per .cu file); all enqueue on `st` and return the number of kernel launches
 int launch_pyramid(const Params& P, const int* const* dTabs, int nSlots, cudaStream_t st);
 int launch_blur(const Params& P, int nSlots, cudaStream_t st);
-int launch_fast(const Params& P, int nSlots, cudaStream_t st);
+int launch_fast(const Params& P, const TmaMaps& M, int nSlots, cudaStream_t st);
 int launch_quadtree(const Params& P, int nSlots, cudaStream_t st);
 int launch_describe(const Params& P, int nSlots, int lap0, int lap1, cudaStream_t st);
 int launch_glue(const Params& P, int nSlots, cudaStream_t st);

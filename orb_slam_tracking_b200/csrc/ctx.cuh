@@ -29,6 +29,7 @@ int compute_tables(int nfeatures, float scaleFactor, int nlevels, HostTables& t)
 struct orbx_ctx {
   orbx::Params P;
   orbx::HostTables T;
+  orbx::TmaMaps tma;               // per-level tensor maps over P.pyr (k_fast tile staging)
   int device;
   cudaStream_t stream;
   std::vector<void*> allocs;       // every cudaMalloc, freed in orbx_destroy

@@ -2,7 +2,7 @@
 //   IC_Angle               Features/ORBextractor.cpp:103-159   (on the UNBLURRED level, :1184-1188)
 //   computeOrbDescriptor   Features/ORBextractor.cpp:169-228   (on the blurred level, :1613)
 //   output packing         Features/ORBextractor.cpp:1558-1652 (level-major, pt *= scale, lapping split)
-// One warp per keypoint.  Moments are integer sums (order-independent, so a shuffle reduction is
+// Moments are integer sums (order-independent, so a shuffle reduction is
 // exact); cv::fastAtan2 is replayed in float32 with explicit round-to-nearest multiplies and adds
 // (this file is also compiled with -fmad=false); the rotated sample coordinates use the same
 // separate float multiply/add roundings and round-half-even as cvRound on x86-64.
@@ -37,71 +37,126 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 
 constexpr int kWarpsPerCta = 8;
+constexpr int kKpPerCta = 32;           // keypoint slots per CTA: 4 per warp, one per thread of warp 0 for the trigonometry
+constexpr int kPatchRows = 37, kPatchWords = 10;  // blurred patch [-18, 18]^2 staged as 37 rows of 10 aligned words
 
+// Three phases per CTA of 32 keypoint slots:
+//   1. IC_Angle, one warp per keypoint: the 31 x 31 disc is read as aligned 32-bit words (9 per row, lanes
+//      over (row, word)), each byte weighted by its column offset u and masked by |u| <= umax[|v|].
+//   2. cos/sin of the 32 angles, one THREAD per keypoint (the double-precision libm calls are the longest
+//      instruction stream of the kernel; a warp per keypoint would run them 32x redundantly).
+//   3. steered BRIEF, one warp per keypoint: the 37 x 37 blurred patch is staged into shared memory with
+//      coalesced word loads, then lane = descriptor byte gathers its 16 samples from shared memory.
 __global__ void __launch_bounds__(kWarpsPerCta * 32) k_describe(const __grid_constant__ Params P) {
   __shared__ char4 sPat[256];  // [i * 32 + byte]: conflict-free for lane = byte
+  __shared__ u32 sPatch[kWarpsPerCta][kPatchRows * kPatchWords];
+  __shared__ float sAngle[kKpPerCta], sCos[kKpPerCta], sSin[kKpPerCta];
+  __shared__ u32 sXY[kKpPerCta];
+  __shared__ signed char sLevel[kKpPerCta];  // -1: empty slot
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   {
     const int b = tid & 31, i = tid >> 5;  // 256 threads: pair (b, i) -> pattern row 8b + i
     const signed char* p = c_pattern + 4 * (8 * b + i);
     sPat[i * 32 + b] = make_char4(p[0], p[1], p[2], p[3]);
   }
-  __syncthreads();
   const int slot = blockIdx.y;
-  const int g = blockIdx.x * kWarpsPerCta + warp;  // keypoint slot in [0, nfeatures)
-  if (g >= P.kpStride) return;
-  int l = 0;
-  while (l + 1 < P.nlevels && g >= P.lv[l + 1].kpOff) ++l;
-  const LevelInfo& L = P.lv[l];
-  const int p = g - L.kpOff;
-  if (p >= P.lvlCount[(size_t)slot * kMaxLevels + l]) return;
-  const size_t ko = (size_t)slot * P.kpStride + g;
-  const u32 xy = P.lvlXY[ko];
-  const int x = (int)(xy & 0xffff), y = (int)(xy >> 16);
-
-  // ---- IC_Angle: lane = patch row v in [-15, 15] ----
-  const u8* __restrict__ img = level_ptr((const u8*)P.pyr, P, slot, l);
-  int m10 = 0, m01 = 0;
-  if (lane < 31) {
-    const int v = lane - kHalfPatch;
-    const int d = P.umax[v < 0 ? -v : v];
-    const u8* row = img + (size_t)(y + v) * L.pitch + x;
-    int si = 0, su = 0;
-    for (int u = -d; u <= d; ++u) {
-      const int I = __ldg(row + u);
-      si += I;
-      su += u * I;
+  const int gBase = blockIdx.x * kKpPerCta;
+  if (tid < kKpPerCta) {
+    const int g = gBase + tid;
+    int l = -1;
+    if (g < P.kpStride) {
+      l = 0;
+      while (l + 1 < P.nlevels && g >= P.lv[l + 1].kpOff) ++l;
+      if (g - P.lv[l].kpOff >= P.lvlCount[(size_t)slot * kMaxLevels + l]) l = -1;
     }
-    m10 = su;
-    m01 = v * si;
+    sLevel[tid] = (signed char)l;
+    if (l >= 0) sXY[tid] = P.lvlXY[(size_t)slot * P.kpStride + g];
   }
-#pragma unroll
-  for (int o = 16; o; o >>= 1) {
-    m10 += __shfl_xor_sync(0xffffffffu, m10, o);
-    m01 += __shfl_xor_sync(0xffffffffu, m01, o);
-  }
-  const float angle = fast_atan2_deg((float)m01, (float)m10);
+  __syncthreads();
 
-  // ---- steered BRIEF: lane = descriptor byte ----
-  const float a = __fmul_rn(angle, (float)(3.1415926535897932384626433832795 / 180.f));
-  float co, si;
-  if (P.trigMode == 0) { co = (float)cos((double)a); si = (float)sin((double)a); }
-  else { co = cosf(a); si = sinf(a); }
-  const u8* __restrict__ bl = level_ptr((const u8*)P.blur, P, slot, l) + (size_t)y * L.pitch + x;
-  u32 val = 0;
+  // ---- phase 1: IC_Angle ----
+  for (int k = warp; k < kKpPerCta; k += kWarpsPerCta) {
+    const int l = sLevel[k];
+    if (l < 0) continue;
+    const LevelInfo& L = P.lv[l];
+    const u32 xy = sXY[k];
+    const int x = (int)(xy & 0xffff), y = (int)(xy >> 16);
+    const int xa = (x - kHalfPatch) & ~3;  // 9 aligned words cover [x-15, x+15]
+    const u8* __restrict__ img = level_ptr((const u8*)P.pyr, P, slot, l) + (size_t)(y - kHalfPatch) * L.pitch + xa;
+    int m10 = 0, m01 = 0;
+#pragma unroll 3
+    for (int i = lane; i < 31 * 9; i += 32) {
+      const int r = i / 9, w = i - 9 * r;
+      const int v = r - kHalfPatch;
+      const int d = P.umax[v < 0 ? -v : v];
+      const u32 word = __ldg(reinterpret_cast<const u32*>(img + (size_t)r * L.pitch) + w);
+      const int u0 = xa + 4 * w - x;
+      int si = 0, su = 0;
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const char4 q = sPat[i * 32 + lane];
-    const float x0 = (float)q.x, y0 = (float)q.y, x1 = (float)q.z, y1 = (float)q.w;
-    const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, si), __fmul_rn(y0, co)));
-    const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, co), __fmul_rn(y0, si)));
-    const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, si), __fmul_rn(y1, co)));
-    const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, co), __fmul_rn(y1, si)));
-    const int t0 = __ldg(bl + r0 * L.pitch + c0), t1 = __ldg(bl + r1 * L.pitch + c1);
-    val |= (u32)(t0 < t1) << i;
+      for (int j = 0; j < 4; ++j) {
+        const int u = u0 + j;
+        const int I = (u >= -d && u <= d) ? (int)((word >> (8 * j)) & 255u) : 0;
+        si += I;
+        su += u * I;
+      }
+      m10 += su;
+      m01 += v * si;
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+      m10 += __shfl_xor_sync(0xffffffffu, m10, o);
+      m01 += __shfl_xor_sync(0xffffffffu, m01, o);
+    }
+    if (lane == 0) sAngle[k] = fast_atan2_deg((float)m01, (float)m10);
   }
-  P.lvlDesc[ko * 32 + lane] = (u8)val;
-  if (lane == 0) P.lvlAngle[ko] = angle;
+  __syncthreads();
+
+  // ---- phase 2: one thread per keypoint ----
+  if (tid < kKpPerCta && sLevel[tid] >= 0) {
+    const float angle = sAngle[tid];
+    const float a = __fmul_rn(angle, (float)(3.1415926535897932384626433832795 / 180.f));
+    float co, si;
+    if (P.trigMode == 0) { co = (float)cos((double)a); si = (float)sin((double)a); }
+    else { co = cosf(a); si = sinf(a); }
+    sCos[tid] = co;
+    sSin[tid] = si;
+    P.lvlAngle[(size_t)slot * P.kpStride + gBase + tid] = angle;
+  }
+  __syncthreads();
+
+  // ---- phase 3: steered BRIEF, lane = descriptor byte ----
+  u32* const patch = sPatch[warp];
+  for (int k = warp; k < kKpPerCta; k += kWarpsPerCta) {
+    const int l = sLevel[k];
+    if (l < 0) continue;
+    const LevelInfo& L = P.lv[l];
+    const u32 xy = sXY[k];
+    const int x = (int)(xy & 0xffff), y = (int)(xy >> 16);
+    const int xa = (x - 18) & ~3;  // 10 aligned words cover [x-18, x+18]
+    const u8* __restrict__ bl = level_ptr((const u8*)P.blur, P, slot, l) + (size_t)(y - 18) * L.pitch + xa;
+    __syncwarp();
+#pragma unroll 4
+    for (int i = lane; i < kPatchRows * kPatchWords; i += 32) {
+      const int r = i / kPatchWords, w = i - kPatchWords * r;
+      patch[i] = __ldg(reinterpret_cast<const u32*>(bl + (size_t)r * L.pitch) + w);
+    }
+    __syncwarp();
+    const u8* centre = reinterpret_cast<const u8*>(patch) + 18 * (4 * kPatchWords) + (x - xa);
+    const float co = sCos[k], si = sSin[k];
+    u32 val = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const char4 q = sPat[i * 32 + lane];
+      const float x0 = (float)q.x, y0 = (float)q.y, x1 = (float)q.z, y1 = (float)q.w;
+      const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, si), __fmul_rn(y0, co)));
+      const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, co), __fmul_rn(y0, si)));
+      const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, si), __fmul_rn(y1, co)));
+      const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, co), __fmul_rn(y1, si)));
+      const int t0 = centre[r0 * (4 * kPatchWords) + c0], t1 = centre[r1 * (4 * kPatchWords) + c1];
+      val |= (u32)(t0 < t1) << i;
+    }
+    P.lvlDesc[((size_t)slot * P.kpStride + gBase + k) * 32 + lane] = (u8)val;
+  }
 }
 
 // ---- output packing: one CTA per slot ----
@@ -168,7 +223,7 @@ __global__ void __launch_bounds__(PK) k_pack(const __grid_constant__ Params P, i
 }
 
 int launch_describe(const Params& P, int nSlots, int lap0, int lap1, cudaStream_t st) {
-  dim3 grid((P.kpStride + kWarpsPerCta - 1) / kWarpsPerCta, nSlots);
+  dim3 grid((P.kpStride + kKpPerCta - 1) / kKpPerCta, nSlots);
   k_describe<<<grid, kWarpsPerCta * 32, 0, st>>>(P);
   k_pack<<<nSlots, PK, 0, st>>>(P, lap0, lap1);
   return 2;

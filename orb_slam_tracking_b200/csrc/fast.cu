@@ -2,7 +2,11 @@
 // (ORBextractor::ComputeKeyPointsOctTree cell loop, Features/ORBextractor.cpp:1051-1141, calling
 // cv::FAST(roi, kps, th, true) at :1109 and :1119; arithmetic in SURVEY.md appendix A3).
 //
-// One CTA per (cell, slot); the cells of ALL levels are in one table, so one launch covers a batch.
+// One CTA of 128 threads per (cell, slot); the cells of ALL levels are in one table, so one launch
+// covers a batch.  The cell ROI (from the 16-byte aligned column left of it) is staged into shared memory by ONE TMA
+// tile copy (cp.async.bulk.tensor.3d over a per-level {x, y, slot} tensor map, completion on an
+// mbarrier); out-of-image box bytes are zero-filled by the hardware and never tested.
+//
 // The segment-test value m(p) = max over the 16 arcs of 9 of min(v - ring) / min(ring - v) does not
 // depend on the threshold: p is a corner at t iff m > t and its NMS score is m - 1.  A corner
 // survives NMS at t iff m >= 2 and m is a strict 3x3 maximum of the m-map restricted to the
@@ -12,8 +16,10 @@
 //
 // Pass 1 is the hot loop: the opposing-pair rejection (every arc of 9 contains one pixel of each
 // opposing ring pair, so a pair with both |d| <= t proves m <= t) runs on FOUR pixels per thread
-// with byte-SWAR arithmetic on 32-bit words of the staged ROI; only the few surviving pixels get
-// the exact arc value.
+// with byte-SWAR arithmetic on 32-bit words of the staged ROI: VABSDIFF4 per ring word, then a
+// carry-free "byte > t" in bit 7 of each byte.  The four pairs that live on rows {-3, 0, +3} go
+// first; only words with a pixel still alive touch the other four rows, and only the few
+// surviving pixels get the exact arc value (pass 2).
 //
 // Survivors are appended to the level's candidate list with an atomic cursor; each carries its
 // position in the reference's emission order (cell row-major, then y, then x) inside its key, which
@@ -22,9 +28,7 @@
 
 namespace orbx {
 
-constexpr int kSB = 96;          // staged row stride in bytes; byte b of a row <-> level column xb - 4 + b
-constexpr int kSW = kSB / 4;     // ... in words
-constexpr int kMaxRows = 76;     // hCell + 6 < 76
+constexpr int kFastThreads = 128;
 
 __device__ __forceinline__ int arc_value(const int (&d)[16]) {
   // max over 16 arcs of min over 9 consecutive ring differences, and the same for -d
@@ -45,105 +49,152 @@ __device__ __forceinline__ int arc_value(const int (&d)[16]) {
   return max(A, B);
 }
 
-// bit 0 of each byte of the result = (that byte of a) > t, with K = (255 - t) * 0x00010001
-__device__ __forceinline__ u32 bytes_gt(u32 a, u32 K) {
-  const u32 e = (a & 0x00ff00ffu) + K, o = ((a >> 8) & 0x00ff00ffu) + K;
-  return ((e >> 8) & 0x00010001u) | (o & 0x01000100u);
+// bit 7 of each byte of the result = (that byte of a) > t  OR  (that byte of b) > t.
+//   t < 128:  K = (127 - t) * 0x01010101; (x & 0x7f) + K carries into bit 7 iff (x & 0x7f) > t, and x >= 128 > t.
+//   t >= 128: K = (255 - t) * 0x01010101; x > t iff bit 7 of x is set and (x & 0x7f) + K carries.
+template <bool HI>
+__device__ __forceinline__ u32 any_gt(u32 a, u32 b, u32 K) {
+  const u32 sa = (a & 0x7f7f7f7fu) + K, sb = (b & 0x7f7f7f7fu) + K;
+  if (HI) return (sa & a) | (sb & b);
+  return sa | sb | a | b;
 }
-// 4 bytes starting at byte offset 4g + dx (dx in [-3, 3]) of a staged row
+// 4 bytes starting at byte offset 4g + DX (DX in [-3, 3]) given the words g-1, g, g+1 of a staged row
 template <int DX>
-__device__ __forceinline__ u32 word_at(const u32* row, int g) {
-  if (DX == 0) return row[g];
-  if (DX > 0) return __funnelshift_r(row[g], row[g + 1], 8 * DX);
-  return __funnelshift_r(row[g - 1], row[g], 32 + 8 * DX);
+__device__ __forceinline__ u32 word_at(u32 wl, u32 wc, u32 wr) {
+  if (DX == 0) return wc;
+  if (DX > 0) return __funnelshift_r(wc, wr, 8 * DX);
+  return __funnelshift_r(wl, wc, 32 + 8 * DX);
 }
 
-__global__ void __launch_bounds__(256) k_fast(const __grid_constant__ Params P) {
-  __shared__ u32 sImgW[kMaxRows * kSW];
-  __shared__ u32 sMW[kMaxRows * kSW];            // m-map, same geometry, zero outside the interior
-  __shared__ unsigned short sList[kMaxRows * kSB];
+__device__ __forceinline__ u32 smem_addr(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+
+template <bool HI>
+__device__ __forceinline__ u32 pass1_word(const u32* __restrict__ r0, int SW, int g, u32 alive, u32 K) {
+  // rows -3, 0, +3 first: pairs (dy,dx) = (3,0), (3,1), (0,3), (-3,1) and their opposites
+  const u32* rm = r0 - 3 * SW;
+  const u32* rp = r0 + 3 * SW;
+  const u32 cl = r0[g - 1], cc = r0[g], cr = r0[g + 1];
+  const u32 ml = rm[g - 1], mc = rm[g], mr = rm[g + 1];
+  const u32 pl = rp[g - 1], pc = rp[g], pr = rp[g + 1];
+  alive &= any_gt<HI>(__vabsdiffu4(cc, pc), __vabsdiffu4(cc, mc), K);
+  alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<3>(cl, cc, cr)), __vabsdiffu4(cc, word_at<-3>(cl, cc, cr)), K);
+  alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<1>(pl, pc, pr)), __vabsdiffu4(cc, word_at<-1>(ml, mc, mr)), K);
+  alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<1>(ml, mc, mr)), __vabsdiffu4(cc, word_at<-1>(pl, pc, pr)), K);
+  if (alive) {
+    // rows +-2: (2,2)/(-2,-2) and (-2,2)/(2,-2); rows +-1: (1,3)/(-1,-3) and (-1,3)/(1,-3)
+    const u32* a2 = r0 + 2 * SW;
+    const u32* b2 = r0 - 2 * SW;
+    const u32 al = a2[g - 1], ac = a2[g], ar = a2[g + 1];
+    const u32 bl = b2[g - 1], bc = b2[g], br = b2[g + 1];
+    alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<2>(al, ac, ar)), __vabsdiffu4(cc, word_at<-2>(bl, bc, br)), K);
+    alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<2>(bl, bc, br)), __vabsdiffu4(cc, word_at<-2>(al, ac, ar)), K);
+    const u32* a1 = r0 + SW;
+    const u32* b1 = r0 - SW;
+    const u32 dl = a1[g - 1], dc = a1[g], dr = a1[g + 1];
+    const u32 el = b1[g - 1], ec = b1[g], er = b1[g + 1];
+    alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<3>(dl, dc, dr)), __vabsdiffu4(cc, word_at<-3>(el, ec, er)), K);
+    alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<3>(el, ec, er)), __vabsdiffu4(cc, word_at<-3>(dl, dc, dr)), K);
+  }
+  return alive;
+}
+
+__global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ Params P, const __grid_constant__ TmaMaps M) {
+  extern __shared__ __align__(128) u8 smem[];
+  __shared__ __align__(8) u64 sBar;
   __shared__ int sN, sPeaks, sIni, sMin, sBase, sCursor;
-  u8* const sImg = reinterpret_cast<u8*>(sImgW);
-  u8* const sM = reinterpret_cast<u8*>(sMW);
 
   const CellDesc c = P.cells[blockIdx.x];
   const int slot = blockIdx.y;
   const LevelInfo& L = P.lv[c.level];
   const int cw = c.x1 - c.x0, ch = c.y1 - c.y0;
-  if (cw < 7 || ch < 7) return;  // cv::FAST returns nothing for such ROIs
   const int tid = threadIdx.x;
-  const int a = c.x0 & 3, xb = c.x0 - a;       // aligned base column; ROI column rx <-> byte rx + 4 + a
-  const int nW = (a + cw + 3) >> 2;             // words per row holding ROI bytes (staged words 1 .. nW)
-  const u8* __restrict__ img = level_ptr((const u8*)P.pyr, P, slot, c.level) + (size_t)c.y0 * L.pitch + xb;
+  const int SB = P.fastBoxW, SW = SB >> 2;  // staged row stride in bytes / words
+  // TMA tile origins must be 16-byte aligned in the innermost dimension: the tile starts at the aligned column
+  // xs <= x0 - 1, so byte b of a staged row <-> level column xs + b and ROI column rx <-> byte rx + off, off in [1, 16]
+  const int xs = (c.x0 - 1) & ~15, off = c.x0 - xs;
+  const int tileBytes = SB * P.fastBoxH;
+  u8* const sImg = smem;
+  u8* const sM = smem + tileBytes;            // m-map, same geometry, zero outside the interior
+  unsigned short* const sList = reinterpret_cast<unsigned short*>(smem + 2 * tileBytes);
+  const u32* const sImgW = reinterpret_cast<const u32*>(sImg);
 
-  for (int i = tid; i < ch * kSW; i += 256) {
-    const int r = i / kSW, k = i - r * kSW;
-    u32 v = 0;
-    if (k >= 1 && k <= nW) v = __ldg(reinterpret_cast<const u32*>(img + (size_t)r * L.pitch) + (k - 1));
-    sImgW[i] = v;
-    sMW[i] = 0;
+  if (tid == 0) {
+    sN = 0; sPeaks = 0; sIni = 0; sMin = 0; sCursor = 0;
+    const u32 bar = smem_addr(&sBar);
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(tileBytes) : "memory");
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+        ::"r"(smem_addr(sImg)), "l"(reinterpret_cast<u64>(&M.lvl[c.level])), "r"(xs), "r"((int)c.y0), "r"(slot), "r"(bar)
+        : "memory");
   }
-  if (tid == 0) { sN = 0; sPeaks = 0; sIni = 0; sMin = 0; sCursor = 0; }
-  __syncthreads();
+  {  // zero the m-map while the tile is in flight
+    uint4* z = reinterpret_cast<uint4*>(sM);
+    for (int i = tid; i < (tileBytes >> 4); i += kFastThreads) z[i] = make_uint4(0, 0, 0, 0);
+  }
+  __syncthreads();  // sBar initialised (and the zeroes visible) before anyone polls
+  {
+    const u32 bar = smem_addr(&sBar);
+    u32 done = 0;
+    while (!done) {
+      asm volatile(
+          "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n selp.u32 %0, 1, 0, p;\n}\n"
+          : "=r"(done) : "r"(bar) : "memory");
+    }
+  }
 
   const int tIni = min(max(P.iniTh, 0), 255), tMin = min(max(P.minTh, 0), 255);
   const int tq = min(tIni, tMin);
-  const u32 K = (u32)(255 - tq) * 0x00010001u;
-  const int bLo = a + 4 + 3, bHi = a + 4 + cw - 3;  // interior bytes [bLo, bHi)
+  const int bLo = off + 3, bHi = off + cw - 3;  // interior bytes [bLo, bHi)
   const int g0 = bLo >> 2, g1 = (bHi - 1) >> 2;
+  const int nW = g1 - g0 + 1, nR = ch - 6;
 
-  // pass 1: opposing-pair rejection on 4 pixels at a time
-  for (int ry = 3 + (tid >> 4); ry < ch - 3; ry += 16) {
-    const u32* r0 = sImgW + ry * kSW;
-    for (int g = g0 + (tid & 15); g <= g1; g += 16) {
-      // bit 0 of byte j set <=> pixel 4g + j is in the interior and not yet rejected
-      u32 alive = 0;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) alive |= (u32)((4 * g + j) >= bLo && (4 * g + j) < bHi) << (8 * j);
-      const u32 v = r0[g];
-#define ORBX_PAIR(DY, DX)                                                                    \
-  if (alive) {                                                                                \
-    const u32 pa = word_at<DX>(r0 + (DY) * kSW, g), pb = word_at<-(DX)>(r0 - (DY) * kSW, g); \
-    alive &= bytes_gt(__vabsdiffu4(v, pa), K) | bytes_gt(__vabsdiffu4(v, pb), K);            \
-  }
-      ORBX_PAIR(3, 0) ORBX_PAIR(0, 3) ORBX_PAIR(2, 2) ORBX_PAIR(-2, 2)
-      ORBX_PAIR(3, 1) ORBX_PAIR(1, 3) ORBX_PAIR(-1, 3) ORBX_PAIR(-3, 1)
-#undef ORBX_PAIR
+  // pass 1: opposing-pair rejection on 4 pixels at a time, items = (interior row, word) flattened over the CTA
+  {
+    const u32 K = (u32)(tq < 128 ? 127 - tq : 255 - tq) * 0x01010101u;
+    const int stepR = kFastThreads / nW, stepG = kFastThreads - stepR * nW;
+    int ry = tid / nW, g = tid - ry * nW;
+    for (; ry < nR; ry += stepR, g += stepG) {
+      if (g >= nW) { g -= nW; ++ry; if (ry >= nR) break; }
+      const int gw = g0 + g;
+      u32 alive = 0x80808080u;
+      if (4 * gw < bLo) alive &= 0xffffffffu << (8 * (bLo - 4 * gw));
+      if (4 * gw + 4 > bHi) alive &= 0xffffffffu >> (8 * (4 * gw + 4 - bHi));
+      const u32* r0 = sImgW + (ry + 3) * SW;
+      alive = tq < 128 ? pass1_word<false>(r0, SW, gw, alive, K) : pass1_word<true>(r0, SW, gw, alive, K);
       while (alive) {
         const int j = (__ffs((int)alive) - 1) >> 3;
-        alive &= ~(1u << (8 * j));
-        sList[atomicAdd(&sN, 1)] = (unsigned short)((ry << 8) | (4 * g + j));
+        alive &= alive - 1;
+        sList[atomicAdd(&sN, 1)] = (unsigned short)(((ry + 3) << 8) | (4 * gw + j));
       }
     }
   }
   __syncthreads();
   const int n = sN;
-  // ring offsets in staged bytes, cv::FAST order
-  constexpr int o0 = 3 * kSB, o1 = 3 * kSB + 1, o2 = 2 * kSB + 2, o3 = kSB + 3, o4 = 3, o5 = -kSB + 3,
-                o6 = -2 * kSB + 2, o7 = -3 * kSB + 1, o8 = -3 * kSB, o9 = -3 * kSB - 1, o10 = -2 * kSB - 2,
-                o11 = -kSB - 3, o12 = -3, o13 = kSB - 3, o14 = 2 * kSB - 2, o15 = 3 * kSB - 1;
-  // pass 2: exact segment-test value of the surviving pixels
-  for (int i = tid; i < n; i += 256) {
+  // pass 2: exact segment-test value of the surviving pixels (ring offsets in cv::FAST order)
+  for (int i = tid; i < n; i += kFastThreads) {
     const int e = sList[i], ry = e >> 8, b = e & 255;
-    const u8* p = sImg + ry * kSB + b;
+    const u8* p = sImg + ry * SB + b;
     const int v = p[0];
     int d[16];
-    d[0] = v - p[o0]; d[1] = v - p[o1]; d[2] = v - p[o2]; d[3] = v - p[o3];
-    d[4] = v - p[o4]; d[5] = v - p[o5]; d[6] = v - p[o6]; d[7] = v - p[o7];
-    d[8] = v - p[o8]; d[9] = v - p[o9]; d[10] = v - p[o10]; d[11] = v - p[o11];
-    d[12] = v - p[o12]; d[13] = v - p[o13]; d[14] = v - p[o14]; d[15] = v - p[o15];
+    d[0] = v - p[3 * SB]; d[1] = v - p[3 * SB + 1]; d[2] = v - p[2 * SB + 2]; d[3] = v - p[SB + 3];
+    d[4] = v - p[3]; d[5] = v - p[-SB + 3]; d[6] = v - p[-2 * SB + 2]; d[7] = v - p[-3 * SB + 1];
+    d[8] = v - p[-3 * SB]; d[9] = v - p[-3 * SB - 1]; d[10] = v - p[-2 * SB - 2]; d[11] = v - p[-SB - 3];
+    d[12] = v - p[-3]; d[13] = v - p[SB - 3]; d[14] = v - p[2 * SB - 2]; d[15] = v - p[3 * SB - 1];
     const int m = arc_value(d);
-    if (m > tq) sM[ry * kSB + b] = (u8)m;
+    if (m > tq) sM[ry * SB + b] = (u8)m;
   }
   __syncthreads();
   // pass 3: strict 3x3 maxima with m >= 2, written behind the pass-1 list
   unsigned short* sPk = sList + n;
-  for (int i = tid; i < n; i += 256) {
+  for (int i = tid; i < n; i += kFastThreads) {
     const int e = sList[i], ry = e >> 8, b = e & 255;
-    const u8* q = sM + ry * kSB + b;
+    const u8* q = sM + ry * SB + b;
     const int m = q[0];
-    if (m >= 2 && m > q[-1] && m > q[1] && m > q[-kSB - 1] && m > q[-kSB] && m > q[-kSB + 1] &&
-        m > q[kSB - 1] && m > q[kSB] && m > q[kSB + 1]) {
+    if (m >= 2 && m > q[-1] && m > q[1] && m > q[-SB - 1] && m > q[-SB] && m > q[-SB + 1] &&
+        m > q[SB - 1] && m > q[SB] && m > q[SB + 1]) {
       sPk[atomicAdd(&sPeaks, 1)] = (unsigned short)e;
       if (m > tIni) atomicAdd(&sIni, 1);
       if (m > tMin) atomicAdd(&sMin, 1);
@@ -161,27 +212,29 @@ __global__ void __launch_bounds__(256) k_fast(const __grid_constant__ Params P) 
     if (tid == 0) atomicMin(P.status + slot, ORBX_ERR_CAPACITY);
     return;
   }
-  const size_t off = (size_t)slot * P.candTotal + L.candOff + base;
+  const size_t co = (size_t)slot * P.candTotal + L.candOff + base;
   const u8* rootTab = P.rootTab + L.rootTabOff;
   const int np = sPeaks;
-  for (int i = tid; i < np; i += 256) {
+  for (int i = tid; i < np; i += kFastThreads) {
     const int e = sPk[i], ry = e >> 8, b = e & 255;
-    const int m = sM[ry * kSB + b];
+    const int m = sM[ry * SB + b];
     if (m > th) {
       const int k = atomicAdd(&sCursor, 1);
-      const int rx = b - 4 - a;  // ROI-relative column; the reference shifts by the cell origin (:1134-1135)
+      const int rx = b - off;  // ROI-relative column; the reference shifts by the cell origin (:1134-1135)
       const int x = rx + c.sx, y = ry + c.sy;  // relative to (16,16)
       const u32 order = ((u32)c.index << 14) | ((u32)ry << 7) | (u32)rx;
-      P.candKey[off + k] = ((u64)(u32)(m - 1) << 32) | (u64)(~order);
-      P.candXY[off + k] = (u32)x | ((u32)y << 16);
-      P.candNode[off + k] = (u32)(L.nIni - 1 - __ldg(rootTab + x));  // root i lives at node nIni-1-i
+      P.candKey[co + k] = ((u64)(u32)(m - 1) << 32) | (u64)(~order);
+      P.candXY[co + k] = (u32)x | ((u32)y << 16);
+      P.candNode[co + k] = (u32)(L.nIni - 1 - __ldg(rootTab + x));  // root i lives at node nIni-1-i
     }
   }
 }
 
-int launch_fast(const Params& P, int nSlots, cudaStream_t st) {
+int launch_fast(const Params& P, const TmaMaps& M, int nSlots, cudaStream_t st) {
   dim3 grid(P.nCells, nSlots);
-  k_fast<<<grid, 256, 0, st>>>(P);
+  // image tile + m-map + pass-1 list and peak list (<= 1.25 entries per staged byte, u16 each)
+  const size_t smem = (size_t)P.fastBoxW * P.fastBoxH * 9 / 2 + 64;
+  k_fast<<<grid, kFastThreads, smem, st>>>(P, M);
   return 1;
 }
 

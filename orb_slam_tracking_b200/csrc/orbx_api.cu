@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstring>
 #include <new>
+#include <string>
 
 #include "ctx.cuh"
 
@@ -29,6 +30,31 @@ static int dupload(orbx_ctx* c, T** p, const std::vector<T>& v) {
   int rc = dalloc(c, p, v.size());
   if (rc) return rc;
   if (!v.empty()) CU(c, cudaMemcpy(*p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return ORBX_OK;
+}
+
+// One u8 tensor map per pyramid level, {x, y, slot}; the driver entry point is taken from the loaded
+// libcuda through the runtime (liborbx.so links cudart statically and does not link libcuda).
+static int build_tensor_maps(orbx_ctx* c) {
+  typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  CU(c, cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q));
+  if (!fn || q != cudaDriverEntryPointSuccess) { c->err = "cuTensorMapEncodeTiled not available"; return ORBX_ERR_CUDA; }
+  const Params& P = c->P;
+  for (int l = 0; l < P.nlevels; ++l) {
+    const LevelInfo& L = P.lv[l];
+    cuuint64_t dims[3] = {(cuuint64_t)L.w, (cuuint64_t)L.h, (cuuint64_t)P.maxBatch};
+    cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)P.slabBytes};
+    cuuint32_t box[3] = {(cuuint32_t)P.fastBoxW, (cuuint32_t)P.fastBoxH, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = ((EncodeFn)fn)(&c->tma.lvl[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, P.pyr + L.imgOff, dims, strides, box, estr,
+                                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { c->err = "cuTensorMapEncodeTiled failed: " + std::to_string((int)r); return ORBX_ERR_CUDA; }
+  }
   return ORBX_OK;
 }
 
@@ -78,8 +104,8 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
     if ((rc = dupload(c, &c->dResizeTabs[l], tab))) return rc;
     c->hTabPtrs[l] = c->dResizeTabs[l];
   }
-  if ((rc = dalloc(c, &P.pyr, B * P.slabBytes))) return rc;
-  if ((rc = dalloc(c, &P.blur, B * P.slabBytes))) return rc;
+  if ((rc = dalloc(c, &P.pyr, B * P.slabBytes + 256))) return rc;   // + slack: aligned word reads may run a few bytes past a row
+  if ((rc = dalloc(c, &P.blur, B * P.slabBytes + 256))) return rc;
   if ((rc = dalloc(c, &P.candKey, B * P.candTotal))) return rc;
   if ((rc = dalloc(c, &P.candXY, B * P.candTotal))) return rc;
   if ((rc = dalloc(c, &P.candNode, B * P.candTotal))) return rc;
@@ -122,6 +148,7 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   if ((rc = dalloc(c, &c->hfNMatches, 1))) return rc;
   if ((rc = dalloc(c, &c->hfCounters, 3))) return rc;
   if ((rc = dalloc(c, &c->hfScratch, 3 * (size_t)c->hfCap))) return rc;
+  if ((rc = build_tensor_maps(c))) return rc;
   CU(c, cudaMemset(P.status, 0, B * sizeof(int)));
   CU(c, cudaMemset(P.outN, 0, B * sizeof(int)));
   CU(c, cudaMemset(P.pyr, 0, B * P.slabBytes));

@@ -24,7 +24,7 @@ int enqueue_extract(orbx_ctx* c, int n, int lap0, int lap1) {
   mark(c, 0);
   c->launches += launch_pyramid(P, c->hTabPtrs, n, st);
   mark(c, 1);
-  c->launches += launch_fast(P, n, st);
+  c->launches += launch_fast(P, c->tma, n, st);
   mark(c, 2);
   c->launches += launch_quadtree(P, n, st);
   mark(c, 3);

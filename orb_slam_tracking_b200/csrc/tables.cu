@@ -2,6 +2,7 @@
 // sizes, resize coefficients, per-level quotas, umax, cell geometry, quadtree roots) is made here
 // once, on the host, with the reference's own expressions, and uploaded as integers.  The GPU
 // never re-derives them.
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 
@@ -92,6 +93,7 @@ int build_geometry(Params& P, const HostTables& T, std::vector<CellDesc>& cells,
   u32 imgOff = 0, candOff = 0, nodeOff = 0;
   int kpOff = 0;
   cells.clear(); tiles.clear(); rootTab.clear(); rootEdges.clear();
+  int maxCw = 7, maxCh = 7;
   for (int l = 0; l < P.nlevels; ++l) {
     LevelInfo& L = P.lv[l];
     L.w = cv_round_f((float)P.W * T.invScale[l]);  // :1662-1663
@@ -136,6 +138,8 @@ int build_geometry(Params& P, const HostTables& T, std::vector<CellDesc>& cells,
         const int iw = c.x1 - c.x0 - 6, ih = c.y1 - c.y0 - 6;
         if (iw < 1 || ih < 1) continue;  // cv::FAST yields nothing for ROIs under 7 px
         cells.push_back(c);
+        maxCw = std::max(maxCw, c.x1 - c.x0);
+        maxCh = std::max(maxCh, c.y1 - c.y0);
         cap += ((iw + 1) / 2) * ((ih + 1) / 2);  // NMS survivors are never 8-adjacent
       }
     }
@@ -171,6 +175,8 @@ int build_geometry(Params& P, const HostTables& T, std::vector<CellDesc>& cells,
   P.candTotal = candOff;
   P.nodeTotal = nodeOff;
   P.nCells = (int)cells.size();
+  P.fastBoxW = (int)align_up((u32)maxCw + 20, 16);  // up to 16 bytes of alignment apron + ROI + the word right of the last interior word
+  P.fastBoxH = maxCh;
   P.nBlurTiles = (int)tiles.size();
   return ORBX_OK;
 }
