@@ -1,6 +1,8 @@
 // ORBmatcher::SearchForInitialization (Features/ORBmatcher.cpp:11-150), ComputeThreeMaxima (:152-183),
 // Frame::GetFeaturesInArea (SlamTypes/Frame.cpp:163-206) and DBoW2::FORB::distance
-// (Thirdparty/DBoW2/src/FORB.cpp:77-100) for a batch of frame pairs: one warp per pair.
+// (Thirdparty/DBoW2/src/FORB.cpp:77-100) for a batch of frame pairs.  k_match_cta (below) is the product path;
+// k_match (one warp per pair, everything in one ordered walk) remains for keypoint capacities whose tables do
+// not fit shared memory.
 //
 // The reference loop over i1 is order-dependent (`vMatchedDistance[i2] <= dist` skips a candidate
 // that an EARLIER query already matched at least as well, :67), so queries are walked in
@@ -10,6 +12,8 @@
 // breaks distance ties by that position (strict `<` keeps the first minimum, :70-76).
 // Descriptors are read as two 128-bit loads and compared with 8 x __popc.
 #include <limits.h>
+
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -184,10 +188,346 @@ __global__ void __launch_bounds__(32) k_match(const __grid_constant__ Params P, 
   }
 }
 
+// ---- the batched matcher: one CTA of 8 warps per pair, distances in parallel, resolve in order -------------
+// The order dependence of the reference loop sits only in `vMatchedDistance[i2] <= dist` (:67) and in
+// the bookkeeping after a match; which candidates a query sees, in which order, and their distances do
+// not depend on earlier queries.  So per chunk of queries all warps fill (distance, i2) entries in the
+// reference's visiting order into shared memory, and then ONE warp replays the reference's loop over
+// those entries (ascending i1), with vMatchedDistance / vnMatches21 in shared memory.
+//   S1  level-0 CSR of F2's grid (SearchForInitialization only asks for level [0, 0], :38-44): same cell
+//       order and in-cell order as mGrid, other octaves dropped, candidate x / y / index staged beside it;
+//   S2  the level-0 queries of F1 in ascending i1;
+//   S3  per chunk: segment sizes (upper bound = level-0 keys in the window's cell rectangle), prefix sums,
+//       warp-per-query fill (window test, 256-bit Hamming), then the ordered replay by warp 0.
+constexpr int MT = 256, MW = MT / 32;
+constexpr int kChunkQ = 128;            // queries per chunk (segment table size)
+constexpr u32 kInvalid = 0xffffffffu;   // entry of a cell-rectangle key outside the window
+
+struct MatchSmem {  // byte offsets into dynamic shared memory
+  int off0, cx, cy, ci, md, m21, q, bin, ent, total;
+  int entCap;
+};
+__host__ __device__ inline MatchSmem match_smem_layout(int stride) {
+  MatchSmem L;
+  int o = 0;
+  auto take = [&](int bytes) { const int r = o; o += (bytes + 15) & ~15; return r; };
+  L.off0 = take((kGridCells + 1) * 2);
+  L.cx = take(stride * 4);
+  L.cy = take(stride * 4);
+  L.ci = take(stride * 2);
+  L.md = take(stride * 2);
+  L.m21 = take(stride * 2);
+  L.q = take(stride * 2);
+  L.bin = take(stride);
+  L.entCap = stride > 8192 ? stride : 8192;
+  L.ent = take(L.entCap * 4);
+  L.total = o;
+  return L;
+}
+
+// the window's cell rectangle, Frame::GetFeaturesInArea :167-185; false = empty result
+__device__ __forceinline__ bool cell_rect(const Params& P, float x, float y, float r, int& minCX, int& maxCX, int& minCY,
+                                          int& maxCY) {
+  const float minX = (float)P.bounds[0], minY = (float)P.bounds[2];
+  minCX = max(0, (int)floorf(__fmul_rn(x - minX - r, P.gridWInv)));
+  if (minCX >= kGridCols) return false;
+  maxCX = min(kGridCols - 1, (int)ceilf(__fmul_rn(x - minX + r, P.gridWInv)));
+  if (maxCX < 0) return false;
+  minCY = max(0, (int)floorf(__fmul_rn(y - minY - r, P.gridHInv)));
+  if (minCY >= kGridRows) return false;
+  maxCY = min(kGridRows - 1, (int)ceilf(__fmul_rn(y - minY + r, P.gridHInv)));
+  if (maxCY < 0) return false;
+  return maxCX >= minCX && maxCY >= minCY;
+}
+
+__global__ void __launch_bounds__(MT) k_match_cta(const __grid_constant__ Params P, const MatchArgs A, int pairStep, float nnratio,
+                                                  int checkOri, int window) {
+  extern __shared__ __align__(16) u8 dsm[];
+  __shared__ int sPart[MT];
+  __shared__ int sSeg[kChunkQ + 1];
+  __shared__ int sColStart[MW][kGridCols + 1];
+  __shared__ int sColBeg[MW][kGridCols];
+  __shared__ int sHist[HISTO_LENGTH];
+  __shared__ int sNQ, sChunkN;
+  const MatchSmem LY = match_smem_layout(A.stride);
+  unsigned short* const sOff0 = reinterpret_cast<unsigned short*>(dsm + LY.off0);
+  float* const sCx = reinterpret_cast<float*>(dsm + LY.cx);
+  float* const sCy = reinterpret_cast<float*>(dsm + LY.cy);
+  unsigned short* const sCi = reinterpret_cast<unsigned short*>(dsm + LY.ci);
+  unsigned short* const sMD = reinterpret_cast<unsigned short*>(dsm + LY.md);
+  unsigned short* const sM21 = reinterpret_cast<unsigned short*>(dsm + LY.m21);
+  unsigned short* const sQ = reinterpret_cast<unsigned short*>(dsm + LY.q);
+  u8* const sBin = dsm + LY.bin;
+  u32* const sEnt = reinterpret_cast<u32*>(dsm + LY.ent);
+
+  const int pair = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int s1 = pair * pairStep, s2 = s1 + 1;
+  const int n1 = A.n[s1], n2 = A.n[s2];
+  const orbx_keypoint* __restrict__ k1 = A.keysUn + (size_t)s1 * A.stride;
+  const orbx_keypoint* __restrict__ k2 = A.keysUn + (size_t)s2 * A.stride;
+  const u8* __restrict__ d1 = A.desc + (size_t)s1 * A.stride * 32;
+  const u8* __restrict__ d2 = A.desc + (size_t)s2 * A.stride * 32;
+  const u32* __restrict__ gOff = A.gridOff + (size_t)s2 * (kGridCells + 1);
+  const u32* __restrict__ gIdx = A.gridIdx + (size_t)s2 * A.stride;
+  int* m12 = A.matches12 + (size_t)pair * A.stride;
+
+  for (int i = tid; i < n1; i += MT) m12[i] = -1;
+  for (int i = tid; i < n2; i += MT) { sMD[i] = 0xffffu; sM21[i] = 0xffffu; }
+  if (tid < HISTO_LENGTH) sHist[tid] = 0;
+
+  // ---- S1: level-0 CSR of F2 (thread t owns cells [12 t, 12 t + 12)) ----
+  constexpr int CPT = kGridCells / MT;
+  int cnt[CPT], tot = 0;
+  {
+    const int c0 = tid * CPT;
+    u32 e = gOff[c0];
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+      const u32 e1 = gOff[c0 + j + 1];
+      int n = 0;
+      for (; e < e1; ++e) n += (k2[gIdx[e]].octave == 0);
+      cnt[j] = n;
+      tot += n;
+    }
+  }
+  sPart[tid] = tot;
+  __syncthreads();
+  for (int o = 1; o < MT; o <<= 1) {
+    const int v = tid >= o ? sPart[tid - o] : 0;
+    __syncthreads();
+    sPart[tid] += v;
+    __syncthreads();
+  }
+  {
+    int run = tid ? sPart[tid - 1] : 0;
+    const int c0 = tid * CPT;
+    u32 e = gOff[c0];
+#pragma unroll
+    for (int j = 0; j < CPT; ++j) {
+      sOff0[c0 + j] = (unsigned short)run;
+      const u32 e1 = gOff[c0 + j + 1];
+      for (; e < e1; ++e) {
+        const int i2 = (int)gIdx[e];
+        const orbx_keypoint k = k2[i2];
+        if (k.octave == 0) { sCx[run] = k.x; sCy[run] = k.y; sCi[run] = (unsigned short)i2; ++run; }
+      }
+    }
+    if (tid == MT - 1) sOff0[kGridCells] = (unsigned short)run;
+  }
+  __syncthreads();
+  // ---- S2: level-0 queries of F1, ascending i1 (:36-39) ----
+  {
+    const int per = (n1 + MT - 1) / MT, b = min(tid * per, n1), e = min(b + per, n1);
+    int c = 0;
+    for (int i = b; i < e; ++i) c += !(k1[i].octave > 0);
+    sPart[tid] = c;
+    __syncthreads();
+    for (int o = 1; o < MT; o <<= 1) {
+      const int v = tid >= o ? sPart[tid - o] : 0;
+      __syncthreads();
+      sPart[tid] += v;
+      __syncthreads();
+    }
+    int run = tid ? sPart[tid - 1] : 0;
+    for (int i = b; i < e; ++i)
+      if (!(k1[i].octave > 0)) { sQ[run] = (unsigned short)i; sBin[run] = 0xff; ++run; }
+    if (tid == MT - 1) sNQ = run;
+  }
+  __syncthreads();
+  const int nQ = sNQ;
+  const float r = (float)window;
+  const float factor = (float)HISTO_LENGTH / 360.0f;
+  int nmatches = 0, badDist = 0, badRatio = 0;  // live in warp 0
+  constexpr u32 kNone = 0xffffffffu;
+
+  for (int qs = 0; qs < nQ;) {
+    // (a) segment sizes, one thread per query of the chunk
+    const int nCand = min(kChunkQ, nQ - qs);
+    if (tid < kChunkQ) {
+      int sz = 0;
+      if (tid < nCand) {
+        const orbx_keypoint kp1 = k1[sQ[qs + tid]];
+        int a, b, c, d;
+        if (cell_rect(P, kp1.x, kp1.y, r, a, b, c, d))
+          for (int ix = a; ix <= b; ++ix) sz += (int)sOff0[ix * kGridRows + d + 1] - (int)sOff0[ix * kGridRows + c];
+      }
+      sPart[tid] = sz;
+    }
+    __syncthreads();
+    // (b) exclusive prefix over the 128 sizes; the chunk takes the queries whose entries fit
+    if (warp == 0) {
+      int v[4], sum = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { v[j] = sPart[lane * 4 + j]; sum += v[j]; }
+      int inc = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+      }
+      int start = inc - sum, fit = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        sSeg[lane * 4 + j] = start;
+        start += v[j];
+        fit += (lane * 4 + j < nCand && start <= LY.entCap);
+      }
+      if (lane == 31) sSeg[kChunkQ] = start;
+#pragma unroll
+      for (int o = 16; o; o >>= 1) fit += __shfl_xor_sync(0xffffffffu, fit, o);
+      if (lane == 0) sChunkN = fit;
+    }
+    __syncthreads();
+    const int nq = sChunkN;  // >= 1: one segment never exceeds the level-0 keys of F2 <= entCap
+    // (c) fill, one warp per query: flattened walk over the column ranges of the cell rectangle
+    for (int qi = warp; qi < nq; qi += MW) {
+      const int segB = sSeg[qi], segN = sSeg[qi + 1] - segB;
+      if (segN == 0) continue;
+      const int i1 = sQ[qs + qi];
+      const orbx_keypoint kp1 = k1[i1];
+      int minCX, maxCX, minCY, maxCY;
+      cell_rect(P, kp1.x, kp1.y, r, minCX, maxCX, minCY, maxCY);
+      const int nCols = maxCX - minCX + 1;
+      int b0 = 0, c0 = 0, b1 = 0, c1 = 0;
+      if (lane < nCols) {
+        const int cell = (minCX + lane) * kGridRows;
+        b0 = (int)sOff0[cell + minCY];
+        c0 = (int)sOff0[cell + maxCY + 1] - b0;
+      }
+      if (lane + 32 < nCols) {
+        const int cell = (minCX + lane + 32) * kGridRows;
+        b1 = (int)sOff0[cell + minCY];
+        c1 = (int)sOff0[cell + maxCY + 1] - b1;
+      }
+      int p0 = c0, p1 = c1;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t0 = __shfl_up_sync(0xffffffffu, p0, o), t1 = __shfl_up_sync(0xffffffffu, p1, o);
+        if (lane >= o) { p0 += t0; p1 += t1; }
+      }
+      const int tot0 = __shfl_sync(0xffffffffu, p0, 31);
+      int* cs = sColStart[warp];
+      int* cb = sColBeg[warp];
+      cs[lane] = p0 - c0; cb[lane] = b0;
+      cs[lane + 32] = tot0 + p1 - c1; cb[lane + 32] = b1;
+      if (lane == 0) cs[kGridCols] = segN;
+      __syncwarp();
+      const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i1 * 32));
+      const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i1 * 32) + 1);
+      for (int t = lane; t < segN; t += 32) {
+        int lo = 0, hi = kGridCols;  // column of flattened position t: last c with cs[c] <= t
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+          const int mid = (lo + hi) >> 1;
+          if (cs[mid] <= t) lo = mid; else hi = mid;
+        }
+        const int p = cb[lo] + (t - cs[lo]);
+        const float dx = sCx[p] - kp1.x, dy = sCy[p] - kp1.y;
+        u32 en = kInvalid;
+        if (fabsf(dx) < r && fabsf(dy) < r) {  // Frame.cpp:196-199
+          const int i2 = sCi[p];
+          en = ((u32)hamming256(a0, a1, d2 + (size_t)i2 * 32) << 16) | (u32)i2;
+        }
+        sEnt[segB + t] = en;
+      }
+      __syncwarp();
+    }
+    __syncthreads();
+    // (d) the reference loop over the chunk's queries, in order (:36-117), by warp 0
+    if (warp == 0) {
+      for (int qi = 0; qi < nq; ++qi) {
+        const int segB = sSeg[qi], segN = sSeg[qi + 1] - segB;
+        if (segN == 0) continue;  // vIndices2.empty(), :46
+        u32 key = kNone;          // (best distance << 20) | visiting position
+        int bidx = -1, bd2 = INT_MAX, found = 0;
+        for (int t = lane; t < segN; t += 32) {
+          const u32 en = sEnt[segB + t];
+          if (en == kInvalid) continue;
+          found = 1;
+          const int dist = (int)(en >> 16), i2 = (int)(en & 0xffffu);
+          if ((int)sMD[i2] <= dist) continue;  // :67
+          const u32 k = ((u32)dist << 20) | (u32)t;
+          if (k < key) {  // lane-local positions ascend, so "dist < best" and "k < key" agree
+            if (key != kNone) bd2 = (int)(key >> 20);
+            key = k; bidx = i2;
+          } else if (dist < bd2) bd2 = dist;
+        }
+        if (!__any_sync(0xffffffffu, found)) continue;  // no key of the rectangle is inside the window
+        const u32 best = __reduce_min_sync(0xffffffffu, key);
+        const int winner = __ffs((int)__ballot_sync(0xffffffffu, key == best)) - 1;
+        const int bestDist = best == kNone ? INT_MAX : (int)(best >> 20);
+        const int mine2 = (lane == winner) ? bd2 : (key == kNone ? INT_MAX : (int)(key >> 20));
+        const int bestDist2 = (int)__reduce_min_sync(0xffffffffu, (u32)mine2);
+        const int bestIdx = __shfl_sync(0xffffffffu, bidx, winner);
+        if (bestDist > TH_LOW) { ++badDist; continue; }                                        // :82
+        if ((float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) { ++badRatio; continue; }  // :87
+        const int prev = sM21[bestIdx] == 0xffffu ? -1 : (int)sM21[bestIdx];
+        if (prev >= 0) --nmatches;  // :95-98
+        ++nmatches;
+        const int i1 = sQ[qs + qi];
+        __syncwarp();
+        if (lane == 0) {
+          if (prev >= 0) m12[prev] = -1;
+          m12[i1] = bestIdx;
+          sM21[bestIdx] = (unsigned short)i1;
+          sMD[bestIdx] = (unsigned short)bestDist;
+          if (checkOri) {
+            float rot = k1[i1].angle - k2[bestIdx].angle;
+            if (rot < 0.0f) rot = rot + 360.0f;
+            int bin = (int)roundf(__fmul_rn(rot, factor));
+            if (bin == HISTO_LENGTH) bin = 0;
+            sBin[qs + qi] = (u8)bin;
+            sHist[bin] += 1;
+          }
+        }
+        __syncwarp();
+      }
+    }
+    __syncthreads();
+    qs += nq;
+  }
+
+  if (warp != 0) return;
+  int badOri = 0;
+  if (checkOri) {
+    // ComputeThreeMaxima, :152-183
+    int i1m = -1, i2m = -1, i3m = -1, m1 = 0, m2 = 0, m3 = 0;
+    for (int i = 0; i < HISTO_LENGTH; ++i) {
+      const int h = sHist[i];
+      if (h > m1) { m3 = m2; m2 = m1; m1 = h; i3m = i2m; i2m = i1m; i1m = i; }
+      else if (h > m2) { m3 = m2; m2 = h; i3m = i2m; i2m = i; }
+      else if (h > m3) { m3 = h; i3m = i; }
+    }
+    if ((float)m2 < __fmul_rn(0.1f, (float)m1)) { i2m = -1; i3m = -1; }
+    else if ((float)m3 < __fmul_rn(0.1f, (float)m1)) { i3m = -1; }
+    for (int qp = lane; qp < nQ; qp += 32) {
+      const int bn = sBin[qp];
+      if (bn != 0xff && bn != i1m && bn != i2m && bn != i3m) { m12[sQ[qp]] = -1; ++badOri; }  // :123-141
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) badOri += __shfl_xor_sync(0xffffffffu, badOri, o);
+    nmatches -= badOri;
+  }
+  if (lane == 0) {
+    A.nmatches[pair] = nmatches;
+    A.counters[pair * 3 + 0] = badDist;
+    A.counters[pair * 3 + 1] = badRatio;
+    A.counters[pair * 3 + 2] = badOri;
+  }
+}
+
 int launch_match(const Params& P, const MatchArgs& A, int nPairs, int pairStep, float nnratio, int checkOri,
                  int window, cudaStream_t st) {
   if (nPairs <= 0) return 0;
-  k_match<<<nPairs, 32, 0, st>>>(P, A, pairStep, nnratio, checkOri, window);
+  const MatchSmem LY = match_smem_layout(A.stride);
+  static const bool forceSerial = std::getenv("ORBX_MATCH_SERIAL") != nullptr;  // test hook for the fallback kernel
+  if (!forceSerial && A.stride < 65535 && LY.total <= 200 * 1024) {
+    if (cudaFuncSetAttribute(k_match_cta, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess) return 0;
+    k_match_cta<<<nPairs, MT, LY.total, st>>>(P, A, pairStep, nnratio, checkOri, window);
+  } else {
+    // keypoint capacities beyond what the shared-memory tables hold: the one-warp-per-pair walk
+    k_match<<<nPairs, 32, 0, st>>>(P, A, pairStep, nnratio, checkOri, window);
+  }
   return 1;
 }
 

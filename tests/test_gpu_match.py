@@ -144,3 +144,54 @@ def test_stream_path(fe, oracle, synth, cfg):
     for k in out:
         assert np.array_equal(out[k].view(np.uint8), out2[k].view(np.uint8)), k
     E.close()
+
+
+def test_matcher_chunking_and_wide_windows(fe, oracle, synth):
+    """Windows that cover the image (brute-force mode of config 5) make every level-0 key a candidate of
+    every query, so the entry buffer of k_match_cta is filled in several chunks."""
+    W, H, nf = 752, 480, 2000
+    K4, D4 = synth.camera_for(W, H)
+    E = fe.ORBextractor(nf, 1.2, 8, 0, 0, W, H)   # thresholds 0/0: full quotas, tie-heavy distances
+    bounds = E.set_camera(K4, D4)
+    R = oracle.Extractor(nf, 1.2, 8, 0, 0)
+    imgs = synth.frames(2, W, H, first_pair=21)
+    G = [fe.Frame(E, im) for im in imgs]
+    O = []
+    for im in imgs:
+        k, d, _ = R(im)
+        O.append(oracle.Frame(k, d, K4, D4, bounds))
+    for w in (8192, 1000, 300, 100, 7, 1):
+        for ratio, ori in ((0.9, True), (0.6, True), (0.95, False)):
+            n, m12, cnt = fe.ORBmatcher(ratio, ori).SearchForInitialization(G[0], G[1], w)
+            rn, rm12, rcnt = oracle.search_for_initialization(O[0], O[1], ratio, ori, w)
+            assert n == rn and np.array_equal(m12, rm12) and np.array_equal(cnt, rcnt), (w, ratio, ori)
+    E.close()
+
+
+def test_serial_matcher_fallback():
+    """k_match (one warp per pair) is the fallback for keypoint capacities beyond the shared-memory tables of
+    k_match_cta; ORBX_MATCH_SERIAL forces it so that it stays covered.  Own process: the hook is read once."""
+    import os
+    import subprocess
+    import sys
+    code = (
+        "import numpy as np\n"
+        "from oracle import orb_oracle as O\n"
+        "from orb_slam_tracking_b200 import frontend as fe, synth\n"
+        "W, H, nf = 640, 480, 1000\n"
+        "K4, D4 = synth.camera_for(W, H)\n"
+        "E = fe.ORBextractor(nf, 1.2, 8, 20, 7, W, H)\n"
+        "b = E.set_camera(K4, D4)\n"
+        "R = O.Extractor(nf, 1.2, 8, 20, 7)\n"
+        "imgs = synth.frames(2, W, H, first_pair=9)\n"
+        "G = [fe.Frame(E, im) for im in imgs]\n"
+        "F = [O.Frame(*R(im)[:2], K4, D4, b) for im in imgs]\n"
+        "for w in (100, 640):\n"
+        "    n, m, c = fe.ORBmatcher(0.9, True).SearchForInitialization(G[0], G[1], w)\n"
+        "    rn, rm, rc = O.search_for_initialization(F[0], F[1], 0.9, True, w)\n"
+        "    assert n == rn and np.array_equal(m, rm) and np.array_equal(c, rc), w\n"
+        "print('serial ok')\n")
+    env = dict(os.environ, ORBX_MATCH_SERIAL="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True)
+    assert out.returncode == 0 and "serial ok" in out.stdout, out.stdout + out.stderr
