@@ -145,6 +145,13 @@ int orbx_stream_run(orbx_ctx* ctx, int n_img, float nnratio, int check_orientati
 int orbx_stream_download(orbx_ctx* ctx, int n_img, orbx_keypoint* kps, orbx_keypoint* kps_un, uint8_t* desc,
                          int cap, int* n_out, int* matches12, int* nmatches, int* counters3);
 /* compact result of the e2e path: per pair nmatches + matches12 only */
+/* Host frames in, everything out, in one call: n_img frames (W*H bytes each, contiguous) are cut into
+ * chunks of `chunk` frames (even; <= 0 picks 128) whose H2D copy, kernels and D2H copy overlap on three
+ * streams.  Buffers as in orbx_stream_download; page-locked memory (orbx_host_alloc) keeps the copies
+ * asynchronous.  Replaces the per-pair sequence of demo/demo_initialization.cpp:65-108 for a stream. */
+int orbx_stream_process(orbx_ctx* ctx, const uint8_t* imgs, int n_img, float nnratio, int check_orientation,
+                        int window_size, int chunk, orbx_keypoint* kps, orbx_keypoint* kps_un, uint8_t* desc, int cap,
+                        int* n_out, int* matches12, int* nmatches, int* counters3);
 int orbx_stream_sync(orbx_ctx* ctx);
 /* CUDA-event timing on the context's stream: start/stop bracket enqueued work; elapsed in ms.
  * which = 0: whole bracket; 1..: per-stage timers recorded inside orbx_stream_run when

@@ -74,6 +74,7 @@ struct Params {
   int kpStride;        // keypoint slots per frame = max(nfeatures, sum of quotas)
   int trigMode;
   int nCells, nBlurTiles;
+  int slot0;               // first slot of this launch inside the context's slot arrays (TMA z origin; pointers below are pre-shifted)
   int fastBoxW, fastBoxH;  // TMA box of k_fast: bytes per staged row (multiple of 16, >= widest cell ROI + 8), rows
   u32 slabBytes, candTotal, nodeTotal;
   int umax[16];
@@ -135,6 +136,7 @@ __device__ __forceinline__ int reflect101(int i, int len) {
 }
 
 // launchers (one per .cu file); all enqueue on `st` and return the number of kernel launches
+int launch_ingest(const Params& P, const u8* dense, int nSlots, cudaStream_t st);
 int launch_pyramid(const Params& P, const int* const* dTabs, int nSlots, cudaStream_t st);
 int launch_blur(const Params& P, int nSlots, cudaStream_t st);
 int launch_fast(const Params& P, const TmaMaps& M, int nSlots, cudaStream_t st);

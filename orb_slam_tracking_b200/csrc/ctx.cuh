@@ -32,6 +32,10 @@ struct orbx_ctx {
   orbx::TmaMaps tma;               // per-level tensor maps over P.pyr (k_fast tile staging)
   int device;
   cudaStream_t stream;
+  cudaStream_t sH2D, sD2H;         // copy streams of the pipelined host path (orbx_stream_process)
+  std::vector<cudaEvent_t> evChunk; // 2 per chunk: images landed, results ready
+  orbx::u8* dIngest;               // dense [maxBatch][H][W] staging of uploaded frames
+  int* hStatus;                    // pinned [maxBatch]
   std::vector<void*> allocs;       // every cudaMalloc, freed in orbx_destroy
   std::vector<int*> dResizeTabs;   // per level (entry 0 unused)
   const int** hTabPtrs;            // host array of device pointers for launch_pyramid

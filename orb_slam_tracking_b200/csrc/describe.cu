@@ -84,23 +84,27 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) k_describe(const __grid_con
     const int xa = (x - kHalfPatch) & ~3;  // 9 aligned words cover [x-15, x+15]
     const u8* __restrict__ img = level_ptr((const u8*)P.pyr, P, slot, l) + (size_t)(y - kHalfPatch) * L.pitch + xa;
     int m10 = 0, m01 = 0;
-#pragma unroll 3
-    for (int i = lane; i < 31 * 9; i += 32) {
-      const int r = i / 9, w = i - 9 * r;
-      const int v = r - kHalfPatch;
-      const int d = P.umax[v < 0 ? -v : v];
-      const u32 word = __ldg(reinterpret_cast<const u32*>(img + (size_t)r * L.pitch) + w);
-      const int u0 = xa + 4 * w - x;
-      int si = 0, su = 0;
+    // lanes 0..26 = 3 rows x 9 words; a lane keeps its word column, so its four column offsets u_j are fixed
+    // and only the row's half-width d = umax[|v|] changes: byte j counts iff |u_j| <= d
+    const int lr = lane / 9, w = lane - 9 * lr;
+    const int u0 = xa + 4 * w - x;
+    const int a0 = abs(u0), a1 = abs(u0 + 1), a2 = abs(u0 + 2), a3 = abs(u0 + 3);
+    const int upk = (u0 & 255) | (((u0 + 1) & 255) << 8) | (((u0 + 2) & 255) << 16) | (((u0 + 3) & 255) << 24);  // s8 x 4
+    if (lane < 27) {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int u = u0 + j;
-        const int I = (u >= -d && u <= d) ? (int)((word >> (8 * j)) & 255u) : 0;
-        si += I;
-        su += u * I;
+      for (int rb = 0; rb < 33; rb += 3) {
+        const int r = rb + lr;
+        if (r < 31) {
+          const int v = r - kHalfPatch;
+          const int d = P.umax[v < 0 ? -v : v];
+          u32 word = __ldg(reinterpret_cast<const u32*>(img + (size_t)r * L.pitch) + w);
+          word &= (d >= a0 ? 0xffu : 0u) | (d >= a1 ? 0xff00u : 0u) | (d >= a2 ? 0xff0000u : 0u) | (d >= a3 ? 0xff000000u : 0u);
+          int su;
+          asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(su) : "r"(word), "r"(upk), "r"(0));
+          m10 += su;
+          m01 += v * (int)__dp4a(word, 0x01010101u, 0u);
+        }
       }
-      m10 += su;
-      m01 += v * si;
     }
 #pragma unroll
     for (int o = 16; o; o >>= 1) {
@@ -135,10 +139,15 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) k_describe(const __grid_con
     const int xa = (x - 18) & ~3;  // 10 aligned words cover [x-18, x+18]
     const u8* __restrict__ bl = level_ptr((const u8*)P.blur, P, slot, l) + (size_t)(y - 18) * L.pitch + xa;
     __syncwarp();
-#pragma unroll 4
-    for (int i = lane; i < kPatchRows * kPatchWords; i += 32) {
-      const int r = i / kPatchWords, w = i - kPatchWords * r;
-      patch[i] = __ldg(reinterpret_cast<const u32*>(bl + (size_t)r * L.pitch) + w);
+    {  // lanes 0..29 = 3 rows x 10 words per step
+      const int lr = lane / kPatchWords, w = lane - kPatchWords * lr;
+      if (lane < 3 * kPatchWords) {
+#pragma unroll
+        for (int rb = 0; rb < 39; rb += 3) {
+          const int r = rb + lr;
+          if (r < kPatchRows) patch[r * kPatchWords + w] = __ldg(reinterpret_cast<const u32*>(bl + (size_t)r * L.pitch) + w);
+        }
+      }
     }
     __syncwarp();
     const u8* centre = reinterpret_cast<const u8*>(patch) + 18 * (4 * kPatchWords) + (x - xa);

@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ P
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(tileBytes) : "memory");
     asm volatile(
         "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
-        ::"r"(smem_addr(sImg)), "l"(reinterpret_cast<u64>(&M.lvl[c.level])), "r"(xs), "r"((int)c.y0), "r"(slot), "r"(bar)
+        ::"r"(smem_addr(sImg)), "l"(reinterpret_cast<u64>(&M.lvl[c.level])), "r"(xs), "r"((int)c.y0), "r"(slot + P.slot0), "r"(bar)
         : "memory");
   }
   {  // zero the m-map while the tile is in flight

@@ -15,9 +15,28 @@ inline void mark(orbx_ctx* c, int i) {
   if (c->stageTiming) cudaEventRecord(c->evStage[i], c->stream);
 }
 
-// Enqueues extraction for slots [0, n).  Level 0 of each slot must already hold the image.
-int enqueue_extract(orbx_ctx* c, int n, int lap0, int lap1) {
-  const Params& P = c->P;
+// The context's Params with every per-slot array advanced to slot s0, so that a launch over nSlots slots
+// works on [s0, s0 + nSlots) (the chunks of orbx_stream_process).
+Params shifted(const orbx_ctx* c, int s0) {
+  Params Q = c->P;
+  if (s0 == 0) return Q;
+  const size_t s = (size_t)s0;
+  Q.slot0 = s0;
+  Q.pyr += s * Q.slabBytes; Q.blur += s * Q.slabBytes;
+  Q.candKey += s * Q.candTotal; Q.candXY += s * Q.candTotal; Q.candNode += s * Q.candTotal;
+  Q.candCount += s * kMaxLevels;
+  Q.nodeBox += s * Q.nodeTotal; Q.nodeCount += s * Q.nodeTotal; Q.nodeSlot += s * Q.nodeTotal; Q.nodeBest += s * Q.nodeTotal;
+  Q.nodeAux += 4 * s * Q.nodeTotal; Q.nodeList += s * Q.nodeTotal; Q.nodeScan += s * Q.nodeTotal; Q.nodeSort += s * Q.nodeTotal;
+  const size_t k = s * (size_t)Q.kpStride;
+  Q.lvlXY += k; Q.lvlResp += k; Q.lvlAngle += k; Q.lvlDesc += k * 32; Q.lvlCount += s * kMaxLevels;
+  Q.status += s;
+  Q.outKp += k; Q.outDesc += k * 32; Q.outN += s; Q.outMono += s;
+  Q.keysUn += k; Q.gridOff += s * (kGridCells + 1); Q.gridIdx += k;
+  return Q;
+}
+
+// Enqueues extraction for the n slots of P (level 0 of each slot must already hold the image).
+int enqueue_extract(orbx_ctx* c, const Params& P, int n, int lap0, int lap1) {
   cudaStream_t st = c->stream;
   CU(c, cudaMemsetAsync(P.candCount, 0, (size_t)n * kMaxLevels * sizeof(u32), st));
   CU(c, cudaMemsetAsync(P.status, 0, (size_t)n * sizeof(int), st));
@@ -34,6 +53,23 @@ int enqueue_extract(orbx_ctx* c, int n, int lap0, int lap1) {
   mark(c, 5);
   CU(c, cudaGetLastError());
   c->lastBatch = n;
+  return ORBX_OK;
+}
+
+// glue + SearchForInitialization over the pairs (2k, 2k+1) of the n slots of P; pair0 = first pair index
+int enqueue_glue_match(orbx_ctx* c, const Params& P, int n, int pair0, float nnratio, int checkOri, int window) {
+  c->launches += launch_glue(P, n, c->stream);
+  mark(c, 6);
+  MatchArgs A;
+  A.keysUn = P.keysUn; A.desc = P.outDesc; A.gridOff = P.gridOff; A.gridIdx = P.gridIdx; A.n = P.outN;
+  A.stride = P.kpStride;
+  A.matches12 = c->dMatches12 + (size_t)pair0 * P.kpStride;
+  A.nmatches = c->dNMatches + pair0;
+  A.counters = c->dCounters + (size_t)pair0 * 3;
+  A.scratch = c->dMatchScratch + (size_t)pair0 * 3 * P.kpStride;
+  c->launches += launch_match(P, A, n / 2, 2, nnratio, checkOri, window, c->stream);
+  mark(c, 7);
+  CU(c, cudaGetLastError());
   return ORBX_OK;
 }
 
@@ -63,7 +99,7 @@ extern "C" int orbx_extract_batch(orbx_ctx* c, const uint8_t* const* imgs, size_
     CU(c, cudaMemcpy2DAsync(P.pyr + (size_t)i * P.slabBytes + P.lv[0].imgOff, P.lv[0].pitch, imgs[i], step, P.W, P.H,
                             cudaMemcpyHostToDevice, c->stream));
   const int lap0 = lapping ? lapping[0] : 0, lap1 = lapping ? lapping[1] : 0;
-  int rc = enqueue_extract(c, n_img, lap0, lap1);
+  int rc = enqueue_extract(c, P, n_img, lap0, lap1);
   if (rc) return rc;
   std::vector<int> n(n_img), mono(n_img);
   CU(c, cudaMemcpyAsync(n.data(), P.outN, n_img * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
@@ -184,10 +220,10 @@ extern "C" int orbx_stream_upload(orbx_ctx* c, const uint8_t* imgs, int n_img) {
   if (!c || !imgs || n_img < 1 || n_img > c->P.maxBatch) return ORBX_ERR_ARG;
   const Params& P = c->P;
   CU(c, cudaSetDevice(c->device));
-  // one strided copy for the whole batch: rows of W bytes, W*H apart per image -> pitch rows, slab apart
-  for (int i = 0; i < n_img; ++i)
-    CU(c, cudaMemcpy2DAsync(P.pyr + (size_t)i * P.slabBytes + P.lv[0].imgOff, P.lv[0].pitch,
-                            imgs + (size_t)i * P.W * P.H, P.W, P.W, P.H, cudaMemcpyHostToDevice, c->stream));
+  // one DMA for the whole batch into the dense staging buffer, then level 0 of every slot on the device
+  CU(c, cudaMemcpyAsync(c->dIngest, imgs, (size_t)n_img * P.W * P.H, cudaMemcpyHostToDevice, c->stream));
+  launch_ingest(P, c->dIngest, n_img, c->stream);
+  CU(c, cudaGetLastError());
   return ORBX_OK;
 }
 
@@ -197,18 +233,9 @@ extern "C" int orbx_stream_run(orbx_ctx* c, int n_img, float nnratio, int check_
   const Params& P = c->P;
   CU(c, cudaSetDevice(c->device));
   c->launches = 0;
-  int rc = enqueue_extract(c, n_img, 0, 0);
+  int rc = enqueue_extract(c, P, n_img, 0, 0);
   if (rc) return rc;
-  c->launches += launch_glue(P, n_img, c->stream);
-  mark(c, 6);
-  MatchArgs A;
-  A.keysUn = P.keysUn; A.desc = P.outDesc; A.gridOff = P.gridOff; A.gridIdx = P.gridIdx; A.n = P.outN;
-  A.stride = P.kpStride; A.matches12 = c->dMatches12; A.nmatches = c->dNMatches; A.counters = c->dCounters;
-  A.scratch = c->dMatchScratch;
-  c->launches += launch_match(P, A, n_img / 2, 2, nnratio, check_orientation, window_size, c->stream);
-  mark(c, 7);
-  CU(c, cudaGetLastError());
-  return ORBX_OK;
+  return enqueue_glue_match(c, P, n_img, 0, nnratio, check_orientation, window_size);
 }
 
 extern "C" int orbx_stream_sync(orbx_ctx* c) {
@@ -258,6 +285,78 @@ extern "C" int orbx_stream_download(orbx_ctx* c, int n_img, orbx_keypoint* kps, 
   }
   CU(c, cudaStreamSynchronize(st));
   return ORBX_OK;
+}
+
+// Host images in, results out, in one call: the batch is cut into chunks of `chunk` frames and the three
+// legs of each chunk run on their own streams -- H2D DMA of chunk k+1 and D2H DMA of chunk k-1 overlap the
+// kernels of chunk k.  imgs and the output buffers should be page-locked (orbx_host_alloc) for the copies
+// to be asynchronous.  Returns after everything has landed on the host.
+extern "C" int orbx_stream_process(orbx_ctx* c, const uint8_t* imgs, int n_img, float nnratio, int check_orientation,
+                                   int window_size, int chunk, orbx_keypoint* kps, orbx_keypoint* kps_un, uint8_t* desc,
+                                   int cap, int* n_out, int* matches12, int* nmatches, int* counters3) {
+  if (!c || !imgs || n_img < 1 || n_img > c->P.maxBatch) return ORBX_ERR_ARG;
+  if (!c->cameraSet) return ORBX_ERR_STATE;
+  if ((kps || kps_un || desc || matches12) && cap < 1) return ORBX_ERR_ARG;
+  const Params& P = c->P;
+  CU(c, cudaSetDevice(c->device));
+  if (chunk <= 0) chunk = 128;
+  chunk = std::max(2, chunk & ~1);
+  const int nChunks = (n_img + chunk - 1) / chunk;
+  while ((int)c->evChunk.size() < 2 * nChunks) {
+    cudaEvent_t e;
+    CU(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    c->evChunk.push_back(e);
+  }
+  const size_t imgBytes = (size_t)P.W * P.H;
+  const int m = std::min(cap, P.kpStride);
+  const size_t w = (size_t)m;
+  const int timing = c->stageTiming;
+  c->stageTiming = 0;  // per-stage events belong to the unchunked orbx_stream_run
+  c->launches = 0;
+  int rc = ORBX_OK;
+  for (int k = 0; k < nChunks && rc == ORBX_OK; ++k) {
+    const int s0 = k * chunk, n = std::min(chunk, n_img - s0), p0 = s0 / 2, np = n / 2;
+    cudaEvent_t evIn = c->evChunk[2 * k], evOut = c->evChunk[2 * k + 1];
+    CU(c, cudaMemcpyAsync(c->dIngest + s0 * imgBytes, imgs + s0 * imgBytes, n * imgBytes, cudaMemcpyHostToDevice, c->sH2D));
+    CU(c, cudaEventRecord(evIn, c->sH2D));
+    CU(c, cudaStreamWaitEvent(c->stream, evIn, 0));
+    const Params Q = shifted(c, s0);
+    c->launches += launch_ingest(Q, c->dIngest + s0 * imgBytes, n, c->stream);
+    if ((rc = enqueue_extract(c, Q, n, 0, 0))) break;
+    if ((rc = enqueue_glue_match(c, Q, n, p0, nnratio, check_orientation, window_size))) break;
+    CU(c, cudaEventRecord(evOut, c->stream));
+    cudaStream_t sd = c->sD2H;
+    CU(c, cudaStreamWaitEvent(sd, evOut, 0));
+    CU(c, cudaMemcpyAsync(c->hStatus + s0, Q.status, n * sizeof(int), cudaMemcpyDeviceToHost, sd));
+    if (kps)
+      CU(c, cudaMemcpy2DAsync(kps + (size_t)s0 * cap, (size_t)cap * sizeof(orbx_keypoint), Q.outKp,
+                              (size_t)P.kpStride * sizeof(orbx_keypoint), w * sizeof(orbx_keypoint), n, cudaMemcpyDeviceToHost, sd));
+    if (kps_un)
+      CU(c, cudaMemcpy2DAsync(kps_un + (size_t)s0 * cap, (size_t)cap * sizeof(orbx_keypoint), Q.keysUn,
+                              (size_t)P.kpStride * sizeof(orbx_keypoint), w * sizeof(orbx_keypoint), n, cudaMemcpyDeviceToHost, sd));
+    if (desc)
+      CU(c, cudaMemcpy2DAsync(desc + (size_t)s0 * cap * 32, (size_t)cap * 32, Q.outDesc, (size_t)P.kpStride * 32, w * 32, n,
+                              cudaMemcpyDeviceToHost, sd));
+    if (n_out) CU(c, cudaMemcpyAsync(n_out + s0, Q.outN, n * sizeof(int), cudaMemcpyDeviceToHost, sd));
+    if (np > 0) {
+      if (matches12)
+        CU(c, cudaMemcpy2DAsync(matches12 + (size_t)p0 * cap, (size_t)cap * sizeof(int), c->dMatches12 + (size_t)p0 * P.kpStride,
+                                (size_t)P.kpStride * sizeof(int), w * sizeof(int), np, cudaMemcpyDeviceToHost, sd));
+      if (nmatches) CU(c, cudaMemcpyAsync(nmatches + p0, c->dNMatches + p0, np * sizeof(int), cudaMemcpyDeviceToHost, sd));
+      if (counters3) CU(c, cudaMemcpyAsync(counters3 + 3 * p0, c->dCounters + 3 * p0, np * 3 * sizeof(int), cudaMemcpyDeviceToHost, sd));
+    }
+  }
+  c->stageTiming = timing;
+  cudaStreamSynchronize(c->sD2H);
+  cudaStreamSynchronize(c->stream);
+  cudaStreamSynchronize(c->sH2D);
+  if (rc) return rc;
+  CU(c, cudaGetLastError());
+  c->lastBatch = n_img;
+  int worst = 0;
+  for (int i = 0; i < n_img; ++i) worst = std::min(worst, c->hStatus[i]);
+  if (worst) c->err = "device-side status " + std::to_string(worst);
+  return worst;
 }
 
 // ---- timing ---------------------------------------------------------------------------------------

@@ -9,6 +9,8 @@
 // 32-bit word; the two source rows are read through the read-only path (a warp touches two
 // 154-byte spans per row).  Coefficient tables are computed once on the host with the
 // reference's float/double expressions and kept in L2.
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace orbx {
@@ -50,6 +52,35 @@ __global__ void __launch_bounds__(256) k_resize(const __grid_constant__ Params P
   }
   // pitch is a multiple of 128, so the 4-pixel group is always inside the row allocation
   *reinterpret_cast<u32*>(dst + (size_t)dy * D.pitch + dx0) = packed;
+}
+
+// Level 0 of each slot from a dense [n][H][W] staging buffer (one DMA from the host for a whole chunk of
+// frames instead of one strided copy per frame): 16 bytes per thread where the geometry allows.
+__global__ void __launch_bounds__(256) k_ingest(const __grid_constant__ Params P, const u8* __restrict__ dense) {
+  const int slot = blockIdx.y;
+  const LevelInfo& L = P.lv[0];
+  const u8* __restrict__ src = dense + (size_t)slot * P.W * P.H;
+  u8* dst = level_ptr(P.pyr, P, slot, 0);
+  if ((P.W & 15) == 0) {
+    const int wv = P.W >> 4, total = wv * P.H;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+      const int y = i / wv, x = i - y * wv;
+      reinterpret_cast<uint4*>(dst + (size_t)y * L.pitch)[x] = __ldg(reinterpret_cast<const uint4*>(src + (size_t)y * P.W) + x);
+    }
+  } else {
+    const int total = P.W * P.H;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+      const int y = i / P.W, x = i - y * P.W;
+      dst[(size_t)y * L.pitch + x] = __ldg(src + i);
+    }
+  }
+}
+
+int launch_ingest(const Params& P, const u8* dense, int nSlots, cudaStream_t st) {
+  const int work = (P.W & 15) == 0 ? (P.W >> 4) * P.H : P.W * P.H;
+  dim3 grid(std::min((work + 255) / 256, 64), nSlots);
+  k_ingest<<<grid, 256, 0, st>>>(P, dense);
+  return 1;
 }
 
 int launch_pyramid(const Params& P, const int* const* dTabs, int nSlots, cudaStream_t st) {

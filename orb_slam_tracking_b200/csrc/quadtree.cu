@@ -20,9 +20,17 @@ namespace orbx {
 
 constexpr int QT = 512;
 
+constexpr int kSortSmem = 2048;  // sort elements kept in shared memory (a generation rarely has more divisible nodes)
+
 struct QtS {
   int nNodes, size, gen0, gen1, nS, nProc, nToExpand, cut;
   int part[QT];
+  u64 srt[kSortSmem];
+};
+
+// (count, UL.x, node id) in one word: std::sort's comparator (:684-696) sees only (count, UL.x)
+struct PackedLess {
+  __device__ __forceinline__ bool operator()(const u64& a, const u64& b) const { return (a >> 24) < (b >> 24); }
 };
 
 // In-place inclusive scan of a[0..n) by the whole CTA.  Returns the total to every thread.
@@ -117,19 +125,29 @@ __global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params 
       for (int j = tid; j < G; j += QT) scan[j] = nCount[gen0 + j] > 1;
       __syncthreads();
       nS = cta_scan(scan, G, S.part);
+      // the sort runs in one thread (its tie order is the algorithm's, see stdsort_emul.cuh): keep its
+      // elements in shared memory as single 64-bit words, count << 40 | UL.x << 24 | node id
+      const bool inSmem = nS <= kSortSmem;
       for (int j = tid; j < G; j += QT) {
         const int node = gen0 + j, c = nCount[node];
         if (c > 1) {
-          SortElem e;
-          e.key = ((u64)(u32)c << 32) | (u64)(u32)(int)nBox[node].x;
-          e.id = (u32)node; e.pad = 0;
-          srt[scan[j] - 1] = e;
+          if (inSmem) {
+            S.srt[scan[j] - 1] = ((u64)(u32)c << 40) | ((u64)(u32)(int)nBox[node].x << 24) | (u64)(u32)node;
+          } else {
+            SortElem e;
+            e.key = ((u64)(u32)c << 32) | (u64)(u32)(int)nBox[node].x;
+            e.id = (u32)node; e.pad = 0;
+            srt[scan[j] - 1] = e;
+          }
         }
       }
       __syncthreads();
-      if (tid == 0) stdsort_emul(srt, nS);
+      if (tid == 0) {
+        if (inSmem) stdsort_emul_t(S.srt, (long)nS, PackedLess());
+        else stdsort_emul(srt, nS);
+      }
       __syncthreads();
-      for (int s = tid; s < nS; s += QT) list[s] = (int)srt[nS - 1 - s].id;
+      for (int s = tid; s < nS; s += QT) list[s] = inSmem ? (int)(S.srt[nS - 1 - s] & 0xffffffu) : (int)srt[nS - 1 - s].id;
     }
     __syncthreads();
     if (nS == 0) break;  // nothing divisible: |L| == prevSize

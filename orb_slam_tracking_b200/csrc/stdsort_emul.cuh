@@ -25,10 +25,14 @@ struct SortElem {
 
 namespace ss {
 
-ORBX_HD bool lt(const SortElem& a, const SortElem& b) { return a.key < b.key; }
-ORBX_HD void swp(SortElem& a, SortElem& b) { SortElem t = a; a = b; b = t; }
+struct KeyLess {
+  ORBX_HD bool operator()(const SortElem& a, const SortElem& b) const { return a.key < b.key; }
+};
+template <class T>
+ORBX_HD void swp(T& a, T& b) { T t = a; a = b; b = t; }
 
-ORBX_HD void push_heap(SortElem* f, long hole, long top, SortElem v) {
+template <class T, class Less>
+ORBX_HD void push_heap(T* f, long hole, long top, T v, Less lt) {
   long parent = (hole - 1) / 2;
   while (hole > top && lt(f[parent], v)) {
     f[hole] = f[parent];
@@ -38,7 +42,8 @@ ORBX_HD void push_heap(SortElem* f, long hole, long top, SortElem v) {
   f[hole] = v;
 }
 
-ORBX_HD void adjust_heap(SortElem* f, long hole, long len, SortElem v) {
+template <class T, class Less>
+ORBX_HD void adjust_heap(T* f, long hole, long len, T v, Less lt) {
   const long top = hole;
   long child = hole;
   while (child < (len - 1) / 2) {
@@ -52,16 +57,17 @@ ORBX_HD void adjust_heap(SortElem* f, long hole, long len, SortElem v) {
     f[hole] = f[child - 1];
     hole = child - 1;
   }
-  push_heap(f, hole, top, v);
+  push_heap(f, hole, top, v, lt);
 }
 
 // std::__partial_sort(first, last, last): make_heap + sort_heap (the heap_select loop is empty)
-ORBX_HD void heap_sort(SortElem* f, long len) {
+template <class T, class Less>
+ORBX_HD void heap_sort(T* f, long len, Less lt) {
   if (len >= 2) {
     long parent = (len - 2) / 2;
     for (;;) {
-      SortElem v = f[parent];
-      adjust_heap(f, parent, len, v);
+      T v = f[parent];
+      adjust_heap(f, parent, len, v, lt);
       if (parent == 0) break;
       parent--;
     }
@@ -69,14 +75,15 @@ ORBX_HD void heap_sort(SortElem* f, long len) {
   long last = len;
   while (last > 1) {
     --last;
-    SortElem v = f[last];
+    T v = f[last];
     f[last] = f[0];
-    adjust_heap(f, 0, last, v);
+    adjust_heap(f, 0, last, v, lt);
   }
 }
 
-ORBX_HD void unguarded_linear_insert(SortElem* f, long last) {
-  SortElem v = f[last];
+template <class T, class Less>
+ORBX_HD void unguarded_linear_insert(T* f, long last, Less lt) {
+  T v = f[last];
   long next = last - 1;
   while (lt(v, f[next])) {
     f[last] = f[next];
@@ -86,23 +93,25 @@ ORBX_HD void unguarded_linear_insert(SortElem* f, long last) {
   f[last] = v;
 }
 
-ORBX_HD void insertion_sort(SortElem* f, long first, long last) {
+template <class T, class Less>
+ORBX_HD void insertion_sort(T* f, long first, long last, Less lt) {
   if (first == last) return;
   for (long i = first + 1; i != last; ++i) {
     if (lt(f[i], f[first])) {
-      SortElem v = f[i];
+      T v = f[i];
       for (long j = i; j > first; --j) f[j] = f[j - 1];
       f[first] = v;
     } else {
-      unguarded_linear_insert(f, i);
+      unguarded_linear_insert(f, i, lt);
     }
   }
 }
 
 }  // namespace ss
 
-// Sorts f[0..n) exactly as std::sort(f, f + n, [](a, b){ return a.key < b.key; }) does.
-ORBX_HD void stdsort_emul(SortElem* f, long n) {
+// Sorts f[0..n) exactly as std::sort(f, f + n, lt) does.
+template <class T, class Less>
+ORBX_HD void stdsort_emul_t(T* f, long n, Less lt) {
   using namespace ss;
   if (n <= 0) return;
   // __introsort_loop with an explicit stack of (first, last, depth) for the right-hand recursions
@@ -116,7 +125,7 @@ ORBX_HD void stdsort_emul(SortElem* f, long n) {
   for (;;) {
     while (last - first > 16) {
       if (depth == 0) {
-        heap_sort(f + first, last - first);
+        heap_sort(f + first, last - first, lt);
         break;
       }
       --depth;
@@ -152,11 +161,15 @@ ORBX_HD void stdsort_emul(SortElem* f, long n) {
   }
   // __final_insertion_sort
   if (n > 16) {
-    insertion_sort(f, 0, 16);
-    for (long i = 16; i < n; ++i) unguarded_linear_insert(f, i);
+    insertion_sort(f, 0, 16, lt);
+    for (long i = 16; i < n; ++i) unguarded_linear_insert(f, i, lt);
   } else {
-    insertion_sort(f, 0, n);
+    insertion_sort(f, 0, n, lt);
   }
 }
+
+// Sorts f[0..n) exactly as std::sort(f, f + n, [](a, b){ return a.key < b.key; }) does.
+ORBX_HD void stdsort_emul(SortElem* f, long n) { stdsort_emul_t(f, n, ss::KeyLess()); }
+
 
 }  // namespace orbx

@@ -161,6 +161,7 @@ int build_geometry(Params& P, const HostTables& T, std::vector<CellDesc>& cells,
       rootTab.push_back((u8)r);
     }
     L.nodeCap = 8 * L.quota + 64 + 4 * L.nIni;
+    if (L.nodeCap >= (1 << 24) || L.candCap >= (1 << 24)) return ORBX_ERR_ARG;  // packed sort words: 24-bit count and node id
     L.nodeOff = nodeOff;
     nodeOff += align_up((u32)L.nodeCap, 32);
     // blur tiles of 128 x 32

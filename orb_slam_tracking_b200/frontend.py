@@ -218,3 +218,20 @@ class Stream:
                                          cap, ptr(out["n"]), ptr(out["matches12"]), ptr(out["nmatches"]),
                                          ptr(out["counters"])), self.ex._h)
         return out
+
+    def process(self, imgs, chunk=0, full=True):
+        """Host frames in, everything out (orbx_stream_process: chunked, copies overlapped with the kernels)."""
+        imgs = np.ascontiguousarray(imgs, np.uint8)
+        assert imgs.shape[1:] == (self.ex.height, self.ex.width)
+        n, cap = imgs.shape[0], self.ex.cap
+        out = {"n": np.zeros(n, np.int32), "nmatches": np.zeros(max(n // 2, 1), np.int32),
+               "counters": np.zeros((max(n // 2, 1), 3), np.int32),
+               "matches12": np.full((max(n // 2, 1), cap), -1, np.int32)}
+        if full:
+            out["kps"] = np.zeros((n, cap), KP_DTYPE)
+            out["kps_un"] = np.zeros((n, cap), KP_DTYPE)
+            out["desc"] = np.zeros((n, cap, 32), np.uint8)
+        check(lib().orbx_stream_process(self.ex._h, ptr(imgs), n, self.nnratio, int(self.checkOri), self.window, chunk,
+                                        ptr(out.get("kps")), ptr(out.get("kps_un")), ptr(out.get("desc")), cap, ptr(out["n"]),
+                                        ptr(out["matches12"]), ptr(out["nmatches"]), ptr(out["counters"])), self.ex._h)
+        return out

@@ -195,3 +195,24 @@ def test_serial_matcher_fallback():
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     out = subprocess.run([sys.executable, "-c", code], cwd=root, env=env, capture_output=True, text=True)
     assert out.returncode == 0 and "serial ok" in out.stdout, out.stdout + out.stderr
+
+
+@pytest.mark.parametrize("chunk", [2, 4, 6, 0])
+def test_stream_process_chunked(fe, oracle, synth, chunk):
+    """orbx_stream_process (chunked, three streams) returns exactly what upload/run/download returns."""
+    W, H, nf, B = 640, 480, 1000, 10
+    K4, D4 = synth.camera_for(W, H)
+    E = fe.ORBextractor(nf, 1.2, 8, 20, 7, W, H, max_batch=B)
+    E.set_camera(K4, D4)
+    imgs = synth.frames(B, W, H, first_pair=60)
+    S = fe.Stream(E, 0.9, True, 100)
+    S.upload(imgs)
+    S.run(B)
+    ref = S.download(B)
+    for n in (B, B - 1, 1):
+        out = S.process(imgs[:n], chunk=chunk)
+        for k in ("n", "kps", "kps_un", "desc"):
+            assert np.array_equal(out[k][:n].view(np.uint8), ref[k][:n].view(np.uint8)), (k, n)
+        for k in ("nmatches", "counters", "matches12"):
+            assert np.array_equal(out[k][:n // 2], ref[k][:n // 2]), (k, n)
+    E.close()
