@@ -4,108 +4,99 @@
 // vertical sums in 8.16, out = (v + 32768) >> 16.  The reference blurs a clone of the level, so the
 // border reflects the level itself.
 //
-// All levels of all slots in ONE launch (host-built tile table).  HBM-bound by design: reads P_l
-// (+ halo out of L2), writes P_l.  A CTA stages (32+6) rows x (128+8) bytes as aligned 32-bit words
-// (byte-wise reflection only in words that straddle the level's border), runs the row pass with
-// two funnel-shifts + two dp4a per pixel into a packed u16 tile, and the column pass with dp2a on
-// vertically paired u16 values; every thread emits 4 adjacent pixels per row as one 32-bit store.
+// All levels of all slots in ONE launch (host-built strip table).  HBM-bound by design: reads P_l
+// (+ halo out of L2), writes P_l.  One WARP per strip of 120 columns x 64 rows, no shared memory:
+// lane = one aligned 32-bit word (4 columns) of the 128 staged columns x0-4 .. x0+123; lanes 1..30 produce
+// output, lanes 0 and 31 only carry the halo.  Walking down the rows, a lane loads its word (rows are
+// fetched 7 at a time so that the loads of a block are in flight together), takes the neighbouring words
+// from the adjacent lanes by shuffle, runs the row pass with funnel shifts and dp4a, and keeps the last 7
+// row-pass results of its 4 columns in registers for the column pass (symmetric taps: 3 adds + 4
+// multiply-adds per pixel).  BORDER_REFLECT_101 in x costs nothing in the loop: a word that touches or
+// lies beyond the level's border is a lane-constant byte permutation of two aligned words inside the level.
 #include "common.cuh"
 
 namespace orbx {
 
-constexpr int kTW = 128, kTH = 32;
-constexpr int kSrcWords = kTW / 4 + 2;  // words per staged row: columns x0-4 .. x0+131
-constexpr int kRows = kTH + 6;
+constexpr int kTW = 120, kTH = 64;
+constexpr int kBlurWarps = 4;
 
-__device__ __forceinline__ u32 load_word_reflect(const u8* __restrict__ src, const LevelInfo& L, int y, int xw) {
-  // 4 bytes at columns xw..xw+3 of row y (already reflected), BORDER_REFLECT_101 in x
-  const u8* row = src + (size_t)y * L.pitch;
-  if (xw >= 0 && xw + 3 < L.w) return __ldg(reinterpret_cast<const u32*>(row + xw));
-  u32 v = 0;
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    int x = xw + k;
-    x = x < 0 ? -x : x;
-    x = x >= L.w ? 2 * (L.w - 1) - x : x;
-    x = max(x, 0);  // columns beyond the halo of the last tile are never used
-    v |= (u32)__ldg(row + x) << (8 * k);
-  }
-  return v;
-}
-
-__global__ void __launch_bounds__(256) k_blur(const __grid_constant__ Params P) {
-  __shared__ u32 sSrc[kRows * kSrcWords];
-  __shared__ uint2 sH[kRows * (kTW / 4)];  // 4 x u16 per entry
-  const BlurTile t = P.blurTiles[blockIdx.x];
+__global__ void __launch_bounds__(kBlurWarps * 32) k_blur(const __grid_constant__ Params P) {
+  const int lane = threadIdx.x & 31;
+  const int ti = blockIdx.x * kBlurWarps + (threadIdx.x >> 5);
+  if (ti >= P.nBlurTiles) return;
+  const BlurTile t = P.blurTiles[ti];
   const int slot = blockIdx.y;
   const LevelInfo& L = P.lv[t.level];
   const u8* __restrict__ src = level_ptr((const u8*)P.pyr, P, slot, t.level);
   u8* dst = level_ptr(P.blur, P, slot, t.level);
-  const int tid = threadIdx.x;
-
-  for (int i = tid; i < kRows * kSrcWords; i += 256) {
-    const int r = i / kSrcWords, k = i - r * kSrcWords;
-    int y = t.y0 + r - 3;
-    y = y < 0 ? -y : y;
-    y = y >= L.h ? 2 * (L.h - 1) - y : y;
-    y = max(y, 0);  // rows beyond the halo of the last tile are never used
-    sSrc[i] = load_word_reflect(src, L, y, t.x0 - 4 + 4 * k);
+  const int xw = t.x0 - 4 + 4 * lane;  // my 4 columns
+  // my word = bytes at the reflected columns c_k, all inside two aligned words starting at column A
+  int A, two;
+  u32 S;
+  {
+    int c[4], lo = 1 << 30, hi = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      int v = xw + k;
+      v = v < 0 ? -v : v;
+      v = v >= L.w ? 2 * (L.w - 1) - v : v;
+      v = min(max(v, 0), L.w - 1);  // lanes far beyond the level: any valid address, never used
+      c[k] = v; lo = min(lo, v); hi = max(hi, v);
+    }
+    A = lo & ~3;
+    S = (u32)(c[0] - A) | ((u32)(c[1] - A) << 4) | ((u32)(c[2] - A) << 8) | ((u32)(c[3] - A) << 12);
+    two = hi - A >= 4;
   }
-  __syncthreads();
-
-  // row pass: h[x] = sum_i k[i] * p[x + i - 3]; pixel j of group c sits at staged byte 4 + 4c + j
+  const bool emit = lane >= 1 && lane <= 30 && xw < L.w;
   constexpr u32 kA = 18u | (34u << 8) | (48u << 16) | (56u << 24);  // taps 0..3
   constexpr u32 kB = 48u | (34u << 8) | (18u << 16);                // taps 4..6 (+ one ignored byte)
-  for (int i = tid; i < kRows * (kTW / 4); i += 256) {
-    const int r = i >> 5, c = i & 31;
-    const u32* w = sSrc + r * kSrcWords + c;
-    const u32 w0 = w[0], w1 = w[1], w2 = w[2];
-    // pixel j: bytes (1+j .. 4+j) of (w0,w1) and bytes (1+j .. 4+j) of (w1,w2)
-    const u32 h0 = __dp4a(__funnelshift_r(w0, w1, 8), kA, __dp4a(__funnelshift_r(w1, w2, 8), kB, 0u));
-    const u32 h1 = __dp4a(__funnelshift_r(w0, w1, 16), kA, __dp4a(__funnelshift_r(w1, w2, 16), kB, 0u));
-    const u32 h2 = __dp4a(__funnelshift_r(w0, w1, 24), kA, __dp4a(__funnelshift_r(w1, w2, 24), kB, 0u));
-    const u32 h3 = __dp4a(w1, kA, __dp4a(w2, kB, 0u));
-    sH[i] = make_uint2(h0 | (h1 << 16), h2 | (h3 << 16));
-  }
-  __syncthreads();
-
-  // column pass: thread = 4 columns x 4 rows; vertical pairs (h[r], h[r+1]) feed dp2a
-  {
-    const int c = tid & 31, rg = tid >> 5;  // rows 4*rg .. 4*rg+3 of the tile
-    const int x = t.x0 + 4 * c;
-    if (x < L.w) {
-      uint2 h[10];
+  u32 h[7][4];
 #pragma unroll
-      for (int k = 0; k < 10; ++k) h[k] = sH[(4 * rg + k) * (kTW / 4) + c];
-      constexpr u32 k01 = 18u | (34u << 8), k23 = 48u | (56u << 8), k45 = 48u | (34u << 8), k6_ = 18u, k_6 = 18u << 8;
+  for (int k = 0; k < 7; ++k) { h[k][0] = h[k][1] = h[k][2] = h[k][3] = 0; }
+  const u8* __restrict__ colp = src + A;
+  for (int rb = 0; rb < kTH + 6; rb += 7) {
+    if (t.y0 + rb - 6 >= L.h) break;  // nothing left to emit in this strip
+    u32 v0[7], v1[7];
 #pragma unroll
-      for (int o = 0; o < 4; ++o) {
-        const int y = t.y0 + 4 * rg + o;
-        if (y < L.h) {
-          u32 px[4];
+    for (int k = 0; k < 7; ++k) {
+      int y = t.y0 + rb + k - 3;
+      y = y < 0 ? -y : y;
+      y = y >= L.h ? 2 * (L.h - 1) - y : y;
+      y = max(y, 0);  // rows beyond the halo of the last strip are never used
+      const u32* rp = reinterpret_cast<const u32*>(colp + y * L.pitch);
+      v0[k] = __ldg(rp);
+      v1[k] = two ? __ldg(rp + 1) : 0u;
+    }
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            // pair(k) = (h[k] pixel j, h[k+1] pixel j)
-            const u32 sel = (j & 1) ? 0x7632u : 0x5410u;
-#define ORBX_PAIR(k) __byte_perm((j < 2) ? h[k].x : h[k].y, (j < 2) ? h[(k) + 1].x : h[(k) + 1].y, sel)
-            u32 v = __dp2a_lo(ORBX_PAIR(o), k01, 32768u);
-            v = __dp2a_lo(ORBX_PAIR(o + 2), k23, v);
-            v = __dp2a_lo(ORBX_PAIR(o + 4), k45, v);
-            if (o < 3) v = __dp2a_lo(ORBX_PAIR(o + 6), k6_, v);   // (h[o+6], h[o+7]) * (18, 0)
-            else v = __dp2a_lo(ORBX_PAIR(o + 5), k_6, v);          // (h[o+5], h[o+6]) * (0, 18)
-#undef ORBX_PAIR
-            px[j] = v >> 16;
-          }
-          *reinterpret_cast<u32*>(dst + (size_t)y * L.pitch + x) = px[0] | (px[1] << 8) | (px[2] << 16) | (px[3] << 24);
+    for (int k = 0; k < 7; ++k) {
+      const u32 w1 = __byte_perm(v0[k], v1[k], S);
+      const u32 w0 = __shfl_up_sync(0xffffffffu, w1, 1);
+      const u32 w2 = __shfl_down_sync(0xffffffffu, w1, 1);
+      // row pass: pixel j uses bytes (1+j .. 4+j) of (w0,w1) and (1+j .. 4+j) of (w1,w2)
+      const u32 n0 = __dp4a(__funnelshift_r(w0, w1, 8), kA, __dp4a(__funnelshift_r(w1, w2, 8), kB, 0u));
+      const u32 n1 = __dp4a(__funnelshift_r(w0, w1, 16), kA, __dp4a(__funnelshift_r(w1, w2, 16), kB, 0u));
+      const u32 n2 = __dp4a(__funnelshift_r(w0, w1, 24), kA, __dp4a(__funnelshift_r(w1, w2, 24), kB, 0u));
+      const u32 n3 = __dp4a(w1, kA, __dp4a(w2, kB, 0u));
+#pragma unroll
+      for (int q = 0; q < 6; ++q) { h[q][0] = h[q + 1][0]; h[q][1] = h[q + 1][1]; h[q][2] = h[q + 1][2]; h[q][3] = h[q + 1][3]; }
+      h[6][0] = n0; h[6][1] = n1; h[6][2] = n2; h[6][3] = n3;
+      const int yo = t.y0 + rb + k - 6;
+      if (emit && rb + k >= 6 && yo < L.h) {
+        u32 px[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const u32 v = 18u * (h[0][j] + h[6][j]) + 34u * (h[1][j] + h[5][j]) + 48u * (h[2][j] + h[4][j]) + 56u * h[3][j] + 32768u;
+          px[j] = v >> 16;
         }
+        *reinterpret_cast<u32*>(dst + yo * L.pitch + xw) = px[0] | (px[1] << 8) | (px[2] << 16) | (px[3] << 24);
       }
     }
   }
 }
 
 int launch_blur(const Params& P, int nSlots, cudaStream_t st) {
-  dim3 grid(P.nBlurTiles, nSlots);
-  k_blur<<<grid, 256, 0, st>>>(P);
+  dim3 grid((P.nBlurTiles + kBlurWarps - 1) / kBlurWarps, nSlots);
+  k_blur<<<grid, kBlurWarps * 32, 0, st>>>(P);
   return 1;
 }
 

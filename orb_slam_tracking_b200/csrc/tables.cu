@@ -164,9 +164,9 @@ int build_geometry(Params& P, const HostTables& T, std::vector<CellDesc>& cells,
     if (L.nodeCap >= (1 << 24) || L.candCap >= (1 << 24)) return ORBX_ERR_ARG;  // packed sort words: 24-bit count and node id
     L.nodeOff = nodeOff;
     nodeOff += align_up((u32)L.nodeCap, 32);
-    // blur tiles of 128 x 32
-    for (int y = 0; y < L.h; y += 32)
-      for (int x = 0; x < L.w; x += 128) {
+    // blur strips of 120 x 64 (one warp each)
+    for (int y = 0; y < L.h; y += 64)
+      for (int x = 0; x < L.w; x += 120) {
         BlurTile t;
         t.level = (short)l; t.pad = 0; t.x0 = (short)x; t.y0 = (short)y;
         tiles.push_back(t);
