@@ -30,24 +30,21 @@ namespace orbx {
 
 constexpr int kFastThreads = 128;
 
-__device__ __forceinline__ int arc_value(const int (&d)[16]) {
-  // max over 16 arcs of min over 9 consecutive ring differences, and the same for -d
-  int mn2[16], mx2[16];
+// m(p) for one pixel.  Both polarities ride in one register per ring position: e_k = v - p_k + 256 in the
+// low half-word and 512 - e_k = p_k - v + 256 in the high one, so the min-of-9 / max-of-16 ladder below
+// (VIMNMX.U16x2) yields A + 256 and B + 256 together.
+__device__ __forceinline__ int arc_value(const u32 (&x)[16]) {
+  u32 mn2[16], mn4[16];
 #pragma unroll
-  for (int k = 0; k < 16; ++k) { mn2[k] = min(d[k], d[(k + 1) & 15]); mx2[k] = max(d[k], d[(k + 1) & 15]); }
-  int mn4[16], mx4[16];
+  for (int k = 0; k < 16; ++k) mn2[k] = __vminu2(x[k], x[(k + 1) & 15]);
 #pragma unroll
-  for (int k = 0; k < 16; ++k) { mn4[k] = min(mn2[k], mn2[(k + 2) & 15]); mx4[k] = max(mx2[k], mx2[(k + 2) & 15]); }
-  int A = -256, B = -256;
+  for (int k = 0; k < 16; ++k) mn4[k] = __vminu2(mn2[k], mn2[(k + 2) & 15]);
+  u32 best = 0;
 #pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    const int mn = min(min(mn4[k], mn4[(k + 4) & 15]), d[(k + 8) & 15]);
-    const int mx = max(max(mx4[k], mx4[(k + 4) & 15]), d[(k + 8) & 15]);
-    A = max(A, mn);
-    B = max(B, -mx);
-  }
-  return max(A, B);
+  for (int k = 0; k < 16; ++k) best = __vmaxu2(best, __vminu2(__vminu2(mn4[k], mn4[(k + 4) & 15]), x[(k + 8) & 15]));
+  return (int)max(best & 0xffffu, best >> 16) - 256;
 }
+__device__ __forceinline__ u32 ring_pack(int vb, int p) { return (u32)(vb - p) * 0xFFFF0001u + 0x02000000u; }
 
 // bit 7 of each byte of the result = (that byte of a) > t  OR  (that byte of b) > t.
 //   t < 128:  K = (127 - t) * 0x01010101; (x & 0x7f) + K carries into bit 7 iff (x & 0x7f) > t, and x >= 128 > t.
@@ -155,19 +152,36 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ P
   {
     const u32 K = (u32)(tq < 128 ? 127 - tq : 255 - tq) * 0x01010101u;
     const int stepR = kFastThreads / nW, stepG = kFastThreads - stepR * nW;
+    const int nIter = (nR * nW + kFastThreads - 1) / kFastThreads;  // the same trip count for every lane: warp collectives below
+    const int lane = tid & 31;
     int ry = tid / nW, g = tid - ry * nW;
-    for (; ry < nR; ry += stepR, g += stepG) {
-      if (g >= nW) { g -= nW; ++ry; if (ry >= nR) break; }
+    for (int it = 0; it < nIter; ++it, ry += stepR, g += stepG) {
+      if (g >= nW) { g -= nW; ++ry; }
+      u32 alive = 0;
       const int gw = g0 + g;
-      u32 alive = 0x80808080u;
-      if (4 * gw < bLo) alive &= 0xffffffffu << (8 * (bLo - 4 * gw));
-      if (4 * gw + 4 > bHi) alive &= 0xffffffffu >> (8 * (4 * gw + 4 - bHi));
-      const u32* r0 = sImgW + (ry + 3) * SW;
-      alive = tq < 128 ? pass1_word<false>(r0, SW, gw, alive, K) : pass1_word<true>(r0, SW, gw, alive, K);
+      if (ry < nR) {
+        alive = 0x80808080u;
+        if (4 * gw < bLo) alive &= 0xffffffffu << (8 * (bLo - 4 * gw));
+        if (4 * gw + 4 > bHi) alive &= 0xffffffffu >> (8 * (4 * gw + 4 - bHi));
+        const u32* r0 = sImgW + (ry + 3) * SW;
+        alive = tq < 128 ? pass1_word<false>(r0, SW, gw, alive, K) : pass1_word<true>(r0, SW, gw, alive, K);
+      }
+      // warp-aggregated append: one shared-memory atomic per warp and iteration
+      if (__ballot_sync(0xffffffffu, alive != 0) == 0) continue;
+      const int cnt = __popc(alive);
+      int inc = cnt;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
+      }
+      int base = 0;
+      if (lane == 31) base = atomicAdd(&sN, inc);
+      base = __shfl_sync(0xffffffffu, base, 31) + inc - cnt;
       while (alive) {
         const int j = (__ffs((int)alive) - 1) >> 3;
         alive &= alive - 1;
-        sList[atomicAdd(&sN, 1)] = (unsigned short)(((ry + 3) << 8) | (4 * gw + j));
+        sList[base++] = (unsigned short)(((ry + 3) << 8) | (4 * gw + j));
       }
     }
   }
@@ -177,13 +191,13 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ P
   for (int i = tid; i < n; i += kFastThreads) {
     const int e = sList[i], ry = e >> 8, b = e & 255;
     const u8* p = sImg + ry * SB + b;
-    const int v = p[0];
-    int d[16];
-    d[0] = v - p[3 * SB]; d[1] = v - p[3 * SB + 1]; d[2] = v - p[2 * SB + 2]; d[3] = v - p[SB + 3];
-    d[4] = v - p[3]; d[5] = v - p[-SB + 3]; d[6] = v - p[-2 * SB + 2]; d[7] = v - p[-3 * SB + 1];
-    d[8] = v - p[-3 * SB]; d[9] = v - p[-3 * SB - 1]; d[10] = v - p[-2 * SB - 2]; d[11] = v - p[-SB - 3];
-    d[12] = v - p[-3]; d[13] = v - p[SB - 3]; d[14] = v - p[2 * SB - 2]; d[15] = v - p[3 * SB - 1];
-    const int m = arc_value(d);
+    const int vb = (int)p[0] + 256;
+    u32 x[16];
+    x[0] = ring_pack(vb, p[3 * SB]); x[1] = ring_pack(vb, p[3 * SB + 1]); x[2] = ring_pack(vb, p[2 * SB + 2]); x[3] = ring_pack(vb, p[SB + 3]);
+    x[4] = ring_pack(vb, p[3]); x[5] = ring_pack(vb, p[-SB + 3]); x[6] = ring_pack(vb, p[-2 * SB + 2]); x[7] = ring_pack(vb, p[-3 * SB + 1]);
+    x[8] = ring_pack(vb, p[-3 * SB]); x[9] = ring_pack(vb, p[-3 * SB - 1]); x[10] = ring_pack(vb, p[-2 * SB - 2]); x[11] = ring_pack(vb, p[-SB - 3]);
+    x[12] = ring_pack(vb, p[-3]); x[13] = ring_pack(vb, p[SB - 3]); x[14] = ring_pack(vb, p[2 * SB - 2]); x[15] = ring_pack(vb, p[3 * SB - 1]);
+    const int m = arc_value(x);
     if (m > tq) sM[ry * SB + b] = (u8)m;
   }
   __syncthreads();

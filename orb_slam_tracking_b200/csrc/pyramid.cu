@@ -5,53 +5,93 @@
 // reflects the level itself), so levels are stored unpadded and the frame is synthesised only
 // when a caller asks for mvImagePyramid (orbx_get_pyramid_level).
 //
-// HBM-bound: reads P_{l-1}, writes P_l.  Each thread produces 4 adjacent pixels and stores one
-// 32-bit word; the two source rows are read through the read-only path (a warp touches two
-// 154-byte spans per row).  Coefficient tables are computed once on the host with the
-// reference's float/double expressions and kept in L2.
+// HBM-bound: reads P_{l-1}, writes P_l.  One warp per strip of 128 output columns x 32 output rows; a lane
+// owns 4 adjacent output columns, so everything that depends on the column only is lane-constant: the 8
+// horizontal coefficients, and the position of its <= 6 source bytes, which sit in 2 (sometimes 3) aligned
+// words -- one funnel shift pair aligns them and two byte permutes gather the left / right taps of the 4
+// pixels.  Walking down the rows, the horizontally interpolated source row sy+1 of output row dy is kept in
+// registers: at scale 1.2 it is source row sy of row dy+1 five times out of six.  Coefficient tables are
+// computed once on the host with the reference's float/double expressions and kept in L2.
 #include <algorithm>
 
 #include "common.cuh"
 
 namespace orbx {
 
+constexpr int kResizeRows = 32, kResizeWarps = 4;
+
 // tab: xofs[dw] | xcoef[dw] (a0 | a1 << 16) | yofs[dh] | ycoef[dh] (b0 | b1 << 16)
-__global__ void __launch_bounds__(256) k_resize(const __grid_constant__ Params P, int l, const int* __restrict__ tab) {
+__global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_constant__ Params P, int l, const int* __restrict__ tab) {
   const LevelInfo& D = P.lv[l];
   const LevelInfo& S = P.lv[l - 1];
-  const int slot = blockIdx.z;
-  const int dy = blockIdx.y * blockDim.y + threadIdx.y;
-  const int dx0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
-  if (dy >= D.h || dx0 >= D.w) return;
+  const int slot = blockIdx.z, lane = threadIdx.x;
+  const int dy0 = (blockIdx.y * kResizeWarps + threadIdx.y) * kResizeRows;
+  const int dx0 = (blockIdx.x * 32 + lane) * 4;
+  if (dy0 >= D.h) return;
   const u8* __restrict__ src = level_ptr((const u8*)P.pyr, P, slot, l - 1);
   u8* dst = level_ptr(P.pyr, P, slot, l);
   const int* xofs = tab;
   const int* xcoef = tab + D.w;
   const int* yofs = tab + 2 * D.w;
   const int* ycoef = yofs + D.h;
-  int sy = __ldg(yofs + dy);
-  const int bc = __ldg(ycoef + dy);
-  const int b0 = (short)(bc & 0xffff), b1 = bc >> 16;
-  const int sy0 = min(max(sy, 0), S.h - 1), sy1 = min(max(sy + 1, 0), S.h - 1);
-  const u8* r0 = src + (size_t)sy0 * S.pitch;
-  const u8* r1 = src + (size_t)sy1 * S.pitch;
-  u32 packed = 0;
+  // lane constants
+  int a0[4], a1[4], e0[4], e1[4];
+  int sx0 = 0;
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    const int dx = dx0 + k;
-    if (dx < D.w) {
-      const int sx = __ldg(xofs + dx);
-      const int ac = __ldg(xcoef + dx);
-      const int a0 = (short)(ac & 0xffff), a1 = ac >> 16;
-      const int sx1 = min(sx + 1, S.w - 1);
-      const int h0 = __ldg(r0 + sx) * a0 + __ldg(r0 + sx1) * a1;
-      const int h1 = __ldg(r1 + sx) * a0 + __ldg(r1 + sx1) * a1;
-      const int v = (((b0 * (h0 >> 4)) >> 16) + ((b1 * (h1 >> 4)) >> 16) + 2) >> 2;
-      packed |= (u32)(v & 0xff) << (8 * k);
-    }
+    const int dx = min(dx0 + k, D.w - 1);  // columns beyond the level repeat the last one and are not stored
+    const int sx = __ldg(xofs + dx), ac = __ldg(xcoef + dx);
+    if (k == 0) sx0 = sx;
+    a0[k] = (short)(ac & 0xffff); a1[k] = ac >> 16;
+    e0[k] = sx - sx0; e1[k] = min(sx + 1, S.w - 1) - sx0;
   }
-  // pitch is a multiple of 128, so the 4-pixel group is always inside the row allocation
-  *reinterpret_cast<u32*>(dst + (size_t)dy * D.pitch + dx0) = packed;
+  const int A = sx0 & ~3, sh = 8 * (sx0 & 3);
+  const u32 sel0 = (u32)e0[0] | ((u32)e0[1] << 4) | ((u32)e0[2] << 8) | ((u32)e0[3] << 12);
+  const u32 sel1 = (u32)e1[0] | ((u32)e1[1] << 4) | ((u32)e1[2] << 8) | ((u32)e1[3] << 12);
+  const bool need3 = (sx0 & 3) + e1[3] >= 8;
+  const u8* __restrict__ colp = src + A;
+
+  // horizontally interpolated row r, pre-shifted: (S[sx] * a0 + S[sx + 1] * a1) >> 4
+  auto hrow = [&](int r, int (&hs)[4]) {
+    const u32* rp = reinterpret_cast<const u32*>(colp + r * S.pitch);
+    const u32 w0 = __ldg(rp), w1 = __ldg(rp + 1), w2 = need3 ? __ldg(rp + 2) : 0u;
+    const u32 q0 = __funnelshift_r(w0, w1, sh), q1 = __funnelshift_r(w1, w2, sh);
+    const u32 p0 = __byte_perm(q0, q1, sel0), p1 = __byte_perm(q0, q1, sel1);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      hs[k] = (int)(__byte_perm(p0, 0u, 0x4440u + k) * (u32)a0[k] + __byte_perm(p1, 0u, 0x4440u + k) * (u32)a1[k]) >> 4;
+  };
+
+  int hPrev[4] = {0, 0, 0, 0}, rPrev = -1;
+  const int dyEnd = min(dy0 + kResizeRows, D.h);
+  for (int dy = dy0; dy < dyEnd; ++dy) {
+    const int sy = __ldg(yofs + dy), bc = __ldg(ycoef + dy);
+    const int b0 = (short)(bc & 0xffff), b1 = bc >> 16;
+    const int r0 = min(max(sy, 0), S.h - 1), r1 = min(max(sy + 1, 0), S.h - 1);
+    int h0[4], h1[4];
+    if (r0 == rPrev) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) h0[k] = hPrev[k];
+    } else {
+      hrow(r0, h0);
+    }
+    if (r1 == r0) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) h1[k] = h0[k];
+    } else {
+      hrow(r1, h1);
+    }
+    u32 packed = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int v = (((b0 * h0[k]) >> 16) + ((b1 * h1[k]) >> 16) + 2) >> 2;
+      packed |= (u32)(v & 0xff) << (8 * k);
+      hPrev[k] = h1[k];
+    }
+    rPrev = r1;
+    // pitch is a multiple of 128, so the 4-pixel group is always inside the row allocation
+    if (dx0 < D.w) *reinterpret_cast<u32*>(dst + dy * D.pitch + dx0) = packed;
+  }
 }
 
 // Level 0 of each slot from a dense [n][H][W] staging buffer (one DMA from the host for a whole chunk of
@@ -86,8 +126,8 @@ int launch_ingest(const Params& P, const u8* dense, int nSlots, cudaStream_t st)
 int launch_pyramid(const Params& P, const int* const* dTabs, int nSlots, cudaStream_t st) {
   int n = 0;
   for (int l = 1; l < P.nlevels; ++l) {
-    dim3 block(32, 8);
-    dim3 grid((P.lv[l].w + 127) / 128, (P.lv[l].h + 7) / 8, nSlots);
+    dim3 block(32, kResizeWarps);
+    dim3 grid((P.lv[l].w + 127) / 128, (P.lv[l].h + kResizeRows * kResizeWarps - 1) / (kResizeRows * kResizeWarps), nSlots);
     k_resize<<<grid, block, 0, st>>>(P, l, dTabs[l]);
     ++n;
   }
