@@ -169,7 +169,7 @@ def run_reference(args, wl):
 def run_ours(args, wl):
     import ctypes as C
     import torch
-    from orb_slam_tracking_b200 import capi, frontend as fe, synth
+    from orb_slam_tracking_b200 import capi, frontend as fe, shard, synth
     rank, world, local = dist_env()
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
@@ -187,7 +187,10 @@ def run_ours(args, wl):
     E.set_camera(K4, D4)
     S = fe.Stream(E, NNRATIO, True, WINDOW)
     # synthetic frames: 16 distinct pairs per rank, tiled to the batch (every slot is processed independently)
-    imgs = synth.tile_frames(B, W, H, unique_pairs=min(16, B // 2), first_pair=1000 * rank)
+    # the job is a stream of world * B/2 pairs; this rank owns one contiguous block of it (shard.py), no collective
+    pair_lo, pair_hi = shard.shard_pairs(world * (B // 2), world, rank)
+    assert pair_hi - pair_lo == B // 2
+    imgs = synth.tile_frames(B, W, H, unique_pairs=min(16, B // 2), first_pair=pair_lo)
     nbytes_in = imgs.nbytes
     hp = L.orbx_host_alloc(nbytes_in)
     assert hp, "pinned allocation failed"
@@ -224,10 +227,7 @@ def run_ours(args, wl):
             fn()
         capi.check(L.orbx_timer_stop(E._h, C.byref(ms)), E._h)
         barrier()
-        t = torch.tensor([ms.value], device="cuda", dtype=torch.float64)
-        if use_dist:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        return shard.max_over_ranks(ms.value, device="cuda")
 
     capi.check(L.orbx_stream_upload(E._h, hp, B), E._h)
     for _ in range(max(args.warmup, 3)):
