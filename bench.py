@@ -30,7 +30,7 @@ WORKLOADS = {
     "tum": dict(W=640, H=480, nfeatures=1000, ini=20, mn=7, batch=512, desc="synthetic TUM-shape 640x480, 1000 kp"),
     "euroc": dict(W=752, H=480, nfeatures=1200, ini=20, mn=7, batch=512, desc="synthetic EuRoC-shape 752x480, 1200 kp"),
     "kitti": dict(W=1241, H=376, nfeatures=2000, ini=20, mn=7, batch=256, desc="synthetic KITTI-shape 1241x376, 2000 kp"),
-    "uhd": dict(W=3840, H=2160, nfeatures=8000, ini=20, mn=7, batch=16, desc="synthetic 3840x2160, 8000 kp"),
+    "uhd": dict(W=3840, H=2160, nfeatures=8000, ini=20, mn=7, batch=64, desc="synthetic 3840x2160, 8000 kp"),
 }
 METRIC = "ORB frames/s (extract+match, 640x480, 1k kp)"
 UNIT = "frames/s"
@@ -100,6 +100,16 @@ def measured_peak():
     if p.exists():
         return float(json.loads(p.read_text())["hbm_gbs"]), "measured"
     return 6650.0, "fallback"
+
+
+def measured_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the newest committed
+    ncu --set full capture (profiles/*_traffic.json, written by tools/ncu_summary.py); None if absent."""
+    files = sorted((ROOT / "profiles").glob("*_traffic.json"))
+    if not files:
+        return None, None
+    t = json.loads(files[-1].read_text())["bytes_per_launch"].get(kernel)
+    return (int(t) if t else None), files[-1].name
 
 
 def host_threads():
@@ -270,6 +280,8 @@ def run_ours(args, wl):
         dom_ms = float(stage_ms[hbm_stages[dom]])
         n_launch_dom = 7 if dom == "pyramid" else 1
         achieved = ab[dom] * B / (dom_ms * 1e-3) / 1e9
+        dom_kernel = {"pyramid": "k_resize", "fast": "k_fast", "blur": "k_blur"}[dom]
+        traffic, traffic_src = measured_traffic(dom_kernel) if (args.workload == "tum" and B == 512) else (None, None)
         line = {
             "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -287,7 +299,7 @@ def run_ours(args, wl):
                              "bytes_per_frame": ab["frame"]},
             "roofline": {"kernel": {"pyramid": "k_resize (7 launches)", "fast": "k_fast", "blur": "k_blur"}[dom],
                          "bound": "hbm", "achieved": achieved, "peak": peak, "peak_source": how, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "launches_per_step": n_launch_dom,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "launches_per_step": n_launch_dom,
                          "ms_per_step": dom_ms, "algorithmic_bytes_per_step": int(ab[dom] * B)},
         }
         if world == 1 and not args.no_cpu:

@@ -13,6 +13,7 @@ CONFIGS = {
     "euroc": (752, 480, 1200, 20, 7),
     "demo_th0": (752, 480, 2000, 0, 0),      # Settings.yaml as the reference parses it: tie-heavy
     "kitti": (1241, 376, 2000, 20, 7),
+    "uhd": (3840, 2160, 8000, 20, 7),        # config 5: 19 737 FAST cells, level quotas up to 1737
 }
 
 
@@ -146,4 +147,40 @@ def test_constructor_and_argument_errors(fe):
     E = fe.ORBextractor(100, 1.0, 1, 20, 7, 640, 480)  # scale 1 with one level is legal
     assert E.GetLevels() == 1
     assert E(np.zeros((0, 0), np.uint8)) == -1  # empty image -> -1 (:1536)
+    E.close()
+
+
+def test_full_batch_properties(fe, oracle, synth):
+    """BASELINE.json's full size (512 frames of 640x480 / 1000 kp per step) through size-independent properties:
+    slots are independent (a tiled batch gives identical results in every repetition of a frame), re-running is
+    idempotent, every frame hits its quota, and a sample of slots is bit-exact against the oracle."""
+    W, H, nf, B, U = 640, 480, 1000, 512, 4
+    K4, D4 = synth.camera_for(W, H)
+    E = fe.ORBextractor(nf, 1.2, 8, 20, 7, W, H, max_batch=B)
+    bounds = E.set_camera(K4, D4)
+    imgs = synth.tile_frames(B, W, H, unique_pairs=U, first_pair=70)
+    S = fe.Stream(E, 0.9, True, 100)
+    out = S.process(imgs, chunk=128)
+    assert (out["n"] == nf).all()
+    per = 2 * U
+    for k in ("n", "kps", "kps_un", "desc"):
+        a = out[k].reshape((B // per, per) + out[k].shape[1:])
+        assert (a == a[0]).all() if a.dtype.names is None else np.array_equal(a.view(np.uint8), np.broadcast_to(a[:1], a.shape).view(np.uint8)), k
+    for k in ("nmatches", "counters", "matches12"):
+        a = out[k].reshape((B // per, U) + out[k].shape[1:])
+        assert (a == a[0]).all(), k
+    S.upload(imgs)
+    S.run(B)
+    out2 = S.download(B)
+    for k in out:
+        assert np.array_equal(out[k].view(np.uint8), out2[k].view(np.uint8)), k
+    R = oracle.Extractor(nf, 1.2, 8, 20, 7)
+    F = []
+    for i in (B - 2, B - 1):
+        k, d, _ = R(imgs[i])
+        assert np.array_equal(out["kps"][i].view(np.uint8), k.view(np.uint8)) and np.array_equal(out["desc"][i], d)
+        F.append(oracle.Frame(k, d, K4, D4, bounds))
+    rn, rm12, rcnt = oracle.search_for_initialization(F[0], F[1], 0.9, True, 100)
+    assert out["nmatches"][-1] == rn and np.array_equal(out["matches12"][-1, :len(rm12)], rm12)
+    assert np.array_equal(out["counters"][-1], rcnt)
     E.close()

@@ -38,6 +38,18 @@ if rep.exists():
             ("smsp__inst_executed.sum", "warp instr"), ("launch__grid_size", "grid"), ("l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "smem conflicts")]
     idx = [(hdr.index(c), n) for c, n in cols if c in hdr]
     out += ["", "## ncu --set full (one launch each)", "", "| " + " | ".join(n for _, n in idx) + " |", "|" + "---|" * len(idx)]
+    # per-launch DRAM traffic (read + write) of each kernel at the bench batch, for bench.py's roofline.traffic
+    ir, iw, ig = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum"), hdr.index("launch__grid_size")
+    unit = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    per = {}
+    for r in rr[2:]:
+        k = r[idx[0][0]].split("(")[0]
+        b = float(r[ir]) * unit[rr[1][ir]] + float(r[iw]) * unit[rr[1][iw]]
+        g = per.setdefault(k, {})
+        g[r[ig]] = max(g.get(r[ig], 0.0), b)
+    traffic = {k: (sum(g.values()) if k == "k_resize" else max(g.values())) for k, g in per.items()}
+    (P / f"{tag}_traffic.json").write_text(json.dumps({"source": f"ncu --set full, {tag}_full.ncu-rep, dram__bytes_read.sum + dram__bytes_write.sum per launch "
+                                                       "(k_resize: sum over its 7 launches of a step)", "bytes_per_launch": traffic}, indent=1))
     seen = {}
     for r in rr[2:]:
         k = r[idx[0][0]].split("(")[0]
