@@ -138,6 +138,9 @@ int orbx_descriptor_distance_batch(orbx_ctx* ctx, const uint8_t* a, const uint8_
  * SearchForInitialization on the pairs (2k, 2k+1).  orbx_set_camera must have been called. */
 /* copy n_img continuous width x height images (host, ideally pinned) into the batch slots */
 int orbx_stream_upload(orbx_ctx* ctx, const uint8_t* imgs, int n_img);
+/* n_img interleaved 3-channel frames (W*H*3 bytes each); level 0 = Converter::toGray (Utils/Converter.cpp:5-19),
+ * i.e. cv::cvtColor BGR2GRAY (rgb = 0, demo/demo_initialization.cpp:67-68) or RGB2GRAY (rgb != 0), on the device */
+int orbx_stream_upload_color(orbx_ctx* ctx, const uint8_t* imgs, int n_img, int rgb);
 /* enqueue the whole pipeline on the context's stream for the first n_img slots; asynchronous */
 int orbx_stream_run(orbx_ctx* ctx, int n_img, float nnratio, int check_orientation, int window_size);
 /* wait, then copy results to the host.  Any pointer may be NULL.  kps/kps_un/desc: blocks of

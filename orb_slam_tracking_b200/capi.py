@@ -55,6 +55,7 @@ SIGNATURES = {
     "orbx_descriptor_distance": (ci, [vp, vp]),
     "orbx_descriptor_distance_batch": (ci, [vp, vp, vp, ci, vp]),
     "orbx_stream_upload": (ci, [vp, vp, ci]),
+    "orbx_stream_upload_color": (ci, [vp, vp, ci, ci]),
     "orbx_stream_run": (ci, [vp, ci, cf, ci, ci]),
     "orbx_stream_download": (ci, [vp, ci, vp, vp, vp, ci, vp, vp, vp, vp]),
     "orbx_stream_process": (ci, [vp, vp, ci, cf, ci, ci, ci, vp, vp, vp, ci, vp, vp, vp, vp]),

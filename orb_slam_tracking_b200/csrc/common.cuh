@@ -137,6 +137,7 @@ __device__ __forceinline__ int reflect101(int i, int len) {
 
 // launchers (one per .cu file); all enqueue on `st` and return the number of kernel launches
 int launch_ingest(const Params& P, const u8* dense, int nSlots, cudaStream_t st);
+int launch_ingest_color(const Params& P, const u8* dense, int rgb, int nSlots, cudaStream_t st);
 int launch_pyramid(const Params& P, const int* const* dTabs, int nSlots, cudaStream_t st);
 int launch_blur(const Params& P, int nSlots, cudaStream_t st);
 int launch_fast(const Params& P, const TmaMaps& M, int nSlots, cudaStream_t st);

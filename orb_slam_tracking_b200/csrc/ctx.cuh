@@ -35,6 +35,7 @@ struct orbx_ctx {
   cudaStream_t sH2D, sD2H;         // copy streams of the pipelined host path (orbx_stream_process)
   std::vector<cudaEvent_t> evChunk; // 2 per chunk: images landed, results ready
   orbx::u8* dIngest;               // dense [maxBatch][H][W] staging of uploaded frames
+  orbx::u8* dIngestColor;          // dense [maxBatch][H][W][3], allocated on the first colour upload
   int* hStatus;                    // pinned [maxBatch]
   std::vector<void*> allocs;       // every cudaMalloc, freed in orbx_destroy
   std::vector<int*> dResizeTabs;   // per level (entry 0 unused)

@@ -165,7 +165,7 @@ extern "C" orbx_ctx* orbx_create(int device, int width, int height, int nfeature
                                  int ini_th_fast, int min_th_fast, int max_batch, int* status) {
   orbx_ctx* c = new (std::nothrow) orbx_ctx();
   if (!c) { if (status) *status = ORBX_ERR_ARG; return nullptr; }
-  c->stream = nullptr; c->sH2D = c->sD2H = nullptr; c->dIngest = nullptr; c->hStatus = nullptr; c->hTabPtrs = nullptr; c->launches = 0; c->cameraSet = 0; c->lastBatch = 0;
+  c->stream = nullptr; c->sH2D = c->sD2H = nullptr; c->dIngest = nullptr; c->dIngestColor = nullptr; c->hStatus = nullptr; c->hTabPtrs = nullptr; c->launches = 0; c->cameraSet = 0; c->lastBatch = 0;
   c->stageTiming = 0; c->evStart = c->evStop = nullptr;
   for (int i = 0; i < 10; ++i) c->evStage[i] = nullptr;
   std::memset(c->stageMs, 0, sizeof(c->stageMs));

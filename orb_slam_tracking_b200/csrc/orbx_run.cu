@@ -227,6 +227,23 @@ extern "C" int orbx_stream_upload(orbx_ctx* c, const uint8_t* imgs, int n_img) {
   return ORBX_OK;
 }
 
+// 3-channel interleaved frames (BGR, or RGB with rgb != 0): Converter::toGray on the device, fused into the ingest
+extern "C" int orbx_stream_upload_color(orbx_ctx* c, const uint8_t* imgs, int n_img, int rgb) {
+  if (!c || !imgs || n_img < 1 || n_img > c->P.maxBatch) return ORBX_ERR_ARG;
+  const Params& P = c->P;
+  CU(c, cudaSetDevice(c->device));
+  if (!c->dIngestColor) {
+    void* q = nullptr;
+    CU(c, cudaMalloc(&q, (size_t)P.maxBatch * P.W * P.H * 3));
+    c->allocs.push_back(q);
+    c->dIngestColor = (u8*)q;
+  }
+  CU(c, cudaMemcpyAsync(c->dIngestColor, imgs, (size_t)n_img * P.W * P.H * 3, cudaMemcpyHostToDevice, c->stream));
+  launch_ingest_color(P, c->dIngestColor, rgb, n_img, c->stream);
+  CU(c, cudaGetLastError());
+  return ORBX_OK;
+}
+
 extern "C" int orbx_stream_run(orbx_ctx* c, int n_img, float nnratio, int check_orientation, int window_size) {
   if (!c || n_img < 1 || n_img > c->P.maxBatch) return ORBX_ERR_ARG;
   if (!c->cameraSet) return ORBX_ERR_STATE;

@@ -116,6 +116,48 @@ __global__ void __launch_bounds__(256) k_ingest(const __grid_constant__ Params P
   }
 }
 
+// Converter::toGray (Utils/Converter.cpp:5-19) / cv::cvtColor(BGR2GRAY | RGB2GRAY) (demo/demo_initialization.cpp:67-68)
+// fused into the ingest: level 0 = (3735 B + 19235 G + 9798 R + 16384) >> 15 (OpenCV's 8U fixed point)
+// from a dense interleaved [n][H][W][3] staging buffer.  One thread per 4 output pixels (three 32-bit loads).
+__global__ void __launch_bounds__(256) k_ingest_color(const __grid_constant__ Params P, const u8* __restrict__ dense, int rgb) {
+  const int slot = blockIdx.y;
+  const LevelInfo& L = P.lv[0];
+  const u8* __restrict__ src = dense + (size_t)slot * P.W * P.H * 3;
+  u8* dst = level_ptr(P.pyr, P, slot, 0);
+  const int c0 = rgb ? 9798 : 3735, c2 = rgb ? 3735 : 9798;  // weight of channel 0 / channel 2
+  const int wq = (P.W + 3) >> 2, total = wq * P.H;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int y = i / wq, x = (i - y * wq) * 4;
+    const u8* s = src + ((size_t)y * P.W + x) * 3;
+    u32 out = 0;
+    if (x + 3 < P.W && ((reinterpret_cast<size_t>(s) & 3) == 0)) {
+      const u32 w0 = __ldg(reinterpret_cast<const u32*>(s)), w1 = __ldg(reinterpret_cast<const u32*>(s) + 1),
+                w2 = __ldg(reinterpret_cast<const u32*>(s) + 2);
+      // bytes: w0 = b0 g0 r0 b1 | w1 = g1 r1 b2 g2 | w2 = r2 b3 g3 r3
+      const int g0 = (c0 * (int)(w0 & 255) + 19235 * (int)((w0 >> 8) & 255) + c2 * (int)((w0 >> 16) & 255) + 16384) >> 15;
+      const int g1 = (c0 * (int)(w0 >> 24) + 19235 * (int)(w1 & 255) + c2 * (int)((w1 >> 8) & 255) + 16384) >> 15;
+      const int g2 = (c0 * (int)((w1 >> 16) & 255) + 19235 * (int)(w1 >> 24) + c2 * (int)(w2 & 255) + 16384) >> 15;
+      const int g3 = (c0 * (int)((w2 >> 8) & 255) + 19235 * (int)((w2 >> 16) & 255) + c2 * (int)(w2 >> 24) + 16384) >> 15;
+      out = (u32)g0 | ((u32)g1 << 8) | ((u32)g2 << 16) | ((u32)g3 << 24);
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (x + k < P.W) {
+          const int g = (c0 * (int)__ldg(s + 3 * k) + 19235 * (int)__ldg(s + 3 * k + 1) + c2 * (int)__ldg(s + 3 * k + 2) + 16384) >> 15;
+          out |= (u32)g << (8 * k);
+        }
+    }
+    *reinterpret_cast<u32*>(dst + (size_t)y * L.pitch + x) = out;  // pitch is a multiple of 128: the word is inside the row
+  }
+}
+
+int launch_ingest_color(const Params& P, const u8* dense, int rgb, int nSlots, cudaStream_t st) {
+  const int work = ((P.W + 3) >> 2) * P.H;
+  dim3 grid(std::min((work + 255) / 256, 128), nSlots);
+  k_ingest_color<<<grid, 256, 0, st>>>(P, dense, rgb);
+  return 1;
+}
+
 int launch_ingest(const Params& P, const u8* dense, int nSlots, cudaStream_t st) {
   const int work = (P.W & 15) == 0 ? (P.W >> 4) * P.H : P.W * P.H;
   dim3 grid(std::min((work + 255) / 256, 64), nSlots);

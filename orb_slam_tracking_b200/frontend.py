@@ -199,6 +199,13 @@ class Stream:
         check(lib().orbx_stream_upload(self.ex._h, ptr(imgs), imgs.shape[0]), self.ex._h)
         return imgs.shape[0]
 
+    def upload_color(self, imgs, rgb=False):
+        """[n, H, W, 3] interleaved BGR (or RGB) frames; Converter::toGray runs on the device."""
+        imgs = np.ascontiguousarray(imgs, np.uint8)
+        assert imgs.shape[1:] == (self.ex.height, self.ex.width, 3)
+        check(lib().orbx_stream_upload_color(self.ex._h, ptr(imgs), imgs.shape[0], int(rgb)), self.ex._h)
+        return imgs.shape[0]
+
     def run(self, n):
         check(lib().orbx_stream_run(self.ex._h, n, self.nnratio, int(self.checkOri), self.window), self.ex._h)
 

@@ -62,3 +62,29 @@ def test_cuda_matches_reference_outputs(name):
             gn, gm = c.matches(a, w)
             assert int(out["nmatches"][a // 2]) == gn and np.array_equal(out["matches12"][a // 2, :len(gm)], gm)
     E.close()
+
+
+def test_color_ingest_matches_cvtcolor():
+    """Row N1 (SURVEY.md 8f): Converter::toGray / cv::cvtColor on the device, fused into the ingest, against the
+    real OpenCV wheel (BGR2GRAY and RGB2GRAY), odd width included; the extraction that follows equals the one
+    on the host-converted gray image."""
+    import cv2
+    from orb_slam_tracking_b200 import frontend as fe
+    rng = np.random.default_rng(11)
+    for W, H in ((640, 480), (333, 250)):
+        E = fe.ORBextractor(500, 1.2, 8, 20, 7, W, H, max_batch=2)
+        E.set_camera(np.array([500, 500, W / 2, H / 2], np.float32), np.zeros(4, np.float32))
+        bgr = rng.integers(0, 256, (2, H, W, 3), dtype=np.uint8)
+        bgr[1] = cv2.GaussianBlur(bgr[1], (9, 9), 3)
+        S = fe.Stream(E, 0.9, True, 100)
+        for rgb, code in ((False, cv2.COLOR_BGR2GRAY), (True, cv2.COLOR_RGB2GRAY)):
+            S.upload_color(bgr, rgb=rgb)
+            S.run(2)
+            out = S.download(2)
+            for i in range(2):
+                gray = cv2.cvtColor(bgr[i], code)
+                assert np.array_equal(E.pyramid_level(0, slot=i), gray), (W, rgb, i)
+                k, d, _ = E(gray)
+                n = int(out["n"][i])
+                assert n == len(k) and same_records(out["kps"][i, :n], k) and np.array_equal(out["desc"][i, :n], d)
+        E.close()
