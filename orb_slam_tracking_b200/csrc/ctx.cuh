@@ -32,6 +32,7 @@ struct orbx_ctx {
   orbx::TmaMaps tma;               // per-level tensor maps over P.pyr (k_fast tile staging)
   int device;
   cudaStream_t stream;
+  cudaStream_t sAlt;               // second compute stream: odd chunks of orbx_stream_process
   cudaStream_t sH2D, sD2H;         // copy streams of the pipelined host path (orbx_stream_process)
   std::vector<cudaEvent_t> evChunk; // 2 per chunk: images landed, results ready
   orbx::u8* dIngest;               // dense [maxBatch][H][W] staging of uploaded frames

@@ -84,6 +84,7 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   c->device = device;
   CU(c, cudaSetDevice(device));
   CU(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CU(c, cudaStreamCreateWithFlags(&c->sAlt, cudaStreamNonBlocking));
   CU(c, cudaStreamCreateWithFlags(&c->sH2D, cudaStreamNonBlocking));
   CU(c, cudaStreamCreateWithFlags(&c->sD2H, cudaStreamNonBlocking));
   CU(c, cudaHostAlloc((void**)&c->hStatus, (size_t)maxBatch * sizeof(int), cudaHostAllocDefault));
@@ -165,7 +166,7 @@ extern "C" orbx_ctx* orbx_create(int device, int width, int height, int nfeature
                                  int ini_th_fast, int min_th_fast, int max_batch, int* status) {
   orbx_ctx* c = new (std::nothrow) orbx_ctx();
   if (!c) { if (status) *status = ORBX_ERR_ARG; return nullptr; }
-  c->stream = nullptr; c->sH2D = c->sD2H = nullptr; c->dIngest = nullptr; c->dIngestColor = nullptr; c->hStatus = nullptr; c->hTabPtrs = nullptr; c->launches = 0; c->cameraSet = 0; c->lastBatch = 0;
+  c->stream = nullptr; c->sH2D = c->sD2H = c->sAlt = nullptr; c->dIngest = nullptr; c->dIngestColor = nullptr; c->hStatus = nullptr; c->hTabPtrs = nullptr; c->launches = 0; c->cameraSet = 0; c->lastBatch = 0;
   c->stageTiming = 0; c->evStart = c->evStop = nullptr;
   for (int i = 0; i < 10; ++i) c->evStage[i] = nullptr;
   std::memset(c->stageMs, 0, sizeof(c->stageMs));
@@ -188,6 +189,7 @@ extern "C" void orbx_destroy(orbx_ctx* c) {
   for (int i = 0; i < 10; ++i) if (c->evStage[i]) cudaEventDestroy(c->evStage[i]);
   for (cudaEvent_t e : c->evChunk) cudaEventDestroy(e);
   if (c->hStatus) cudaFreeHost(c->hStatus);
+  if (c->sAlt) cudaStreamDestroy(c->sAlt);
   if (c->sH2D) cudaStreamDestroy(c->sH2D);
   if (c->sD2H) cudaStreamDestroy(c->sD2H);
   if (c->stream) cudaStreamDestroy(c->stream);

@@ -36,8 +36,8 @@ Params shifted(const orbx_ctx* c, int s0) {
 }
 
 // Enqueues extraction for the n slots of P (level 0 of each slot must already hold the image).
-int enqueue_extract(orbx_ctx* c, const Params& P, int n, int lap0, int lap1) {
-  cudaStream_t st = c->stream;
+int enqueue_extract(orbx_ctx* c, const Params& P, int n, int lap0, int lap1, cudaStream_t st = nullptr) {
+  if (!st) st = c->stream;
   CU(c, cudaMemsetAsync(P.candCount, 0, (size_t)n * kMaxLevels * sizeof(u32), st));
   CU(c, cudaMemsetAsync(P.status, 0, (size_t)n * sizeof(int), st));
   mark(c, 0);
@@ -57,8 +57,10 @@ int enqueue_extract(orbx_ctx* c, const Params& P, int n, int lap0, int lap1) {
 }
 
 // glue + SearchForInitialization over the pairs (2k, 2k+1) of the n slots of P; pair0 = first pair index
-int enqueue_glue_match(orbx_ctx* c, const Params& P, int n, int pair0, float nnratio, int checkOri, int window) {
-  c->launches += launch_glue(P, n, c->stream);
+int enqueue_glue_match(orbx_ctx* c, const Params& P, int n, int pair0, float nnratio, int checkOri, int window,
+                       cudaStream_t st = nullptr) {
+  if (!st) st = c->stream;
+  c->launches += launch_glue(P, n, st);
   mark(c, 6);
   MatchArgs A;
   A.keysUn = P.keysUn; A.desc = P.outDesc; A.gridOff = P.gridOff; A.gridIdx = P.gridIdx; A.n = P.outN;
@@ -67,7 +69,7 @@ int enqueue_glue_match(orbx_ctx* c, const Params& P, int n, int pair0, float nnr
   A.nmatches = c->dNMatches + pair0;
   A.counters = c->dCounters + (size_t)pair0 * 3;
   A.scratch = c->dMatchScratch + (size_t)pair0 * 3 * P.kpStride;
-  c->launches += launch_match(P, A, n / 2, 2, nnratio, checkOri, window, c->stream);
+  c->launches += launch_match(P, A, n / 2, 2, nnratio, checkOri, window, st);
   mark(c, 7);
   CU(c, cudaGetLastError());
   return ORBX_OK;
@@ -318,7 +320,10 @@ extern "C" int orbx_stream_process(orbx_ctx* c, const uint8_t* imgs, int n_img, 
   CU(c, cudaSetDevice(c->device));
   if (chunk <= 0) chunk = 128;
   chunk = std::max(2, chunk & ~1);
-  const int nChunks = (n_img + chunk - 1) / chunk;
+  // chunk boundaries: a short first chunk (chunk / 4, then chunk / 2) so that the kernels start early, then `chunk`
+  std::vector<int> cut(1, 0);
+  for (int sz = std::max(2, (chunk / 4) & ~1); cut.back() < n_img; sz = std::min(chunk, 2 * sz)) cut.push_back(std::min(n_img, cut.back() + sz));
+  const int nChunks = (int)cut.size() - 1;
   while ((int)c->evChunk.size() < 2 * nChunks) {
     cudaEvent_t e;
     CU(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -332,16 +337,19 @@ extern "C" int orbx_stream_process(orbx_ctx* c, const uint8_t* imgs, int n_img, 
   c->launches = 0;
   int rc = ORBX_OK;
   for (int k = 0; k < nChunks && rc == ORBX_OK; ++k) {
-    const int s0 = k * chunk, n = std::min(chunk, n_img - s0), p0 = s0 / 2, np = n / 2;
+    const int s0 = cut[k], n = cut[k + 1] - s0, p0 = s0 / 2, np = n / 2;
     cudaEvent_t evIn = c->evChunk[2 * k], evOut = c->evChunk[2 * k + 1];
     CU(c, cudaMemcpyAsync(c->dIngest + s0 * imgBytes, imgs + s0 * imgBytes, n * imgBytes, cudaMemcpyHostToDevice, c->sH2D));
     CU(c, cudaEventRecord(evIn, c->sH2D));
-    CU(c, cudaStreamWaitEvent(c->stream, evIn, 0));
+    // consecutive chunks alternate between two compute streams: the latency-bound tail of a chunk (quadtree,
+    // matcher: few CTAs) overlaps the bandwidth-heavy head of the next one; chunks touch disjoint slots
+    cudaStream_t sc = (k & 1) ? c->sAlt : c->stream;
+    CU(c, cudaStreamWaitEvent(sc, evIn, 0));
     const Params Q = shifted(c, s0);
-    c->launches += launch_ingest(Q, c->dIngest + s0 * imgBytes, n, c->stream);
-    if ((rc = enqueue_extract(c, Q, n, 0, 0))) break;
-    if ((rc = enqueue_glue_match(c, Q, n, p0, nnratio, check_orientation, window_size))) break;
-    CU(c, cudaEventRecord(evOut, c->stream));
+    c->launches += launch_ingest(Q, c->dIngest + s0 * imgBytes, n, sc);
+    if ((rc = enqueue_extract(c, Q, n, 0, 0, sc))) break;
+    if ((rc = enqueue_glue_match(c, Q, n, p0, nnratio, check_orientation, window_size, sc))) break;
+    CU(c, cudaEventRecord(evOut, sc));
     cudaStream_t sd = c->sD2H;
     CU(c, cudaStreamWaitEvent(sd, evOut, 0));
     CU(c, cudaMemcpyAsync(c->hStatus + s0, Q.status, n * sizeof(int), cudaMemcpyDeviceToHost, sd));
@@ -366,6 +374,7 @@ extern "C" int orbx_stream_process(orbx_ctx* c, const uint8_t* imgs, int n_img, 
   c->stageTiming = timing;
   cudaStreamSynchronize(c->sD2H);
   cudaStreamSynchronize(c->stream);
+  cudaStreamSynchronize(c->sAlt);
   cudaStreamSynchronize(c->sH2D);
   if (rc) return rc;
   CU(c, cudaGetLastError());
