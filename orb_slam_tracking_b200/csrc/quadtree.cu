@@ -18,14 +18,12 @@
 
 namespace orbx {
 
-constexpr int QT = 512;
+constexpr int QT = 64;   // small CTAs: the one-thread std::sort replay of a CTA overlaps the parallel phases of its SM neighbours
 
-constexpr int kSortSmem = 2048;  // sort elements kept in shared memory (a generation rarely has more divisible nodes)
 
 struct QtS {
   int nNodes, size, gen0, gen1, nS, nProc, nToExpand, cut;
   int part[QT];
-  u64 srt[kSortSmem];
 };
 
 // (count, UL.x, node id) in one word: std::sort's comparator (:684-696) sees only (count, UL.x)
@@ -62,8 +60,9 @@ __device__ __forceinline__ int quadrant(const short4 b, const u32 xy) {
   return (x >= midx ? 1 : 0) + (y >= midy ? 2 : 0);  // n1, n2, n3, n4
 }
 
-__global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params P) {
+__global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params P, int sortCap) {
   __shared__ QtS S;
+  extern __shared__ __align__(8) u64 sSrt[];  // sortCap packed sort words (launch_quadtree sizes it from the largest quota)
   const int l = blockIdx.x, slot = blockIdx.y, tid = threadIdx.x;
   const LevelInfo& L = P.lv[l];
   const int N = L.quota;
@@ -127,12 +126,12 @@ __global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params 
       nS = cta_scan(scan, G, S.part);
       // the sort runs in one thread (its tie order is the algorithm's, see stdsort_emul.cuh): keep its
       // elements in shared memory as single 64-bit words, count << 40 | UL.x << 24 | node id
-      const bool inSmem = nS <= kSortSmem;
+      const bool inSmem = nS <= sortCap;
       for (int j = tid; j < G; j += QT) {
         const int node = gen0 + j, c = nCount[node];
         if (c > 1) {
           if (inSmem) {
-            S.srt[scan[j] - 1] = ((u64)(u32)c << 40) | ((u64)(u32)(int)nBox[node].x << 24) | (u64)(u32)node;
+            sSrt[scan[j] - 1] = ((u64)(u32)c << 40) | ((u64)(u32)(int)nBox[node].x << 24) | (u64)(u32)node;
           } else {
             SortElem e;
             e.key = ((u64)(u32)c << 32) | (u64)(u32)(int)nBox[node].x;
@@ -143,11 +142,11 @@ __global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params 
       }
       __syncthreads();
       if (tid == 0) {
-        if (inSmem) stdsort_emul_t(S.srt, (long)nS, PackedLess());
+        if (inSmem) stdsort_emul_t(sSrt, (long)nS, PackedLess());
         else stdsort_emul(srt, nS);
       }
       __syncthreads();
-      for (int s = tid; s < nS; s += QT) list[s] = inSmem ? (int)(S.srt[nS - 1 - s] & 0xffffffu) : (int)srt[nS - 1 - s].id;
+      for (int s = tid; s < nS; s += QT) list[s] = inSmem ? (int)(sSrt[nS - 1 - s] & 0xffffffu) : (int)srt[nS - 1 - s].id;
     }
     __syncthreads();
     if (nS == 0) break;  // nothing divisible: |L| == prevSize
@@ -247,7 +246,11 @@ __global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params 
 
 int launch_quadtree(const Params& P, int nSlots, cudaStream_t st) {
   dim3 grid(P.nlevels, nSlots);
-  k_quadtree<<<grid, QT, 0, st>>>(P);
+  // a generation has at most ~quota divisible nodes; beyond sortCap the kernel sorts in global memory
+  int q = 0;
+  for (int l = 0; l < P.nlevels; ++l) q = q > P.lv[l].quota ? q : P.lv[l].quota;
+  const int sortCap = 2 * q < 256 ? 256 : (2 * q > 4096 ? 4096 : 2 * q);
+  k_quadtree<<<grid, QT, (size_t)sortCap * sizeof(u64), st>>>(P, sortCap);
   return 1;
 }
 
