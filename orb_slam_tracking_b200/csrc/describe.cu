@@ -48,7 +48,8 @@ constexpr int kPatchRows = 37, kPatchWords = 10;  // blurred patch [-18, 18]^2 s
 //   3. steered BRIEF, one warp per keypoint: the 37 x 37 blurred patch is staged into shared memory with
 //      coalesced word loads, then lane = descriptor byte gathers its 16 samples from shared memory.
 __global__ void __launch_bounds__(kWarpsPerCta * 32) k_describe(const __grid_constant__ Params P) {
-  __shared__ char4 sPat[256];  // [i * 32 + byte]: conflict-free for lane = byte
+  __shared__ float4 sPat[256];  // pattern pair (x0, y0, x1, y1) as floats, [i * 32 + byte]: conflict-free for lane = byte
+  __shared__ u32 sDD[32];       // per patch row: 0x80808080 | umax[|v|] * 0x01010101 (byte-wise column limit of IC_Angle)
   __shared__ u32 sPatch[kWarpsPerCta][kPatchRows * kPatchWords];
   __shared__ float sAngle[kKpPerCta], sCos[kKpPerCta], sSin[kKpPerCta];
   __shared__ u32 sXY[kKpPerCta];
@@ -57,7 +58,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) k_describe(const __grid_con
   {
     const int b = tid & 31, i = tid >> 5;  // 256 threads: pair (b, i) -> pattern row 8b + i
     const signed char* p = c_pattern + 4 * (8 * b + i);
-    sPat[i * 32 + b] = make_char4(p[0], p[1], p[2], p[3]);
+    sPat[i * 32 + b] = make_float4((float)p[0], (float)p[1], (float)p[2], (float)p[3]);
+    if (tid < 31) sDD[tid] = 0x80808080u | ((u32)P.umax[tid < kHalfPatch ? kHalfPatch - tid : tid - kHalfPatch] * 0x01010101u);
   }
   const int slot = blockIdx.y;
   const int gBase = blockIdx.x * kKpPerCta;
@@ -88,7 +90,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) k_describe(const __grid_con
     // and only the row's half-width d = umax[|v|] changes: byte j counts iff |u_j| <= d
     const int lr = lane / 9, w = lane - 9 * lr;
     const int u0 = xa + 4 * w - x;
-    const int a0 = abs(u0), a1 = abs(u0 + 1), a2 = abs(u0 + 2), a3 = abs(u0 + 3);
+    // |u_j| per byte (< 128); byte j of a row counts iff umax >= |u_j|: bit 7 of (0x80 | umax) - |u_j| survives
+    const u32 apk = (u32)abs(u0) | ((u32)abs(u0 + 1) << 8) | ((u32)abs(u0 + 2) << 16) | ((u32)abs(u0 + 3) << 24);
     const int upk = (u0 & 255) | (((u0 + 1) & 255) << 8) | (((u0 + 2) & 255) << 16) | (((u0 + 3) & 255) << 24);  // s8 x 4
     if (lane < 27) {
 #pragma unroll
@@ -96,9 +99,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) k_describe(const __grid_con
         const int r = rb + lr;
         if (r < 31) {
           const int v = r - kHalfPatch;
-          const int d = P.umax[v < 0 ? -v : v];
           u32 word = __ldg(reinterpret_cast<const u32*>(img + (size_t)r * L.pitch) + w);
-          word &= (d >= a0 ? 0xffu : 0u) | (d >= a1 ? 0xff00u : 0u) | (d >= a2 ? 0xff0000u : 0u) | (d >= a3 ? 0xff000000u : 0u);
+          word &= (((sDD[r] - apk) & 0x80808080u) >> 7) * 255u;
           int su;
           asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(su) : "r"(word), "r"(upk), "r"(0));
           m10 += su;
@@ -155,8 +157,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) k_describe(const __grid_con
     u32 val = 0;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const char4 q = sPat[i * 32 + lane];
-      const float x0 = (float)q.x, y0 = (float)q.y, x1 = (float)q.z, y1 = (float)q.w;
+      const float4 q = sPat[i * 32 + lane];
+      const float x0 = q.x, y0 = q.y, x1 = q.z, y1 = q.w;
       const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, si), __fmul_rn(y0, co)));
       const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, co), __fmul_rn(y0, si)));
       const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, si), __fmul_rn(y1, co)));

@@ -5,7 +5,7 @@
 // reflects the level itself), so levels are stored unpadded and the frame is synthesised only
 // when a caller asks for mvImagePyramid (orbx_get_pyramid_level).
 //
-// HBM-bound: reads P_{l-1}, writes P_l.  One warp per strip of 128 output columns x 32 output rows; a lane
+// HBM-bound: reads P_{l-1}, writes P_l.  One warp per strip of 128 output columns x 16 output rows; a lane
 // owns 4 adjacent output columns, so everything that depends on the column only is lane-constant: the 8
 // horizontal coefficients, and the position of its <= 6 source bytes, which sit in 2 (sometimes 3) aligned
 // words -- one funnel shift pair aligns them and two byte permutes gather the left / right taps of the 4
@@ -13,19 +13,20 @@
 // registers: at scale 1.2 it is source row sy of row dy+1 five times out of six.  Coefficient tables are
 // computed once on the host with the reference's float/double expressions and kept in L2.
 #include <algorithm>
+#include <cstdlib>
 
 #include "common.cuh"
 
 namespace orbx {
 
-constexpr int kResizeRows = 32, kResizeWarps = 4;
+constexpr int kResizeRows = 16, kResizeWarps = 4;
 
 // tab: xofs[dw] | xcoef[dw] (a0 | a1 << 16) | yofs[dh] | ycoef[dh] (b0 | b1 << 16)
-__global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_constant__ Params P, int l, const int* __restrict__ tab) {
+__global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_constant__ Params P, int l, const int* __restrict__ tab, int rows) {
   const LevelInfo& D = P.lv[l];
   const LevelInfo& S = P.lv[l - 1];
   const int slot = blockIdx.z, lane = threadIdx.x;
-  const int dy0 = (blockIdx.y * kResizeWarps + threadIdx.y) * kResizeRows;
+  const int dy0 = (blockIdx.y * kResizeWarps + threadIdx.y) * rows;
   const int dx0 = (blockIdx.x * 32 + lane) * 4;
   if (dy0 >= D.h) return;
   const u8* __restrict__ src = level_ptr((const u8*)P.pyr, P, slot, l - 1);
@@ -63,7 +64,7 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
   };
 
   int hPrev[4] = {0, 0, 0, 0}, rPrev = -1;
-  const int dyEnd = min(dy0 + kResizeRows, D.h);
+  const int dyEnd = min(dy0 + rows, D.h);
   for (int dy = dy0; dy < dyEnd; ++dy) {
     const int sy = __ldg(yofs + dy), bc = __ldg(ycoef + dy);
     const int b0 = (short)(bc & 0xffff), b1 = bc >> 16;
@@ -169,8 +170,10 @@ int launch_pyramid(const Params& P, const int* const* dTabs, int nSlots, cudaStr
   int n = 0;
   for (int l = 1; l < P.nlevels; ++l) {
     dim3 block(32, kResizeWarps);
-    dim3 grid((P.lv[l].w + 127) / 128, (P.lv[l].h + kResizeRows * kResizeWarps - 1) / (kResizeRows * kResizeWarps), nSlots);
-    k_resize<<<grid, block, 0, st>>>(P, l, dTabs[l]);
+    static const int rowsEnv = std::getenv("ORBX_RESIZE_ROWS") ? std::atoi(std::getenv("ORBX_RESIZE_ROWS")) : 0;
+    const int rows = rowsEnv > 0 ? rowsEnv : kResizeRows;
+    dim3 grid((P.lv[l].w + 127) / 128, (P.lv[l].h + rows * kResizeWarps - 1) / (rows * kResizeWarps), nSlots);
+    k_resize<<<grid, block, 0, st>>>(P, l, dTabs[l], rows);
     ++n;
   }
   return n;
