@@ -43,11 +43,23 @@ int enqueue_extract(orbx_ctx* c, const Params& P, int n, int lap0, int lap1, cud
   mark(c, 0);
   c->launches += launch_pyramid(P, c->hTabPtrs, n, st);
   mark(c, 1);
+  // the blur only needs the pyramid: it runs on a side stream next to the quadtree (latency-bound, a third of the
+  // issue slots; the blur is issue-bound, so they share the SMs well) and joins before the descriptors.  With per-stage timing on,
+  // everything stays on one stream so that the stage events bracket one kernel each.
+  const int side = (st == c->sAlt) ? 1 : 0;
+  const bool fork = !c->stageTiming;
   c->launches += launch_fast(P, c->tma, n, st);
   mark(c, 2);
+  if (fork) {  // forked AFTER FAST (itself issue-bound): the blur then shares the SMs with the quadtree only
+    CU(c, cudaEventRecord(c->evFork[side], st));
+    CU(c, cudaStreamWaitEvent(c->sSide[side], c->evFork[side], 0));
+    c->launches += launch_blur(P, n, c->sSide[side]);
+    CU(c, cudaEventRecord(c->evJoin[side], c->sSide[side]));
+  }
   c->launches += launch_quadtree(P, n, st);
   mark(c, 3);
-  c->launches += launch_blur(P, n, st);
+  if (fork) CU(c, cudaStreamWaitEvent(st, c->evJoin[side], 0));
+  else c->launches += launch_blur(P, n, st);
   mark(c, 4);
   c->launches += launch_describe(P, n, lap0, lap1, st);
   mark(c, 5);
@@ -375,6 +387,8 @@ extern "C" int orbx_stream_process(orbx_ctx* c, const uint8_t* imgs, int n_img, 
   cudaStreamSynchronize(c->sD2H);
   cudaStreamSynchronize(c->stream);
   cudaStreamSynchronize(c->sAlt);
+  cudaStreamSynchronize(c->sSide[0]);
+  cudaStreamSynchronize(c->sSide[1]);
   cudaStreamSynchronize(c->sH2D);
   if (rc) return rc;
   CU(c, cudaGetLastError());
