@@ -34,7 +34,7 @@ struct orbx_ctx {
   cudaStream_t stream;
   cudaStream_t sAlt;               // second compute stream: odd chunks of orbx_stream_process
   cudaStream_t sSide[2];           // blur runs here, beside FAST + quadtree of stream / sAlt
-  cudaEvent_t evFork[2], evJoin[2];
+  cudaEvent_t evFork[2], evJoin[2], evHalf;
   cudaStream_t sH2D, sD2H;         // copy streams of the pipelined host path (orbx_stream_process)
   std::vector<cudaEvent_t> evChunk; // 2 per chunk: images landed, results ready
   orbx::u8* dIngest;               // dense [maxBatch][H][W] staging of uploaded frames

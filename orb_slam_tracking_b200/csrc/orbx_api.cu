@@ -85,6 +85,7 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   CU(c, cudaSetDevice(device));
   CU(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CU(c, cudaStreamCreateWithFlags(&c->sAlt, cudaStreamNonBlocking));
+  CU(c, cudaEventCreateWithFlags(&c->evHalf, cudaEventDisableTiming));
   for (int i = 0; i < 2; ++i) {
     CU(c, cudaStreamCreateWithFlags(&c->sSide[i], cudaStreamNonBlocking));
     CU(c, cudaEventCreateWithFlags(&c->evFork[i], cudaEventDisableTiming));
@@ -172,7 +173,8 @@ extern "C" orbx_ctx* orbx_create(int device, int width, int height, int nfeature
   orbx_ctx* c = new (std::nothrow) orbx_ctx();
   if (!c) { if (status) *status = ORBX_ERR_ARG; return nullptr; }
   c->stream = nullptr; c->sH2D = c->sD2H = c->sAlt = nullptr;
-  for (int i = 0; i < 2; ++i) { c->sSide[i] = nullptr; c->evFork[i] = c->evJoin[i] = nullptr; } c->dIngest = nullptr; c->dIngestColor = nullptr; c->hStatus = nullptr; c->hTabPtrs = nullptr; c->launches = 0; c->cameraSet = 0; c->lastBatch = 0;
+  for (int i = 0; i < 2; ++i) { c->sSide[i] = nullptr; c->evFork[i] = c->evJoin[i] = nullptr; }
+  c->evHalf = nullptr; c->dIngest = nullptr; c->dIngestColor = nullptr; c->hStatus = nullptr; c->hTabPtrs = nullptr; c->launches = 0; c->cameraSet = 0; c->lastBatch = 0;
   c->stageTiming = 0; c->evStart = c->evStop = nullptr;
   for (int i = 0; i < 10; ++i) c->evStage[i] = nullptr;
   std::memset(c->stageMs, 0, sizeof(c->stageMs));
@@ -200,6 +202,7 @@ extern "C" void orbx_destroy(orbx_ctx* c) {
     if (c->evFork[i]) cudaEventDestroy(c->evFork[i]);
     if (c->evJoin[i]) cudaEventDestroy(c->evJoin[i]);
   }
+  if (c->evHalf) cudaEventDestroy(c->evHalf);
   if (c->sAlt) cudaStreamDestroy(c->sAlt);
   if (c->sH2D) cudaStreamDestroy(c->sH2D);
   if (c->sD2H) cudaStreamDestroy(c->sD2H);

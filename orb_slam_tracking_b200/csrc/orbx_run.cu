@@ -264,8 +264,24 @@ extern "C" int orbx_stream_run(orbx_ctx* c, int n_img, float nnratio, int check_
   const Params& P = c->P;
   CU(c, cudaSetDevice(c->device));
   c->launches = 0;
-  int rc = enqueue_extract(c, P, n_img, 0, 0);
-  if (rc) return rc;
+  int rc;
+  if (n_img >= 128 && !c->stageTiming) {
+    // two halves (each a whole number of pairs) on the two compute streams: the latency-bound kernels of one half
+    // (quadtree, matcher) overlap the issue-bound ones of the other; both halves fence on the context's stream
+    const int h = (n_img / 2) & ~1;
+    CU(c, cudaEventRecord(c->evFork[1], c->stream));
+    CU(c, cudaStreamWaitEvent(c->sAlt, c->evFork[1], 0));
+    const Params Q = shifted(c, h);
+    if ((rc = enqueue_extract(c, P, h, 0, 0, c->stream))) return rc;
+    if ((rc = enqueue_extract(c, Q, n_img - h, 0, 0, c->sAlt))) return rc;
+    if ((rc = enqueue_glue_match(c, P, h, 0, nnratio, check_orientation, window_size, c->stream))) return rc;
+    if ((rc = enqueue_glue_match(c, Q, n_img - h, h / 2, nnratio, check_orientation, window_size, c->sAlt))) return rc;
+    CU(c, cudaEventRecord(c->evHalf, c->sAlt));
+    CU(c, cudaStreamWaitEvent(c->stream, c->evHalf, 0));
+    c->lastBatch = n_img;
+    return ORBX_OK;
+  }
+  if ((rc = enqueue_extract(c, P, n_img, 0, 0))) return rc;
   return enqueue_glue_match(c, P, n_img, 0, nnratio, check_orientation, window_size);
 }
 
