@@ -1,6 +1,7 @@
 // C ABI, part 2: the launch sequences (extract, glue, match), result transfer and inspection.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "ctx.cuh"
@@ -47,7 +48,8 @@ int enqueue_extract(orbx_ctx* c, const Params& P, int n, int lap0, int lap1, cud
   // issue slots; the blur is issue-bound, so they share the SMs well) and joins before the descriptors.  With per-stage timing on,
   // everything stays on one stream so that the stage events bracket one kernel each.
   const int side = (st == c->sAlt) ? 1 : 0;
-  const bool fork = !c->stageTiming;
+  static const bool singleStream = std::getenv("ORBX_SINGLE_STREAM") != nullptr;
+  const bool fork = !c->stageTiming && !singleStream;
   c->launches += launch_fast(P, c->tma, n, st);
   mark(c, 2);
   if (fork) {  // forked AFTER FAST (itself issue-bound): the blur then shares the SMs with the quadtree only
@@ -265,7 +267,8 @@ extern "C" int orbx_stream_run(orbx_ctx* c, int n_img, float nnratio, int check_
   CU(c, cudaSetDevice(c->device));
   c->launches = 0;
   int rc;
-  if (n_img >= 128 && !c->stageTiming) {
+  static const bool single = std::getenv("ORBX_SINGLE_STREAM") != nullptr;  // profiling aid: whole-batch launches in order
+  if (n_img >= 128 && !c->stageTiming && !single) {
     // two halves (each a whole number of pairs) on the two compute streams: the latency-bound kernels of one half
     // (quadtree, matcher) overlap the issue-bound ones of the other; both halves fence on the context's stream
     const int h = (n_img / 2) & ~1;

@@ -55,7 +55,13 @@ if rep.exists():
         k = r[idx[0][0]].split("(")[0]
         seen[k] = seen.get(k, 0) + 1
         if seen[k] > (7 if k == "k_resize" else 1): continue
-        vals = [k] + [("%.4g" % float(r[i])) if r[i].replace(".", "").replace("e+", "").replace("-", "").isdigit() else r[i] for i, _ in idx[1:]]
+        scale = {"ns": 1e-6, "us": 1e-3, "usecond": 1e-3, "msecond": 1.0, "ms": 1.0, "s": 1e3, "byte": 1e-6, "Kbyte": 1e-3, "Mbyte": 1.0, "Gbyte": 1e3}
+        vals = [k]
+        for i, _ in idx[1:]:
+            try:
+                vals.append("%.4g" % (float(r[i]) * scale.get(rr[1][i], 1.0)))
+            except ValueError:
+                vals.append(r[i])
         out.append("| " + " | ".join(vals) + " |")
 shutil.copy(G / f"{tag}_launches.csv", P / f"{tag}_launches.csv")
 (P / f"{tag}_summary.md").write_text("\n".join(out) + "\n")
