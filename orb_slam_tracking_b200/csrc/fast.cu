@@ -15,8 +15,8 @@
 // m > iniTh, or, if the cell has none, the peaks with m > minTh.
 //
 // Pass 1 is the hot loop: the opposing-pair rejection (every arc of 9 contains one pixel of each
-// opposing ring pair, so a pair with both |d| <= t proves m <= t) runs on FOUR pixels per thread
-// with byte-SWAR arithmetic on 32-bit words of the staged ROI: VABSDIFF4 per ring word, then a
+// opposing ring pair, so a pair with both |d| <= t proves m <= t) runs on 2 x 4 pixels per thread (two vertically
+// adjacent words, which share 6 of their 8 staged rows) with byte-SWAR arithmetic on 32-bit words of the staged ROI: VABSDIFF4 per ring word, then a
 // carry-free "byte > t" in bit 7 of each byte.  The four pairs that live on rows {-3, 0, +3} go
 // first; only words with a pixel still alive touch the other four rows, and only the few
 // surviving pixels get the exact arc value (pass 2).
@@ -65,34 +65,43 @@ __device__ __forceinline__ u32 word_at(u32 wl, u32 wc, u32 wr) {
 
 __device__ __forceinline__ u32 smem_addr(const void* p) { return (u32)__cvta_generic_to_shared(p); }
 
+struct Row3 { u32 l, c, r; };  // words g-1, g, g+1 of one staged row
+__device__ __forceinline__ Row3 load3(const u32* __restrict__ row, int g) { return Row3{row[g - 1], row[g], row[g + 1]}; }
+
+// pairs on rows {-3, 0, +3}: (dy,dx) = (3,0), (0,3), (3,1), (-3,1) and their opposites
 template <bool HI>
-__device__ __forceinline__ u32 pass1_word(const u32* __restrict__ r0, int SW, int g, u32 alive, u32 K) {
-  // rows -3, 0, +3 first: pairs (dy,dx) = (3,0), (3,1), (0,3), (-3,1) and their opposites
-  const u32* rm = r0 - 3 * SW;
-  const u32* rp = r0 + 3 * SW;
-  const u32 cl = r0[g - 1], cc = r0[g], cr = r0[g + 1];
-  const u32 ml = rm[g - 1], mc = rm[g], mr = rm[g + 1];
-  const u32 pl = rp[g - 1], pc = rp[g], pr = rp[g + 1];
-  alive &= any_gt<HI>(__vabsdiffu4(cc, pc), __vabsdiffu4(cc, mc), K);
-  alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<3>(cl, cc, cr)), __vabsdiffu4(cc, word_at<-3>(cl, cc, cr)), K);
-  alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<1>(pl, pc, pr)), __vabsdiffu4(cc, word_at<-1>(ml, mc, mr)), K);
-  alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<1>(ml, mc, mr)), __vabsdiffu4(cc, word_at<-1>(pl, pc, pr)), K);
-  if (alive) {
-    // rows +-2: (2,2)/(-2,-2) and (-2,2)/(2,-2); rows +-1: (1,3)/(-1,-3) and (-1,3)/(1,-3)
-    const u32* a2 = r0 + 2 * SW;
-    const u32* b2 = r0 - 2 * SW;
-    const u32 al = a2[g - 1], ac = a2[g], ar = a2[g + 1];
-    const u32 bl = b2[g - 1], bc = b2[g], br = b2[g + 1];
-    alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<2>(al, ac, ar)), __vabsdiffu4(cc, word_at<-2>(bl, bc, br)), K);
-    alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<2>(bl, bc, br)), __vabsdiffu4(cc, word_at<-2>(al, ac, ar)), K);
-    const u32* a1 = r0 + SW;
-    const u32* b1 = r0 - SW;
-    const u32 dl = a1[g - 1], dc = a1[g], dr = a1[g + 1];
-    const u32 el = b1[g - 1], ec = b1[g], er = b1[g + 1];
-    alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<3>(dl, dc, dr)), __vabsdiffu4(cc, word_at<-3>(el, ec, er)), K);
-    alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<3>(el, ec, er)), __vabsdiffu4(cc, word_at<-3>(dl, dc, dr)), K);
-  }
+__device__ __forceinline__ u32 pairs_rows_0_3(u32 alive, const Row3& m, const Row3& c, const Row3& p, u32 K) {
+  const u32 cc = c.c;
+  alive &= any_gt<HI>(__vabsdiffu4(cc, p.c), __vabsdiffu4(cc, m.c), K);
+  alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<3>(c.l, c.c, c.r)), __vabsdiffu4(cc, word_at<-3>(c.l, c.c, c.r)), K);
+  alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<1>(p.l, p.c, p.r)), __vabsdiffu4(cc, word_at<-1>(m.l, m.c, m.r)), K);
+  alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<1>(m.l, m.c, m.r)), __vabsdiffu4(cc, word_at<-1>(p.l, p.c, p.r)), K);
   return alive;
+}
+// pairs on rows +-2: (2,2)/(-2,-2), (-2,2)/(2,-2) and rows +-1: (1,3)/(-1,-3), (-1,3)/(1,-3)
+template <bool HI>
+__device__ __forceinline__ u32 pairs_rows_1_2(u32 alive, u32 cc, const Row3& b2, const Row3& b1, const Row3& a1, const Row3& a2, u32 K) {
+  alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<2>(a2.l, a2.c, a2.r)), __vabsdiffu4(cc, word_at<-2>(b2.l, b2.c, b2.r)), K);
+  alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<2>(b2.l, b2.c, b2.r)), __vabsdiffu4(cc, word_at<-2>(a2.l, a2.c, a2.r)), K);
+  alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<3>(a1.l, a1.c, a1.r)), __vabsdiffu4(cc, word_at<-3>(b1.l, b1.c, b1.r)), K);
+  alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<3>(b1.l, b1.c, b1.r)), __vabsdiffu4(cc, word_at<-3>(a1.l, a1.c, a1.r)), K);
+  return alive;
+}
+
+// Two vertically adjacent words (rows y and y+1 of the same word column) per call: the 8 staged rows y-3 .. y+4
+// serve both.  r0 points at row y.  The pairs of rows {-3,0,+3} go first; the other four rows are only
+// evaluated for a word that still has a pixel alive.
+template <bool HI>
+__device__ __forceinline__ void pass1_words(const u32* __restrict__ r0, int SW, int g, u32& aliveA, u32& aliveB, u32 K) {
+  const Row3 rm3 = load3(r0 - 3 * SW, g), r00 = load3(r0, g), rp3 = load3(r0 + 3 * SW, g);
+  const Row3 rm2 = load3(r0 - 2 * SW, g), rp1 = load3(r0 + SW, g), rp4 = load3(r0 + 4 * SW, g);
+  aliveA = pairs_rows_0_3<HI>(aliveA, rm3, r00, rp3, K);
+  aliveB = pairs_rows_0_3<HI>(aliveB, rm2, rp1, rp4, K);
+  if (aliveA | aliveB) {
+    const Row3 rm1 = load3(r0 - SW, g), rp2 = load3(r0 + 2 * SW, g);
+    if (aliveA) aliveA = pairs_rows_1_2<HI>(aliveA, r00.c, rm2, rm1, rp1, rp2, K);
+    if (aliveB) aliveB = pairs_rows_1_2<HI>(aliveB, rp1.c, rm1, r00, rp2, rp3, K);
+  }
 }
 
 __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ Params P, const __grid_constant__ TmaMaps M) {
@@ -151,24 +160,29 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ P
   // pass 1: opposing-pair rejection on 4 pixels at a time, items = (interior row, word) flattened over the CTA
   {
     const u32 K = (u32)(tq < 128 ? 127 - tq : 255 - tq) * 0x01010101u;
+    // items = (pair of interior rows, word): thread-private indices advance by the CTA size, row-major
+    const int nRP = (nR + 1) >> 1;
     const int stepR = kFastThreads / nW, stepG = kFastThreads - stepR * nW;
-    const int nIter = (nR * nW + kFastThreads - 1) / kFastThreads;  // the same trip count for every lane: warp collectives below
+    const int nIter = (nRP * nW + kFastThreads - 1) / kFastThreads;  // the same trip count for every lane: warp collectives below
     const int lane = tid & 31;
-    int ry = tid / nW, g = tid - ry * nW;
-    for (int it = 0; it < nIter; ++it, ry += stepR, g += stepG) {
-      if (g >= nW) { g -= nW; ++ry; }
-      u32 alive = 0;
-      const int gw = g0 + g;
+    int rp = tid / nW, g = tid - rp * nW;
+    for (int it = 0; it < nIter; ++it, rp += stepR, g += stepG) {
+      if (g >= nW) { g -= nW; ++rp; }
+      u32 aliveA = 0, aliveB = 0;
+      const int gw = g0 + g, ry = 2 * rp;
       if (ry < nR) {
-        alive = 0x80808080u;
-        if (4 * gw < bLo) alive &= 0xffffffffu << (8 * (bLo - 4 * gw));
-        if (4 * gw + 4 > bHi) alive &= 0xffffffffu >> (8 * (4 * gw + 4 - bHi));
+        u32 m = 0x80808080u;
+        if (4 * gw < bLo) m &= 0xffffffffu << (8 * (bLo - 4 * gw));
+        if (4 * gw + 4 > bHi) m &= 0xffffffffu >> (8 * (4 * gw + 4 - bHi));
+        aliveA = m;
+        aliveB = ry + 1 < nR ? m : 0u;  // the row below the last interior row is staged (apron) but not tested
         const u32* r0 = sImgW + (ry + 3) * SW;
-        alive = tq < 128 ? pass1_word<false>(r0, SW, gw, alive, K) : pass1_word<true>(r0, SW, gw, alive, K);
+        if (tq < 128) pass1_words<false>(r0, SW, gw, aliveA, aliveB, K);
+        else pass1_words<true>(r0, SW, gw, aliveA, aliveB, K);
       }
       // warp-aggregated append: one shared-memory atomic per warp and iteration
-      if (__ballot_sync(0xffffffffu, alive != 0) == 0) continue;
-      const int cnt = __popc(alive);
+      if (__ballot_sync(0xffffffffu, (aliveA | aliveB) != 0) == 0) continue;
+      const int cnt = __popc(aliveA) + __popc(aliveB);
       int inc = cnt;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
@@ -178,10 +192,15 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ P
       int base = 0;
       if (lane == 31) base = atomicAdd(&sN, inc);
       base = __shfl_sync(0xffffffffu, base, 31) + inc - cnt;
-      while (alive) {
-        const int j = (__ffs((int)alive) - 1) >> 3;
-        alive &= alive - 1;
+      while (aliveA) {
+        const int j = (__ffs((int)aliveA) - 1) >> 3;
+        aliveA &= aliveA - 1;
         sList[base++] = (unsigned short)(((ry + 3) << 8) | (4 * gw + j));
+      }
+      while (aliveB) {
+        const int j = (__ffs((int)aliveB) - 1) >> 3;
+        aliveB &= aliveB - 1;
+        sList[base++] = (unsigned short)(((ry + 4) << 8) | (4 * gw + j));
       }
     }
   }
