@@ -22,6 +22,7 @@ namespace orbx {
 constexpr int kResizeRows = 16, kResizeWarps = 4;
 
 // tab: xofs[dw] | xcoef[dw] (a0 | a1 << 16) | yofs[dh] | ycoef[dh] (b0 | b1 << 16)
+template <bool WIDE>
 __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_constant__ Params P, int l, const int* __restrict__ tab, int rows) {
   const LevelInfo& D = P.lv[l];
   const LevelInfo& S = P.lv[l - 1];
@@ -52,8 +53,15 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
   const bool need3 = (sx0 & 3) + e1[3] >= 8;
   const u8* __restrict__ colp = src + A;
 
+  // WIDE: scale factors above 2 spread a lane's taps over more than the 8 bytes the permutes can reach -> byte loads
   // horizontally interpolated row r, pre-shifted: (S[sx] * a0 + S[sx + 1] * a1) >> 4
   auto hrow = [&](int r, int (&hs)[4]) {
+    if (WIDE) {
+      const u8* rowp = src + r * S.pitch + sx0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) hs[k] = (int)((u32)__ldg(rowp + e0[k]) * (u32)a0[k] + (u32)__ldg(rowp + e1[k]) * (u32)a1[k]) >> 4;
+      return;
+    }
     const u32* rp = reinterpret_cast<const u32*>(colp + r * S.pitch);
     const u32 w0 = __ldg(rp), w1 = __ldg(rp + 1), w2 = need3 ? __ldg(rp + 2) : 0u;
     const u32 q0 = __funnelshift_r(w0, w1, sh), q1 = __funnelshift_r(w1, w2, sh);
@@ -173,7 +181,9 @@ int launch_pyramid(const Params& P, const int* const* dTabs, int nSlots, cudaStr
     static const int rowsEnv = std::getenv("ORBX_RESIZE_ROWS") ? std::atoi(std::getenv("ORBX_RESIZE_ROWS")) : 0;
     const int rows = rowsEnv > 0 ? rowsEnv : kResizeRows;
     dim3 grid((P.lv[l].w + 127) / 128, (P.lv[l].h + rows * kResizeWarps - 1) / (rows * kResizeWarps), nSlots);
-    k_resize<<<grid, block, 0, st>>>(P, l, dTabs[l], rows);
+    // taps of 4 adjacent output columns span 3 * scale + 2 source bytes
+    if (P.lv[l - 1].w > 2 * P.lv[l].w + 1) k_resize<true><<<grid, block, 0, st>>>(P, l, dTabs[l], rows);
+    else k_resize<false><<<grid, block, 0, st>>>(P, l, dTabs[l], rows);
     ++n;
   }
   return n;

@@ -184,3 +184,19 @@ def test_full_batch_properties(fe, oracle, synth):
     assert out["nmatches"][-1] == rn and np.array_equal(out["matches12"][-1, :len(rm12)], rm12)
     assert np.array_equal(out["counters"][-1], rcnt)
     E.close()
+
+
+@pytest.mark.parametrize("nf,sf,nl,W,H", [(500, 1.5, 4, 640, 480), (300, 2.0, 3, 640, 480), (300, 2.5, 2, 800, 600),
+                                          (200, 1.0, 1, 320, 240), (700, 1.1, 8, 752, 480), (400, 1.2, 10, 1241, 600)])
+def test_other_pyramid_shapes(fe, oracle, synth, nf, sf, nl, W, H):
+    """Scale factors and level counts other than the demo's 1.2 / 8 (ORBextractor takes any, :492-505)."""
+    E = fe.ORBextractor(nf, sf, nl, 20, 7, W, H)
+    R = oracle.Extractor(nf, sf, nl, 20, 7)
+    img = synth.frames(2, W, H, first_pair=31)[1]
+    kps, desc, mono = E(img)
+    rk, rd, rmono = R(img)
+    for l in range(nl):
+        assert np.array_equal(E.pyramid_level(l), R.level(l)), ("pyramid", l)
+    _assert_kps_equal(kps, rk, "packed keypoints")
+    assert np.array_equal(desc, rd) and mono == rmono
+    E.close()
