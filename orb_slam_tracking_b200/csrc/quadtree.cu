@@ -18,9 +18,12 @@
 
 namespace orbx {
 
-constexpr int QT = 64;   // small CTAs: the one-thread std::sort replay of a CTA overlaps the parallel phases of its SM neighbours
+// CTA size QT is a template parameter: small CTAs (64 threads) for the usual quotas of a few hundred keypoints per
+// level, so that the one-thread std::sort replay of a CTA overlaps the parallel phases of its SM neighbours; 512
+// threads when a level carries thousands of candidates (3840x2160 / 8000 kp), where the candidate loops dominate.
 
 
+template <int QT>
 struct QtS {
   int nNodes, size, gen0, gen1, nS, nProc, nToExpand, cut;
   int part[QT];
@@ -32,6 +35,7 @@ struct PackedLess {
 };
 
 // In-place inclusive scan of a[0..n) by the whole CTA.  Returns the total to every thread.
+template <int QT>
 __device__ int cta_scan(int* a, int n, int* part) {
   const int tid = threadIdx.x;
   const int chunk = (n + QT - 1) / QT;
@@ -60,8 +64,9 @@ __device__ __forceinline__ int quadrant(const short4 b, const u32 xy) {
   return (x >= midx ? 1 : 0) + (y >= midy ? 2 : 0);  // n1, n2, n3, n4
 }
 
+template <int QT>
 __global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params P, int sortCap) {
-  __shared__ QtS S;
+  __shared__ QtS<QT> S;
   extern __shared__ __align__(8) u64 sSrt[];  // sortCap packed sort words (launch_quadtree sizes it from the largest quota)
   const int l = blockIdx.x, slot = blockIdx.y, tid = threadIdx.x;
   const LevelInfo& L = P.lv[l];
@@ -115,7 +120,7 @@ __global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params 
     if (!phase2) {
       for (int j = tid; j < G; j += QT) scan[j] = nCount[gen1 - 1 - j] > 1;
       __syncthreads();
-      nS = cta_scan(scan, G, S.part);
+      nS = cta_scan<QT>(scan, G, S.part);
       for (int j = tid; j < G; j += QT) {
         const int node = gen1 - 1 - j;
         if (nCount[node] > 1) list[scan[j] - 1] = node;
@@ -123,7 +128,7 @@ __global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params 
     } else {
       for (int j = tid; j < G; j += QT) scan[j] = nCount[gen0 + j] > 1;
       __syncthreads();
-      nS = cta_scan(scan, G, S.part);
+      nS = cta_scan<QT>(scan, G, S.part);
       // the sort runs in one thread (its tie order is the algorithm's, see stdsort_emul.cuh): keep its
       // elements in shared memory as single 64-bit words, count << 40 | UL.x << 24 | node id
       const bool inSmem = nS <= sortCap;
@@ -164,7 +169,7 @@ __global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params 
       scan[s] = (aux[4 * s] > 0) + (aux[4 * s + 1] > 0) + (aux[4 * s + 2] > 0) + (aux[4 * s + 3] > 0);
     if (tid == 0) { S.cut = nS - 1; S.nToExpand = 0; }
     __syncthreads();
-    cta_scan(scan, nS, S.part);
+    cta_scan<QT>(scan, nS, S.part);
     if (phase2) {
       for (int s = tid; s < nS; s += QT)
         if (prevSize + scan[s] - (s + 1) >= N) atomicMin(&S.cut, s);
@@ -223,7 +228,7 @@ __global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params 
   for (int k = tid; k < M; k += QT) atomicMax(nBest + cNode[k], cKey[k]);
   for (int j = tid; j < nNodes; j += QT) scan[j] = nCount[nNodes - 1 - j] > 0;
   __syncthreads();
-  const int alive = cta_scan(scan, nNodes, S.part);
+  const int alive = cta_scan<QT>(scan, nNodes, S.part);
   const size_t ko = (size_t)slot * P.kpStride + L.kpOff;
   for (int j = tid; j < nNodes; j += QT) {
     const int node = nNodes - 1 - j;
@@ -250,7 +255,10 @@ int launch_quadtree(const Params& P, int nSlots, cudaStream_t st) {
   int q = 0;
   for (int l = 0; l < P.nlevels; ++l) q = q > P.lv[l].quota ? q : P.lv[l].quota;
   const int sortCap = 2 * q < 256 ? 256 : (2 * q > 4096 ? 4096 : 2 * q);
-  k_quadtree<<<grid, QT, (size_t)sortCap * sizeof(u64), st>>>(P, sortCap);
+  const size_t smem = (size_t)sortCap * sizeof(u64);
+  if (q < 400) k_quadtree<64><<<grid, 64, smem, st>>>(P, sortCap);
+  else if (q < 1000) k_quadtree<256><<<grid, 256, smem, st>>>(P, sortCap);
+  else k_quadtree<512><<<grid, 512, smem, st>>>(P, sortCap);
   return 1;
 }
 
