@@ -263,8 +263,47 @@ def run_ours(args, wl):
         st = np.zeros(8, np.float32)
         L.orbx_get_stage_times(E._h, capi.ptr(st))
         acc += st
-    L.orbx_set_stage_timing(E._h, 0)
     stage_ms = acc / reps
+    # the step after the path, outside every timed region above: Initializer::CheckHomography /
+    # CheckFundamental for a RANSAC set of 200 hypotheses per model on every resident pair
+    scoring = None
+    if rank == 0:
+        import time
+        nP, nh = B // 2, 200
+        rng = np.random.default_rng(5)
+        Hs = np.tile(np.eye(3, dtype=np.float32).reshape(1, 1, 9), (nP, nh, 1))
+        Hs[:, :, [2, 5]] += rng.uniform(-20, 20, (nP, nh, 2)).astype(np.float32)
+        Hinv = Hs.copy()
+        Hinv[:, :, [2, 5]] *= -1
+        Fs = rng.normal(0, 1e-3, (nP, nh, 9)).astype(np.float32)
+        S.score_models(nP, Hs, Hinv, Fs)   # warm-up (allocates the scratch)
+        t0 = time.perf_counter()
+        sc = S.score_models(nP, Hs, Hinv, Fs)
+        call_ms = (time.perf_counter() - t0) * 1e3
+        st = np.zeros(8, np.float32)
+        L.orbx_get_stage_times(E._h, capi.ptr(st))
+        evals = 2.0 * nh * float(sc["n_list"].sum())
+        scoring = {"pairs": nP, "hypotheses_per_model": nh, "mean_matches": float(sc["n_list"].mean()),
+                   "kernel_ms": round(float(st[5]), 4), "call_ms_with_copies": round(call_ms, 3),
+                   "hypothesis_match_evals_per_s": evals / (float(st[5]) * 1e-3) if st[5] > 0 else None}
+        if world == 1 and not args.no_cpu:
+            from oracle import orb_oracle as orc, ref_orb
+            n_all = np.ctypeslib.as_array(C.cast(res["n"], C.POINTER(C.c_int32)), shape=(B,))
+            ku = np.ctypeslib.as_array(C.cast(res["kps_un"], C.POINTER(C.c_ubyte)), shape=(B * cap * 28,)).view(capi.KP_DTYPE).reshape(B, cap)
+            m12 = np.ctypeslib.as_array(C.cast(res["m12"], C.POINTER(C.c_int32)), shape=(B // 2, cap))
+            use_ref = ref_orb.available() and hasattr(ref_orb.lib(), "ref_check_homography")
+            impl = ref_orb if use_ref else orc
+            t0 = time.perf_counter()
+            ev = 0
+            for p in range(min(nP, 8)):
+                k1, k2, m = ku[2 * p][: n_all[2 * p]], ku[2 * p + 1][: n_all[2 * p + 1]], m12[p][: n_all[2 * p]]
+                impl.check_homography(k1, k2, m, Hs[p], Hinv[p])
+                impl.check_fundamental(k1, k2, m, Fs[p])
+                ev += 2 * nh * int((m >= 0).sum())
+            dt = time.perf_counter() - t0
+            scoring["cpu"] = {"hypothesis_match_evals_per_s": ev / dt, "cores": 1, "kind": "reference" if use_ref else "port",
+                              "sample": "%d pairs x %d hypotheses x 2 models" % (min(nP, 8), nh)}
+    L.orbx_set_stage_timing(E._h, 0)
     # sanity of the work done: every frame produced keypoints and pairs produced matches
     n_out = np.ctypeslib.as_array(C.cast(res["n"], C.POINTER(C.c_int32)), shape=(B,)).copy()
     nm = np.ctypeslib.as_array(C.cast(res["nm"], C.POINTER(C.c_int32)), shape=(B // 2,)).copy()
@@ -302,6 +341,7 @@ def run_ours(args, wl):
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "launches_per_step": n_launch_dom,
                          "ms_per_step": dom_ms, "algorithmic_bytes_per_step": int(ab[dom] * B)},
         }
+        line["next_rows"] = {"init_scoring": scoring}
         if world == 1 and not args.no_cpu:
             threads = host_threads()
             n_cpu = max(16 * threads, 64) if W * H < 2_000_000 else 2 * threads

@@ -16,6 +16,8 @@
  *   orbx_features_in_area                 Frame::GetFeaturesInArea      SlamTypes/Frame.cpp:163-206
  *   orbx_search_for_initialization        ORBmatcher::SearchForInitialization  Features/ORBmatcher.cpp:11-150
  *   orbx_descriptor_distance              DBoW2::FORB::distance         Thirdparty/DBoW2/src/FORB.cpp:77-100
+ *   orbx_check_homography / _fundamental  Initializer::CheckHomography / CheckFundamental (+ the RANSAC selection)
+ *   orbx_stream_score_models              Initialization/Initializer.cpp:268-438, :205-209, :257-261
  *   orbx_stream_*                         the demo's per-pair sequence  demo/demo_initialization.cpp:65-108
  *                                         kept resident on the device (throughput path)
  *
@@ -133,6 +135,30 @@ int orbx_descriptor_distance(const uint8_t a[32], const uint8_t b[32]);
 /* n distances a[i] vs b[i] on the device (32 bytes each). */
 int orbx_descriptor_distance_batch(orbx_ctx* ctx, const uint8_t* a, const uint8_t* b, int n, int* out);
 
+/* ---- Initializer scoring (the step after the matcher) --------------------------- */
+/* Initializer::CheckHomography (Initialization/Initializer.cpp:268-353) for n_hyp hypotheses on one pair.
+ * kps1_un / kps2_un = mvKeysUn of the reference and the current frame, matches12 = vnMatches12 (n1 ints); the match
+ * list mvMatches12 is the ascending i with matches12[i] >= 0 (Initializer.cpp:27-34), *n_list its length N.
+ * H21, H12 (= its inverse, as the caller computed it): n_hyp x 9 floats, row-major.  scores: n_hyp floats, bit-equal
+ * to the reference's.  inliers (may be NULL): n_hyp x N bytes, vbMatchesInliers per hypothesis.  *best (may be NULL):
+ * the selection of the RANSAC loop FindHomography (:205-209) over the set -- the first hypothesis whose score is
+ * strictly larger than every earlier one and than 0, or -1. */
+int orbx_check_homography(orbx_ctx* ctx, const orbx_keypoint* kps1_un, int n1, const orbx_keypoint* kps2_un, int n2,
+                          const int* matches12, const float* H21, const float* H12, int n_hyp, float sigma,
+                          float* scores, uint8_t* inliers, int* n_list, int* best);
+/* Initializer::CheckFundamental (Initializer.cpp:355-438); selection as FindFundamental (:257-261). */
+int orbx_check_fundamental(orbx_ctx* ctx, const orbx_keypoint* kps1_un, int n1, const orbx_keypoint* kps2_un, int n2,
+                           const int* matches12, const float* F21, int n_hyp, float sigma, float* scores,
+                           uint8_t* inliers, int* n_list, int* best);
+/* Both models on the first n_pairs pairs still resident from the last orbx_stream_run / orbx_stream_process (their
+ * undistorted keys and vnMatches12 never leave the device).  H21, H12, F21: n_pairs x n_hyp x 9 floats (H21 / H12 or
+ * F21 may be NULL to skip a model).  scores_*: n_pairs x n_hyp; best_*: n_pairs; inliers_*: blocks of `cap` bytes per
+ * pair holding the flags of the selected hypothesis by list position (0 beyond N or when best = -1); n_list: n_pairs.
+ * Any output may be NULL. */
+int orbx_stream_score_models(orbx_ctx* ctx, int n_pairs, const float* H21, const float* H12, const float* F21,
+                             int n_hyp, float sigma, float* scores_h, float* scores_f, int* best_h, int* best_f,
+                             uint8_t* inliers_h, uint8_t* inliers_f, int cap, int* n_list);
+
 /* ---- device-resident stream (throughput path) ---------------------------------------------- */
 /* The frames of a batch stay in HBM from the image to the match list: extract -> glue ->
  * SearchForInitialization on the pairs (2k, 2k+1).  orbx_set_camera must have been called. */
@@ -162,7 +188,7 @@ int orbx_stream_sync(orbx_ctx* ctx);
 int orbx_timer_start(orbx_ctx* ctx);
 int orbx_timer_stop(orbx_ctx* ctx, float* ms);
 int orbx_set_stage_timing(orbx_ctx* ctx, int enable);
-/* 8 stages: pyramid, fast, quadtree, blur, describe+pack, (unused, 0), glue, match */
+/* 8 slots: pyramid, fast, quadtree, blur, describe+pack, scoring kernels of the last orbx_stream_score_models, glue, match */
 int orbx_get_stage_times(orbx_ctx* ctx, float* ms8);
 /* number of kernel launches issued by the last orbx_stream_run / orbx_extract_batch */
 int orbx_last_launch_count(const orbx_ctx* ctx);

@@ -8,9 +8,14 @@ HERE="$(cd "$(dirname "$0")" && pwd)"
 REF="${REFERENCE_ROOT:-/root/reference}"
 [ -f "$REF/Features/ORBextractor.cpp" ] || { echo "build_ref.sh: no reference checkout at $REF"; exit 0; }
 mkdir -p "$HERE/_ref"
+# Initializer.cpp needs calib3d and Eigen as a whole; only its constructor and the two scoring functions
+# (CheckHomography, CheckFundamental: plain float arithmetic) are cut out, each from its signature line to the
+# first closing brace in column 0, into a generated include that stays under _ref/.
+awk '/^Initializer::Initializer\(/ || /^float Initializer::CheckHomography\(/ || /^float Initializer::CheckFundamental\(/ {on=1}
+     on {print} on && /^}/ {on=0}' "$REF/Initialization/Initializer.cpp" > "$HERE/_ref/initializer_slice.inc"
 g++ -O3 -std=c++17 -fPIC -shared -pthread -ffp-contract=off -w \
   -I"$HERE/refshim" -I"$REF" -I"$REF/Thirdparty/DBoW2/include" -I"$REF/Thirdparty/DBoW2/include/DBoW2" \
   "$REF/Features/ORBextractor.cpp" "$REF/Features/ORBmatcher.cpp" "$REF/SlamTypes/Frame.cpp" \
   "$REF/Thirdparty/DBoW2/src/FORB.cpp" "$REF/Thirdparty/DBoW2/src/BowVector.cpp" "$REF/Thirdparty/DBoW2/src/FeatureVector.cpp" \
-  "$HERE/ref_driver.cpp" -o "$HERE/_ref/libref_orb.so"
+  "$HERE/ref_driver.cpp" "$HERE/ref_init_driver.cpp" -I"$HERE/_ref" -o "$HERE/_ref/libref_orb.so"
 echo "built $HERE/_ref/libref_orb.so"

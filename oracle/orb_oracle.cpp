@@ -790,4 +790,91 @@ long long orc_run_stream(const u8* imgs, int nframes, int W, int H, int nfeature
   return matches.load();
 }
 
+// ---- Initializer scoring ---------------------------------------------------
+// Initializer::CheckHomography (Initialization/Initializer.cpp:268-353) and CheckFundamental (:355-438) for
+// nHyp hypotheses (row-major 3x3 float32 each) on one pair.  The match list mvMatches12 is built as
+// Initializer::Initialize does (:27-34): ascending i with matches12[i] >= 0.  All arithmetic is float32 in the
+// order written in the reference; `1.0 / x` is a double division narrowed to float (:314,331,293,372).
+// Returns N = number of matches.  inliers (may be NULL): nHyp x N bytes.
+static int match_list(const KeyPoint* k1, const KeyPoint* k2, const int* m12, int n1, std::vector<float>& uv) {
+  uv.clear();
+  for (int i = 0; i < n1; ++i)
+    if (m12[i] >= 0) {
+      uv.push_back(k1[i].x); uv.push_back(k1[i].y); uv.push_back(k2[m12[i]].x); uv.push_back(k2[m12[i]].y);
+    }
+  return (int)(uv.size() / 4);
+}
+int orc_check_homography(const KeyPoint* k1, const KeyPoint* k2, const int* m12, int n1, const float* H21s, const float* H12s,
+                         int nHyp, float sigma, float* scores, u8* inliers) {
+  std::vector<float> uv;
+  const int N = match_list(k1, k2, m12, n1, uv);
+  const float th = 5.991;                                // :291
+  const float invSigmaSquare = 1.0 / (sigma * sigma);    // :293
+  for (int h = 0; h < nHyp; ++h) {
+    const float* A = H21s + 9 * h;
+    const float* B = H12s + 9 * h;
+    float score = 0;
+    for (int i = 0; i < N; ++i) {
+      bool bIn = true;
+      const float u1 = uv[4 * i], v1 = uv[4 * i + 1], u2 = uv[4 * i + 2], v2 = uv[4 * i + 3];
+      const float w2in1inv = 1.0 / (B[6] * u2 + B[7] * v2 + B[8]);   // :314
+      const float u2in1 = (B[0] * u2 + B[1] * v2 + B[2]) * w2in1inv;
+      const float v2in1 = (B[3] * u2 + B[4] * v2 + B[5]) * w2in1inv;
+      const float squareDist1 = (u1 - u2in1) * (u1 - u2in1) + (v1 - v2in1) * (v1 - v2in1);
+      const float chiSquare1 = squareDist1 * invSigmaSquare;
+      if (chiSquare1 > th) bIn = false; else score += th - chiSquare1;
+      const float w1in2inv = 1.0 / (A[6] * u1 + A[7] * v1 + A[8]);   // :331
+      const float u1in2 = (A[0] * u1 + A[1] * v1 + A[2]) * w1in2inv;
+      const float v1in2 = (A[3] * u1 + A[4] * v1 + A[5]) * w1in2inv;
+      const float squareDist2 = (u2 - u1in2) * (u2 - u1in2) + (v2 - v1in2) * (v2 - v1in2);
+      const float chiSquare2 = squareDist2 * invSigmaSquare;
+      if (chiSquare2 > th) bIn = false; else score += th - chiSquare2;
+      if (inliers) inliers[(size_t)h * N + i] = bIn ? 1 : 0;
+    }
+    scores[h] = score;
+  }
+  return N;
+}
+int orc_check_fundamental(const KeyPoint* k1, const KeyPoint* k2, const int* m12, int n1, const float* F21s, int nHyp, float sigma,
+                          float* scores, u8* inliers) {
+  std::vector<float> uv;
+  const int N = match_list(k1, k2, m12, n1, uv);
+  const float th = 3.841;        // :372
+  const float thScore = 5.991;   // :374
+  const float invSigmaSquare = 1.0 / (sigma * sigma);
+  for (int h = 0; h < nHyp; ++h) {
+    const float* F = F21s + 9 * h;
+    float score = 0;
+    for (int i = 0; i < N; ++i) {
+      bool bIn = true;
+      const float u1 = uv[4 * i], v1 = uv[4 * i + 1], u2 = uv[4 * i + 2], v2 = uv[4 * i + 3];
+      const float a2 = F[0] * u1 + F[1] * v1 + F[2];                 // l2 = F21 x1 (:392-394)
+      const float b2 = F[3] * u1 + F[4] * v1 + F[5];
+      const float c2 = F[6] * u1 + F[7] * v1 + F[8];
+      const float num2 = a2 * u2 + b2 * v2 + c2;
+      const float squareDist1 = num2 * num2 / (a2 * a2 + b2 * b2);
+      const float chiSquare1 = squareDist1 * invSigmaSquare;
+      if (chiSquare1 > th) bIn = false; else score += thScore - chiSquare1;
+      const float a1 = F[0] * u2 + F[3] * v2 + F[6];                 // l1 = F21^T x2 (:414-416)
+      const float b1 = F[1] * u2 + F[4] * v2 + F[7];
+      const float c1 = F[2] * u2 + F[5] * v2 + F[8];
+      const float num1 = a1 * u1 + b1 * v1 + c1;
+      const float squareDist2 = num1 * num1 / (a1 * a1 + b1 * b1);
+      const float chiSquare2 = squareDist2 * invSigmaSquare;
+      if (chiSquare2 > th) bIn = false; else score += thScore - chiSquare2;
+      if (inliers) inliers[(size_t)h * N + i] = bIn ? 1 : 0;
+    }
+    scores[h] = score;
+  }
+  return N;
+}
+// the selection of the RANSAC loops FindHomography / FindFundamental (:205-209, :257-261): the running best starts
+// at 0 and is replaced only by a strictly larger score; -1 when no hypothesis scores above 0
+int orc_ransac_best(const float* scores, int nHyp) {
+  float score = 0; int best = -1;
+  for (int it = 0; it < nHyp; ++it)
+    if (scores[it] > score) { score = scores[it]; best = it; }
+  return best;
+}
+
 }  // extern "C"

@@ -69,6 +69,9 @@ def lib():
         L.orc_run_stream.restype = C.c_longlong
         L.orc_run_stream.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int,
                                      C.c_int, vp, vp, C.c_int, C.c_float, C.c_int, vp]
+        L.orc_check_homography.argtypes = [vp, vp, vp, C.c_int, vp, vp, C.c_int, C.c_float, vp, vp]
+        L.orc_check_fundamental.argtypes = [vp, vp, vp, C.c_int, vp, C.c_int, C.c_float, vp, vp]
+        L.orc_ransac_best.argtypes = [vp, C.c_int]
         _LIB = L
     return _LIB
 
@@ -271,3 +274,37 @@ def run_stream(imgs, nfeatures, scale_factor, nlevels, ini_th, min_th, K4, D4, w
     m = lib().orc_run_stream(_p(imgs), n, W, H, nfeatures, scale_factor, nlevels, ini_th, min_th, _p(K4), _p(D4),
                              window, nnratio, threads, C.addressof(tot))
     return int(m), int(tot.value)
+
+
+# ------------------------------------------------------------------ Initializer scoring (row N2)
+def _hyp(M):
+    M = np.ascontiguousarray(M, np.float32).reshape(-1, 9)
+    return M
+
+
+def check_homography(kps1_un, kps2_un, matches12, H21, H12, sigma=1.0):
+    """Initializer::CheckHomography for each hypothesis -> (scores[nHyp], inliers[nHyp, N])."""
+    k1, k2 = np.ascontiguousarray(kps1_un, KP_DTYPE), np.ascontiguousarray(kps2_un, KP_DTYPE)
+    m = np.ascontiguousarray(matches12, np.int32)
+    A, B = _hyp(H21), _hyp(H12)
+    N = int((m >= 0).sum())
+    scores = np.zeros(len(A), np.float32)
+    inl = np.zeros((len(A), N), np.uint8)
+    lib().orc_check_homography(_p(k1), _p(k2), _p(m), len(m), _p(A), _p(B), len(A), sigma, _p(scores), _p(inl))
+    return scores, inl
+
+
+def check_fundamental(kps1_un, kps2_un, matches12, F21, sigma=1.0):
+    k1, k2 = np.ascontiguousarray(kps1_un, KP_DTYPE), np.ascontiguousarray(kps2_un, KP_DTYPE)
+    m = np.ascontiguousarray(matches12, np.int32)
+    A = _hyp(F21)
+    N = int((m >= 0).sum())
+    scores = np.zeros(len(A), np.float32)
+    inl = np.zeros((len(A), N), np.uint8)
+    lib().orc_check_fundamental(_p(k1), _p(k2), _p(m), len(m), _p(A), len(A), sigma, _p(scores), _p(inl))
+    return scores, inl
+
+
+def ransac_best(scores):
+    s = np.ascontiguousarray(scores, np.float32)
+    return int(lib().orc_ransac_best(_p(s), len(s)))

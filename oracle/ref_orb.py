@@ -20,7 +20,7 @@ _LIB = None
 
 def build():
     """Needs /root/reference; a no-op (and `available()` stays False) without it."""
-    srcs = [_DIR / "ref_driver.cpp", _DIR / "cv_prims.hpp", _DIR / "refshim" / "opencv2" / "opencv.hpp"]
+    srcs = [_DIR / "ref_driver.cpp", _DIR / "ref_init_driver.cpp", _DIR / "build_ref.sh", _DIR / "cv_prims.hpp", _DIR / "refshim" / "opencv2" / "opencv.hpp"]
     if SO.exists() and all(s.stat().st_mtime <= SO.stat().st_mtime for s in srcs):
         return SO
     subprocess.run(["bash", str(_DIR / "build_ref.sh")], check=True, stdout=subprocess.DEVNULL)
@@ -55,6 +55,9 @@ def lib():
         L.ref_forb_distance.argtypes = [vp, vp]
         L.ref_run_stream.restype = C.c_longlong
         L.ref_run_stream.argtypes = [vp, ci, ci, ci, ci, cf, ci, ci, ci, vp, vp, ci, cf, ci, vp]
+        if hasattr(L, "ref_check_homography"):
+            L.ref_check_homography.argtypes = [vp, ci, vp, ci, vp, vp, vp, ci, cf, vp, vp]
+            L.ref_check_fundamental.argtypes = [vp, ci, vp, ci, vp, vp, ci, cf, vp, vp]
         _LIB = L
     return _LIB
 
@@ -159,3 +162,27 @@ def run_stream(imgs, nfeatures, scale_factor, nlevels, ini_th, min_th, K4, D4, w
     m = lib().ref_run_stream(_p(imgs), n, W, H, nfeatures, scale_factor, nlevels, ini_th, min_th, _p(K4), _p(D4), window, nnratio,
                              threads, C.byref(tot))
     return int(m), int(tot.value)
+
+
+def check_homography(kps1_un, kps2_un, matches12, H21, H12, sigma=1.0):
+    """The reference's own Initializer::CheckHomography (Initializer.cpp:268-353) per hypothesis."""
+    k1, k2 = np.ascontiguousarray(kps1_un, KP_DTYPE), np.ascontiguousarray(kps2_un, KP_DTYPE)
+    m = np.ascontiguousarray(matches12, np.int32)
+    A = np.ascontiguousarray(H21, np.float32).reshape(-1, 9)
+    B = np.ascontiguousarray(H12, np.float32).reshape(-1, 9)
+    N = int((m >= 0).sum())
+    scores = np.zeros(len(A), np.float32)
+    inl = np.zeros((len(A), N), np.uint8)
+    lib().ref_check_homography(_p(k1), len(k1), _p(k2), len(k2), _p(m), _p(A), _p(B), len(A), sigma, _p(scores), _p(inl))
+    return scores, inl
+
+
+def check_fundamental(kps1_un, kps2_un, matches12, F21, sigma=1.0):
+    k1, k2 = np.ascontiguousarray(kps1_un, KP_DTYPE), np.ascontiguousarray(kps2_un, KP_DTYPE)
+    m = np.ascontiguousarray(matches12, np.int32)
+    A = np.ascontiguousarray(F21, np.float32).reshape(-1, 9)
+    N = int((m >= 0).sum())
+    scores = np.zeros(len(A), np.float32)
+    inl = np.zeros((len(A), N), np.uint8)
+    lib().ref_check_fundamental(_p(k1), len(k1), _p(k2), len(k2), _p(m), _p(A), len(A), sigma, _p(scores), _p(inl))
+    return scores, inl

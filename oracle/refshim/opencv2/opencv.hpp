@@ -69,6 +69,13 @@ typedef Point_<int> Point2i;
 typedef Point2i Point;
 typedef Point_<float> Point2f;
 typedef Point_<double> Point2d;
+template <typename T>
+struct Point3_ {
+  T x, y, z;
+  Point3_() : x(0), y(0), z(0) {}
+  Point3_(T x_, T y_, T z_) : x(x_), y(y_), z(z_) {}
+};
+typedef Point3_<float> Point3f;  // Initialization/Initializer.hpp signatures
 
 template <typename T>
 struct Size_ {

@@ -54,6 +54,9 @@ SIGNATURES = {
     "orbx_search_for_initialization": (ci, [vp, vp, vp, cf, ci, ci, vp, vp, vp]),
     "orbx_descriptor_distance": (ci, [vp, vp]),
     "orbx_descriptor_distance_batch": (ci, [vp, vp, vp, ci, vp]),
+    "orbx_check_homography": (ci, [vp, vp, ci, vp, ci, vp, vp, vp, ci, cf, vp, vp, vp, vp]),
+    "orbx_check_fundamental": (ci, [vp, vp, ci, vp, ci, vp, vp, ci, cf, vp, vp, vp, vp]),
+    "orbx_stream_score_models": (ci, [vp, ci, vp, vp, vp, ci, cf, vp, vp, vp, vp, vp, vp, ci, vp]),
     "orbx_stream_upload": (ci, [vp, vp, ci]),
     "orbx_stream_upload_color": (ci, [vp, vp, ci, ci]),
     "orbx_stream_run": (ci, [vp, ci, cf, ci, ci]),

@@ -159,4 +159,22 @@ struct MatchArgs {
 int launch_match(const Params& P, const MatchArgs& A, int nPairs, int pairStep, float nnratio, int checkOri,
                  int window, cudaStream_t st);
 
+// Initializer::CheckHomography / CheckFundamental over hypothesis sets (score.cu)
+struct ScoreArgs {
+  const orbx_keypoint* keysUn;  // [slot][stride]
+  const int* n;                 // [slot]
+  int stride, pairStep;         // frames of pair p live in slots p * pairStep and p * pairStep + 1
+  const int* matches12;         // [pair][stride]
+  const float* hypA;            // [pair][nHyp][9]  H21 or F21, row-major
+  const float* hypB;            // [pair][nHyp][9]  H12 (homography only)
+  int nHyp;
+  float invSigmaSquare;
+  float* scores;                // [pair][nHyp]
+  int* best;                    // [pair]  -1: no hypothesis scored above 0
+  int* nList;                   // [pair]  N = length of the match list
+  u8* inlAll;                   // nullable, [pair][nHyp][N] (packed with the pair's own N; single-pair calls)
+  u8* inlBest;                  // nullable, [pair][stride]: inlier flags of the selected hypothesis, 0 beyond N
+};
+int launch_score_models(const ScoreArgs& S, int nPairs, bool fundamental, cudaStream_t st);
+
 }  // namespace orbx

@@ -63,6 +63,9 @@ struct orbx_ctx {
   int* hfCounters;
   int* hfScratch;
   int hfCap;
+  // Initializer scoring scratch (grown on demand): hypotheses, scores, best, list lengths, inlier flags
+  orbx::u8* dScore;
+  size_t scoreBytes;
   // timing
   cudaEvent_t evStart, evStop;
   int stageTiming;

@@ -174,7 +174,7 @@ extern "C" orbx_ctx* orbx_create(int device, int width, int height, int nfeature
   if (!c) { if (status) *status = ORBX_ERR_ARG; return nullptr; }
   c->stream = nullptr; c->sH2D = c->sD2H = c->sAlt = nullptr;
   for (int i = 0; i < 2; ++i) { c->sSide[i] = nullptr; c->evFork[i] = c->evJoin[i] = nullptr; }
-  c->evHalf = nullptr; c->dIngest = nullptr; c->dIngestColor = nullptr; c->hStatus = nullptr; c->hTabPtrs = nullptr; c->launches = 0; c->cameraSet = 0; c->lastBatch = 0;
+  c->evHalf = nullptr; c->dIngest = nullptr; c->dIngestColor = nullptr; c->hStatus = nullptr; c->hTabPtrs = nullptr; c->launches = 0; c->cameraSet = 0; c->lastBatch = 0; c->dScore = nullptr; c->scoreBytes = 0;
   c->stageTiming = 0; c->evStart = c->evStop = nullptr;
   for (int i = 0; i < 10; ++i) c->evStage[i] = nullptr;
   std::memset(c->stageMs, 0, sizeof(c->stageMs));
@@ -192,6 +192,7 @@ extern "C" void orbx_destroy(orbx_ctx* c) {
   if (!c) return;
   if (c->stream) cudaStreamSynchronize(c->stream);
   for (void* p : c->allocs) cudaFree(p);
+  if (c->dScore) cudaFree(c->dScore);
   if (c->evStart) cudaEventDestroy(c->evStart);
   if (c->evStop) cudaEventDestroy(c->evStop);
   for (int i = 0; i < 10; ++i) if (c->evStage[i]) cudaEventDestroy(c->evStage[i]);

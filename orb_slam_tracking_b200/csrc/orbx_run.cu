@@ -296,7 +296,8 @@ extern "C" int orbx_stream_sync(orbx_ctx* c) {
     static const int a[ST_N] = {0, 1, 2, 3, 4, 5, 5, 6}, b[ST_N] = {1, 2, 3, 4, 5, 5, 6, 7};
     for (int i = 0; i < ST_N; ++i) {
       float ms = 0.f;
-      if (a[i] != b[i]) cudaEventElapsedTime(&ms, c->evStage[a[i]], c->evStage[b[i]]);
+      if (a[i] == b[i]) continue;  // slot 5 belongs to orbx_stream_score_models
+      cudaEventElapsedTime(&ms, c->evStage[a[i]], c->evStage[b[i]]);
       c->stageMs[i] = ms;
     }
     cudaGetLastError();

@@ -171,3 +171,128 @@ extern "C" int orbx_descriptor_distance_batch(orbx_ctx* c, const uint8_t* a, con
   cudaFree(da); cudaFree(db); cudaFree(dout);
   return rc;
 }
+
+// ---- Initializer scoring -------------------------------------------------------------
+namespace {
+size_t up256(size_t b) { return (b + 255) & ~(size_t)255; }
+int score_reserve(orbx_ctx* c, size_t bytes) {
+  if (bytes <= c->scoreBytes) return ORBX_OK;
+  if (c->dScore) cudaFree(c->dScore);
+  c->dScore = nullptr; c->scoreBytes = 0;
+  CU(c, cudaMalloc(&c->dScore, bytes));
+  c->scoreBytes = bytes;
+  return ORBX_OK;
+}
+// invSigmaSquare = 1.0 / (sigma * sigma): float product, double division, narrowed (Initializer.cpp:293,376)
+float inv_sigma_square(float sigma) { const float s2 = sigma * sigma; return (float)(1.0 / (double)s2); }
+
+// one model kind over nPairs pairs whose frames / matches are already on the device; host in / out
+int score_run(orbx_ctx* c, ScoreArgs S, int nPairs, bool fund, const float* hA, const float* hB, float* scores, int* best,
+              int* nList, uint8_t* inlAll, int listLen, uint8_t* inlBest, int cap) {
+  const size_t nh = (size_t)nPairs * S.nHyp;
+  if ((size_t)S.stride * 16 + (size_t)S.nHyp * 4 > 200 * 1024) return ORBX_ERR_CAPACITY;
+  const size_t oA = 0, oB = oA + up256(nh * 36), oS = oB + up256(nh * 36), oBest = oS + up256(nh * 4),
+               oN = oBest + up256((size_t)nPairs * 4), oIB = oN + up256((size_t)nPairs * 4),
+               oIA = oIB + up256((size_t)nPairs * S.stride), total = oIA + (inlAll ? up256(nh * (size_t)listLen) : 0);
+  int rc = score_reserve(c, total);
+  if (rc) return rc;
+  cudaStream_t st = c->stream;
+  u8* d = c->dScore;
+  CU(c, cudaMemcpyAsync(d + oA, hA, nh * 36, cudaMemcpyHostToDevice, st));
+  if (!fund) CU(c, cudaMemcpyAsync(d + oB, hB, nh * 36, cudaMemcpyHostToDevice, st));
+  S.hypA = reinterpret_cast<const float*>(d + oA);
+  S.hypB = reinterpret_cast<const float*>(d + oB);
+  S.scores = reinterpret_cast<float*>(d + oS);
+  S.best = reinterpret_cast<int*>(d + oBest);
+  S.nList = reinterpret_cast<int*>(d + oN);
+  S.inlBest = inlBest ? d + oIB : nullptr;
+  S.inlAll = inlAll ? d + oIA : nullptr;
+  if (c->stageTiming) cudaEventRecord(c->evStage[8], st);
+  c->launches = launch_score_models(S, nPairs, fund, st);
+  CU(c, cudaGetLastError());
+  if (c->stageTiming) cudaEventRecord(c->evStage[9], st);
+  if (scores) CU(c, cudaMemcpyAsync(scores, d + oS, nh * 4, cudaMemcpyDeviceToHost, st));
+  if (best) CU(c, cudaMemcpyAsync(best, d + oBest, (size_t)nPairs * 4, cudaMemcpyDeviceToHost, st));
+  if (nList) CU(c, cudaMemcpyAsync(nList, d + oN, (size_t)nPairs * 4, cudaMemcpyDeviceToHost, st));
+  if (inlAll && nh * (size_t)listLen) CU(c, cudaMemcpyAsync(inlAll, d + oIA, nh * (size_t)listLen, cudaMemcpyDeviceToHost, st));
+  if (inlBest)
+    CU(c, cudaMemcpy2DAsync(inlBest, (size_t)cap, d + oIB, (size_t)S.stride, (size_t)std::min(cap, S.stride), nPairs,
+                            cudaMemcpyDeviceToHost, st));
+  CU(c, cudaStreamSynchronize(st));
+  if (c->stageTiming) {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, c->evStage[8], c->evStage[9]);
+    c->stageMs[5] += ms;
+  }
+  return ORBX_OK;
+}
+
+// host frames of one pair -> staging slots 0 / 1; returns the list length in *listLen
+int score_stage(orbx_ctx* c, const orbx_keypoint* k1, int n1, const orbx_keypoint* k2, int n2, const int* m12, int* listLen) {
+  if (!c || n1 < 0 || n2 < 0 || (n1 > 0 && (!k1 || !m12)) || (n2 > 0 && !k2)) return ORBX_ERR_ARG;
+  if (n1 > c->hfCap || n2 > c->hfCap) return ORBX_ERR_CAPACITY;
+  int N = 0;
+  for (int i = 0; i < n1; ++i) {
+    if (m12[i] >= n2) return ORBX_ERR_ARG;
+    N += m12[i] >= 0;
+  }
+  *listLen = N;
+  CU(c, cudaSetDevice(c->device));
+  cudaStream_t st = c->stream;
+  const size_t cap = (size_t)c->hfCap;
+  const int n[2] = {n1, n2};
+  if (n1) {
+    CU(c, cudaMemcpyAsync(c->hfKeys, k1, (size_t)n1 * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, st));
+    CU(c, cudaMemcpyAsync(c->hfMatches, m12, (size_t)n1 * sizeof(int), cudaMemcpyHostToDevice, st));
+  }
+  if (n2) CU(c, cudaMemcpyAsync(c->hfKeys + cap, k2, (size_t)n2 * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, st));
+  CU(c, cudaMemcpyAsync(c->hfN, n, sizeof(n), cudaMemcpyHostToDevice, st));
+  CU(c, cudaStreamSynchronize(st));  // n[] lives on this stack frame
+  return ORBX_OK;
+}
+ScoreArgs host_pair_args(orbx_ctx* c, int nHyp, float sigma) {
+  ScoreArgs S{};
+  S.keysUn = c->hfKeys; S.n = c->hfN; S.stride = c->hfCap; S.pairStep = 2; S.matches12 = c->hfMatches;
+  S.nHyp = nHyp; S.invSigmaSquare = inv_sigma_square(sigma);
+  return S;
+}
+}  // namespace
+
+extern "C" int orbx_check_homography(orbx_ctx* c, const orbx_keypoint* kps1_un, int n1, const orbx_keypoint* kps2_un, int n2,
+                                     const int* matches12, const float* H21, const float* H12, int n_hyp, float sigma,
+                                     float* scores, uint8_t* inliers, int* n_list, int* best) {
+  if (!c || n_hyp < 1 || !H21 || !H12) return ORBX_ERR_ARG;
+  int N = 0;
+  int rc = score_stage(c, kps1_un, n1, kps2_un, n2, matches12, &N);
+  if (rc) return rc;
+  return score_run(c, host_pair_args(c, n_hyp, sigma), 1, false, H21, H12, scores, best, n_list, inliers, N, nullptr, 0);
+}
+
+extern "C" int orbx_check_fundamental(orbx_ctx* c, const orbx_keypoint* kps1_un, int n1, const orbx_keypoint* kps2_un, int n2,
+                                      const int* matches12, const float* F21, int n_hyp, float sigma, float* scores,
+                                      uint8_t* inliers, int* n_list, int* best) {
+  if (!c || n_hyp < 1 || !F21) return ORBX_ERR_ARG;
+  int N = 0;
+  int rc = score_stage(c, kps1_un, n1, kps2_un, n2, matches12, &N);
+  if (rc) return rc;
+  return score_run(c, host_pair_args(c, n_hyp, sigma), 1, true, F21, nullptr, scores, best, n_list, inliers, N, nullptr, 0);
+}
+
+extern "C" int orbx_stream_score_models(orbx_ctx* c, int n_pairs, const float* H21, const float* H12, const float* F21,
+                                        int n_hyp, float sigma, float* scores_h, float* scores_f, int* best_h, int* best_f,
+                                        uint8_t* inliers_h, uint8_t* inliers_f, int cap, int* n_list) {
+  if (!c || n_pairs < 1 || n_hyp < 1 || (H21 && !H12) || (!H21 && !F21)) return ORBX_ERR_ARG;
+  if (2 * n_pairs > c->lastBatch) return ORBX_ERR_STATE;  // the pairs must be resident from the last stream run
+  if ((inliers_h || inliers_f) && cap < 1) return ORBX_ERR_ARG;
+  CU(c, cudaSetDevice(c->device));
+  const Params& P = c->P;
+  ScoreArgs S{};
+  S.keysUn = P.keysUn; S.n = P.outN; S.stride = P.kpStride; S.pairStep = 2; S.matches12 = c->dMatches12;
+  S.nHyp = n_hyp; S.invSigmaSquare = inv_sigma_square(sigma);
+  int rc = ORBX_OK;
+  c->stageMs[5] = 0.f;
+  if (H21) rc = score_run(c, S, n_pairs, false, H21, H12, scores_h, best_h, n_list, nullptr, 0, inliers_h, cap);
+  if (rc) return rc;
+  if (F21) rc = score_run(c, S, n_pairs, true, F21, nullptr, scores_f, best_f, n_list, nullptr, 0, inliers_f, cap);
+  return rc;
+}

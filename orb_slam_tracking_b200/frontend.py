@@ -187,6 +187,36 @@ class ORBmatcher:
         return int(lib().orbx_descriptor_distance(ptr(a), ptr(b)))
 
 
+class Initializer:
+    """The scoring half of the reference's Initializer (Initialization/Initializer.hpp:57-85): CheckHomography and
+    CheckFundamental over a set of hypotheses, and the selection rule of the RANSAC loops around them.  Estimating
+    the hypotheses (cv::findHomography / findFundamentalMat in the reference) stays with the caller."""
+
+    def __init__(self, referenceFrame, sigma=1.0, iterations=200):
+        self.ex = referenceFrame.ex
+        self.mvKeys1 = referenceFrame.mvKeysUn
+        self.mSigma, self.mMaxIterations = sigma, iterations
+
+    def _run(self, fn, currentFrame, matches12, mats):
+        m12 = np.ascontiguousarray(matches12, np.int32)
+        k2 = np.ascontiguousarray(currentFrame.mvKeysUn, KP_DTYPE)
+        mats = [np.ascontiguousarray(M, np.float32).reshape(-1, 9) for M in mats]
+        nh, N = len(mats[0]), int((m12 >= 0).sum())
+        scores, inl = np.zeros(nh, np.float32), np.zeros((nh, N), np.uint8)
+        nl, best = C.c_int(0), C.c_int(0)
+        check(fn(self.ex._h, ptr(self.mvKeys1), len(self.mvKeys1), ptr(k2), len(k2), ptr(m12), *[ptr(M) for M in mats], nh,
+                 self.mSigma, ptr(scores), ptr(inl), C.addressof(nl), C.addressof(best)), self.ex._h)
+        assert nl.value == N
+        return scores, inl, best.value
+
+    def CheckHomography(self, currentFrame, matches12, H21, H12):
+        """-> (scores[nHyp], vbMatchesInliers[nHyp, N], best)"""
+        return self._run(lib().orbx_check_homography, currentFrame, matches12, [H21, H12])
+
+    def CheckFundamental(self, currentFrame, matches12, F21):
+        return self._run(lib().orbx_check_fundamental, currentFrame, matches12, [F21])
+
+
 class Stream:
     """Batch of frames kept in HBM from image to match list (orbx_stream_*)."""
 
@@ -241,4 +271,22 @@ class Stream:
         check(lib().orbx_stream_process(self.ex._h, ptr(imgs), n, self.nnratio, int(self.checkOri), self.window, chunk,
                                         ptr(out.get("kps")), ptr(out.get("kps_un")), ptr(out.get("desc")), cap, ptr(out["n"]),
                                         ptr(out["matches12"]), ptr(out["nmatches"]), ptr(out["counters"])), self.ex._h)
+        return out
+
+    def score_models(self, n_pairs, H21=None, H12=None, F21=None, sigma=1.0):
+        """CheckHomography / CheckFundamental for [n_pairs, n_hyp, 9] hypothesis sets on the resident pairs."""
+        cap = self.ex.cap
+        mats = {k: (None if M is None else np.ascontiguousarray(M, np.float32).reshape(n_pairs, -1, 9))
+                for k, M in (("H21", H21), ("H12", H12), ("F21", F21))}
+        nh = (mats["H21"] if mats["H21"] is not None else mats["F21"]).shape[1]
+        out = {"n_list": np.zeros(n_pairs, np.int32)}
+        for m in ("h", "f"):
+            on = mats["H21" if m == "h" else "F21"] is not None
+            out["scores_" + m] = np.zeros((n_pairs, nh), np.float32) if on else None
+            out["best_" + m] = np.zeros(n_pairs, np.int32) if on else None
+            out["inliers_" + m] = np.zeros((n_pairs, cap), np.uint8) if on else None
+        check(lib().orbx_stream_score_models(self.ex._h, n_pairs, ptr(mats["H21"]), ptr(mats["H12"]), ptr(mats["F21"]), nh,
+                                             sigma, ptr(out["scores_h"]), ptr(out["scores_f"]), ptr(out["best_h"]),
+                                             ptr(out["best_f"]), ptr(out["inliers_h"]), ptr(out["inliers_f"]), cap,
+                                             ptr(out["n_list"])), self.ex._h)
         return out
