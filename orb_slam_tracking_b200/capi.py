@@ -62,6 +62,8 @@ SIGNATURES = {
     "orbx_stream_run": (ci, [vp, ci, cf, ci, ci]),
     "orbx_stream_download": (ci, [vp, ci, vp, vp, vp, ci, vp, vp, vp, vp]),
     "orbx_stream_process": (ci, [vp, vp, ci, cf, ci, ci, ci, vp, vp, vp, ci, vp, vp, vp, vp]),
+    "orbx_stream_process_async": (ci, [vp, vp, ci, cf, ci, ci, ci, vp, vp, vp, ci, vp, vp, vp, vp]),
+    "orbx_stream_wait": (ci, [vp, ci]),
     "orbx_stream_sync": (ci, [vp]),
     "orbx_timer_start": (ci, [vp]),
     "orbx_timer_stop": (ci, [vp, vp]),

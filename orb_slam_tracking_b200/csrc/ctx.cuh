@@ -32,14 +32,18 @@ struct orbx_ctx {
   orbx::TmaMaps tma;               // per-level tensor maps over P.pyr (k_fast tile staging)
   int device;
   cudaStream_t stream;
-  cudaStream_t sAlt;               // second compute stream: odd chunks of orbx_stream_process
-  cudaStream_t sSide[2];           // blur runs here, beside FAST + quadtree of stream / sAlt
-  cudaEvent_t evFork[2], evJoin[2], evHalf;
+  static constexpr int kLanes = 4;
+  cudaStream_t sLane[kLanes];      // compute lanes: [0] = stream; chunks of orbx_stream_process / parts of orbx_stream_run rotate over them
+  cudaStream_t sSide[kLanes];      // blur runs here, beside the quadtree of the same lane
+  cudaEvent_t evFork[kLanes], evJoin[kLanes], evLane[kLanes];
   cudaStream_t sH2D, sD2H;         // copy streams of the pipelined host path (orbx_stream_process)
-  std::vector<cudaEvent_t> evChunk; // 2 per chunk: images landed, results ready
+  std::vector<cudaEvent_t> evChunk; // 4 per chunk: images landed, kernels done, staging consumed, results on the host
   orbx::u8* dIngest;               // dense [maxBatch][H][W] staging of uploaded frames
   orbx::u8* dIngestColor;          // dense [maxBatch][H][W][3], allocated on the first colour upload
-  int* hStatus;                    // pinned [maxBatch]
+  int* hStatus;                    // pinned [2][maxBatch]: one block per step in flight
+  struct Flight { int active, n, chunk; } flight[2];  // steps of orbx_stream_process_async not yet waited for
+  cudaEvent_t evDone[2];
+  int nextTicket;
   std::vector<void*> allocs;       // every cudaMalloc, freed in orbx_destroy
   std::vector<int*> dResizeTabs;   // per level (entry 0 unused)
   const int** hTabPtrs;            // host array of device pointers for launch_pyramid
@@ -72,3 +76,5 @@ struct orbx_ctx {
   cudaEvent_t evStage[10];
   float stageMs[8];
 };
+
+int drain_flights(orbx_ctx* c);

@@ -84,16 +84,18 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   c->device = device;
   CU(c, cudaSetDevice(device));
   CU(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-  CU(c, cudaStreamCreateWithFlags(&c->sAlt, cudaStreamNonBlocking));
-  CU(c, cudaEventCreateWithFlags(&c->evHalf, cudaEventDisableTiming));
-  for (int i = 0; i < 2; ++i) {
+  c->sLane[0] = c->stream;
+  for (int i = 0; i < orbx_ctx::kLanes; ++i) {
+    if (i) CU(c, cudaStreamCreateWithFlags(&c->sLane[i], cudaStreamNonBlocking));
+    CU(c, cudaEventCreateWithFlags(&c->evLane[i], cudaEventDisableTiming));
     CU(c, cudaStreamCreateWithFlags(&c->sSide[i], cudaStreamNonBlocking));
     CU(c, cudaEventCreateWithFlags(&c->evFork[i], cudaEventDisableTiming));
     CU(c, cudaEventCreateWithFlags(&c->evJoin[i], cudaEventDisableTiming));
   }
   CU(c, cudaStreamCreateWithFlags(&c->sH2D, cudaStreamNonBlocking));
   CU(c, cudaStreamCreateWithFlags(&c->sD2H, cudaStreamNonBlocking));
-  CU(c, cudaHostAlloc((void**)&c->hStatus, (size_t)maxBatch * sizeof(int), cudaHostAllocDefault));
+  CU(c, cudaHostAlloc((void**)&c->hStatus, 2 * (size_t)maxBatch * sizeof(int), cudaHostAllocDefault));
+  for (int i = 0; i < 2; ++i) CU(c, cudaEventCreateWithFlags(&c->evDone[i], cudaEventDisableTiming));
   CU(c, cudaEventCreate(&c->evStart));
   CU(c, cudaEventCreate(&c->evStop));
   for (int i = 0; i < 10; ++i) CU(c, cudaEventCreate(&c->evStage[i]));
@@ -172,9 +174,11 @@ extern "C" orbx_ctx* orbx_create(int device, int width, int height, int nfeature
                                  int ini_th_fast, int min_th_fast, int max_batch, int* status) {
   orbx_ctx* c = new (std::nothrow) orbx_ctx();
   if (!c) { if (status) *status = ORBX_ERR_ARG; return nullptr; }
-  c->stream = nullptr; c->sH2D = c->sD2H = c->sAlt = nullptr;
-  for (int i = 0; i < 2; ++i) { c->sSide[i] = nullptr; c->evFork[i] = c->evJoin[i] = nullptr; }
-  c->evHalf = nullptr; c->dIngest = nullptr; c->dIngestColor = nullptr; c->hStatus = nullptr; c->hTabPtrs = nullptr; c->launches = 0; c->cameraSet = 0; c->lastBatch = 0; c->dScore = nullptr; c->scoreBytes = 0;
+  c->stream = nullptr; c->sH2D = c->sD2H = nullptr;
+  for (int i = 0; i < orbx_ctx::kLanes; ++i) { c->sLane[i] = c->sSide[i] = nullptr; c->evFork[i] = c->evJoin[i] = c->evLane[i] = nullptr; }
+  c->dIngest = nullptr; c->dIngestColor = nullptr; c->hStatus = nullptr; c->hTabPtrs = nullptr; c->launches = 0; c->cameraSet = 0; c->lastBatch = 0; c->dScore = nullptr; c->scoreBytes = 0;
+  for (int i = 0; i < 2; ++i) { c->flight[i].active = 0; c->flight[i].n = 0; c->flight[i].chunk = 0; c->evDone[i] = nullptr; }
+  c->nextTicket = 0;
   c->stageTiming = 0; c->evStart = c->evStop = nullptr;
   for (int i = 0; i < 10; ++i) c->evStage[i] = nullptr;
   std::memset(c->stageMs, 0, sizeof(c->stageMs));
@@ -198,13 +202,14 @@ extern "C" void orbx_destroy(orbx_ctx* c) {
   for (int i = 0; i < 10; ++i) if (c->evStage[i]) cudaEventDestroy(c->evStage[i]);
   for (cudaEvent_t e : c->evChunk) cudaEventDestroy(e);
   if (c->hStatus) cudaFreeHost(c->hStatus);
-  for (int i = 0; i < 2; ++i) {
+  for (int i = 0; i < 2; ++i) if (c->evDone[i]) cudaEventDestroy(c->evDone[i]);
+  for (int i = 0; i < orbx_ctx::kLanes; ++i) {
     if (c->sSide[i]) cudaStreamDestroy(c->sSide[i]);
     if (c->evFork[i]) cudaEventDestroy(c->evFork[i]);
     if (c->evJoin[i]) cudaEventDestroy(c->evJoin[i]);
+    if (c->evLane[i]) cudaEventDestroy(c->evLane[i]);
+    if (i && c->sLane[i]) cudaStreamDestroy(c->sLane[i]);
   }
-  if (c->evHalf) cudaEventDestroy(c->evHalf);
-  if (c->sAlt) cudaStreamDestroy(c->sAlt);
   if (c->sH2D) cudaStreamDestroy(c->sH2D);
   if (c->sD2H) cudaStreamDestroy(c->sD2H);
   if (c->stream) cudaStreamDestroy(c->stream);

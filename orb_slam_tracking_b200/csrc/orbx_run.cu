@@ -8,6 +8,20 @@
 
 using namespace orbx;
 
+// Waits for every step of orbx_stream_process_async still in flight (entry points that touch the slot arrays call it
+// first).  Returns the worst device-side status of those steps.
+int drain_flights(orbx_ctx* c) {
+  int worst = 0;
+  for (int t = 0; t < 2; ++t) {
+    if (!c->flight[t].active) continue;
+    CU(c, cudaEventSynchronize(c->evDone[t]));
+    c->flight[t].active = 0;
+    for (int i = 0; i < c->flight[t].n; ++i) worst = std::min(worst, c->hStatus[(size_t)t * c->P.maxBatch + i]);
+  }
+  if (worst) c->err = "device-side status " + std::to_string(worst);
+  return worst;
+}
+
 namespace {
 
 enum { ST_PYR = 0, ST_FAST, ST_QUAD, ST_BLUR, ST_DESC, ST_PACK, ST_GLUE, ST_MATCH, ST_N };
@@ -47,7 +61,8 @@ int enqueue_extract(orbx_ctx* c, const Params& P, int n, int lap0, int lap1, cud
   // the blur only needs the pyramid: it runs on a side stream next to the quadtree (latency-bound, a third of the
   // issue slots; the blur is issue-bound, so they share the SMs well) and joins before the descriptors.  With per-stage timing on,
   // everything stays on one stream so that the stage events bracket one kernel each.
-  const int side = (st == c->sAlt) ? 1 : 0;
+  int side = 0;
+  for (int i = 1; i < orbx_ctx::kLanes; ++i) if (st == c->sLane[i]) side = i;
   static const bool singleStream = std::getenv("ORBX_SINGLE_STREAM") != nullptr;
   const bool fork = !c->stageTiming && !singleStream;
   c->launches += launch_fast(P, c->tma, n, st);
@@ -268,19 +283,26 @@ extern "C" int orbx_stream_run(orbx_ctx* c, int n_img, float nnratio, int check_
   c->launches = 0;
   int rc;
   static const bool single = std::getenv("ORBX_SINGLE_STREAM") != nullptr;  // profiling aid: whole-batch launches in order
-  if (n_img >= 128 && !c->stageTiming && !single) {
-    // two halves (each a whole number of pairs) on the two compute streams: the latency-bound kernels of one half
-    // (quadtree, matcher) overlap the issue-bound ones of the other; both halves fence on the context's stream
-    const int h = (n_img / 2) & ~1;
-    CU(c, cudaEventRecord(c->evFork[1], c->stream));
-    CU(c, cudaStreamWaitEvent(c->sAlt, c->evFork[1], 0));
-    const Params Q = shifted(c, h);
-    if ((rc = enqueue_extract(c, P, h, 0, 0, c->stream))) return rc;
-    if ((rc = enqueue_extract(c, Q, n_img - h, 0, 0, c->sAlt))) return rc;
-    if ((rc = enqueue_glue_match(c, P, h, 0, nnratio, check_orientation, window_size, c->stream))) return rc;
-    if ((rc = enqueue_glue_match(c, Q, n_img - h, h / 2, nnratio, check_orientation, window_size, c->sAlt))) return rc;
-    CU(c, cudaEventRecord(c->evHalf, c->sAlt));
-    CU(c, cudaStreamWaitEvent(c->stream, c->evHalf, 0));
+  static const int partsEnv = std::getenv("ORBX_RUN_PARTS") ? std::atoi(std::getenv("ORBX_RUN_PARTS")) : 0;
+  const int parts = std::min(orbx_ctx::kLanes, std::max(1, partsEnv > 0 ? partsEnv : 2));
+  if (n_img >= 64 * parts && parts > 1 && !c->stageTiming && !single) {
+    // the batch in `parts` pieces (each a whole number of pairs), one per compute lane: the latency-bound kernels of
+    // one piece (quadtree, matcher) overlap the issue-bound ones of the others; all pieces fence on the context's stream
+    CU(c, cudaEventRecord(c->evLane[0], c->stream));
+    int s0 = 0;
+    for (int k = 0; k < parts; ++k) {
+      const int s1 = k == parts - 1 ? n_img : (int)((long)n_img * (k + 1) / parts) & ~1;
+      cudaStream_t st = c->sLane[k];
+      if (k) CU(c, cudaStreamWaitEvent(st, c->evLane[0], 0));
+      const Params Q = shifted(c, s0);
+      if ((rc = enqueue_extract(c, Q, s1 - s0, 0, 0, st))) return rc;
+      if ((rc = enqueue_glue_match(c, Q, s1 - s0, s0 / 2, nnratio, check_orientation, window_size, st))) return rc;
+      if (k) {
+        CU(c, cudaEventRecord(c->evLane[k], st));
+        CU(c, cudaStreamWaitEvent(c->stream, c->evLane[k], 0));
+      }
+      s0 = s1;
+    }
     c->lastBatch = n_img;
     return ORBX_OK;
   }
@@ -291,6 +313,8 @@ extern "C" int orbx_stream_run(orbx_ctx* c, int n_img, float nnratio, int check_
 extern "C" int orbx_stream_sync(orbx_ctx* c) {
   if (!c) return ORBX_ERR_ARG;
   CU(c, cudaSetDevice(c->device));
+  const int flights = drain_flights(c);
+  if (flights) return flights;
   CU(c, cudaStreamSynchronize(c->stream));
   if (c->stageTiming) {
     static const int a[ST_N] = {0, 1, 2, 3, 4, 5, 5, 6}, b[ST_N] = {1, 2, 3, 4, 5, 5, 6, 7};
@@ -338,53 +362,74 @@ extern "C" int orbx_stream_download(orbx_ctx* c, int n_img, orbx_keypoint* kps, 
   return ORBX_OK;
 }
 
-// Host images in, results out, in one call: the batch is cut into chunks of `chunk` frames and the three
-// legs of each chunk run on their own streams -- H2D DMA of chunk k+1 and D2H DMA of chunk k-1 overlap the
-// kernels of chunk k.  imgs and the output buffers should be page-locked (orbx_host_alloc) for the copies
-// to be asynchronous.  Returns after everything has landed on the host.
-extern "C" int orbx_stream_process(orbx_ctx* c, const uint8_t* imgs, int n_img, float nnratio, int check_orientation,
-                                   int window_size, int chunk, orbx_keypoint* kps, orbx_keypoint* kps_un, uint8_t* desc,
-                                   int cap, int* n_out, int* matches12, int* nmatches, int* counters3) {
-  if (!c || !imgs || n_img < 1 || n_img > c->P.maxBatch) return ORBX_ERR_ARG;
-  if (!c->cameraSet) return ORBX_ERR_STATE;
-  if ((kps || kps_un || desc || matches12) && cap < 1) return ORBX_ERR_ARG;
+// Host images in, results out: the batch is cut into chunks of `chunk` frames and the three legs of each chunk run on
+// their own streams -- H2D DMA of chunk k+1 and D2H DMA of chunk k-1 overlap the kernels of chunk k.  imgs and the
+// output buffers should be page-locked (orbx_host_alloc) for the copies to be asynchronous.
+//
+// process_enqueue only enqueues; up to two steps may be in flight (orbx_stream_process_async / orbx_stream_wait), so that
+// the upload of step s+1 overlaps the kernels and the download of step s.  What keeps two steps apart on the device:
+//   * chunk j of every step runs on compute lane j % lanes: stream order separates its kernels from the previous step's;
+//   * the H2D stream waits for evIngested[j] (the previous step's k_ingest has consumed the staging area of chunk j);
+//   * the lane waits for evD2H[j] (the previous step's results of chunk j have left the device) before it overwrites them.
+// A step with another chunk schedule than the one in flight drains the pipeline first.
+namespace {
+
+
+int process_enqueue(orbx_ctx* c, const uint8_t* imgs, int n_img, float nnratio, int check_orientation, int window_size,
+                    int chunk, orbx_keypoint* kps, orbx_keypoint* kps_un, uint8_t* desc, int cap, int* n_out, int* matches12,
+                    int* nmatches, int* counters3, int ticket) {
   const Params& P = c->P;
-  CU(c, cudaSetDevice(c->device));
   if (chunk <= 0) chunk = 128;
   chunk = std::max(2, chunk & ~1);
   // chunk boundaries: a short first chunk (chunk / 4, then chunk / 2) so that the kernels start early, then `chunk`
   std::vector<int> cut(1, 0);
   for (int sz = std::max(2, (chunk / 4) & ~1); cut.back() < n_img; sz = std::min(chunk, 2 * sz)) cut.push_back(std::min(n_img, cut.back() + sz));
   const int nChunks = (int)cut.size() - 1;
-  while ((int)c->evChunk.size() < 2 * nChunks) {
+  if (c->flight[ticket ^ 1].active && (c->flight[ticket ^ 1].n != n_img || c->flight[ticket ^ 1].chunk != chunk)) {
+    const int rc = drain_flights(c);
+    if (rc) return rc;
+  }
+  while ((int)c->evChunk.size() < 4 * nChunks) {
     cudaEvent_t e;
     CU(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     c->evChunk.push_back(e);
   }
+  const bool chained = c->flight[ticket ^ 1].active != 0;  // the other step is still in flight with the same schedule
   const size_t imgBytes = (size_t)P.W * P.H;
   const int m = std::min(cap, P.kpStride);
   const size_t w = (size_t)m;
   const int timing = c->stageTiming;
   c->stageTiming = 0;  // per-stage events belong to the unchunked orbx_stream_run
   c->launches = 0;
+  int* hStatus = c->hStatus + (size_t)ticket * P.maxBatch;
+  static const int lanesEnv = std::getenv("ORBX_LANES") ? std::atoi(std::getenv("ORBX_LANES")) : 0;
+  const int lanes = std::min(orbx_ctx::kLanes, std::max(1, lanesEnv > 0 ? lanesEnv : 3));
   int rc = ORBX_OK;
+  if (!chained) {  // whatever the caller enqueued on the context's stream (orbx_stream_run ...) comes first
+    CU(c, cudaEventRecord(c->evLane[0], c->stream));
+    for (int i = 1; i < lanes; ++i) CU(c, cudaStreamWaitEvent(c->sLane[i], c->evLane[0], 0));
+    CU(c, cudaStreamWaitEvent(c->sH2D, c->evLane[0], 0));
+  }
   for (int k = 0; k < nChunks && rc == ORBX_OK; ++k) {
     const int s0 = cut[k], n = cut[k + 1] - s0, p0 = s0 / 2, np = n / 2;
-    cudaEvent_t evIn = c->evChunk[2 * k], evOut = c->evChunk[2 * k + 1];
+    cudaEvent_t evIn = c->evChunk[4 * k], evOut = c->evChunk[4 * k + 1], evIngested = c->evChunk[4 * k + 2], evD2H = c->evChunk[4 * k + 3];
+    if (chained) CU(c, cudaStreamWaitEvent(c->sH2D, evIngested, 0));
     CU(c, cudaMemcpyAsync(c->dIngest + s0 * imgBytes, imgs + s0 * imgBytes, n * imgBytes, cudaMemcpyHostToDevice, c->sH2D));
     CU(c, cudaEventRecord(evIn, c->sH2D));
-    // consecutive chunks alternate between two compute streams: the latency-bound tail of a chunk (quadtree,
-    // matcher: few CTAs) overlaps the bandwidth-heavy head of the next one; chunks touch disjoint slots
-    cudaStream_t sc = (k & 1) ? c->sAlt : c->stream;
+    // consecutive chunks rotate over the compute lanes: the latency-bound tail of a chunk (quadtree, matcher: few
+    // CTAs) overlaps the issue-bound head of the next ones; chunks touch disjoint slots
+    cudaStream_t sc = c->sLane[k % lanes];
     CU(c, cudaStreamWaitEvent(sc, evIn, 0));
+    if (chained) CU(c, cudaStreamWaitEvent(sc, evD2H, 0));
     const Params Q = shifted(c, s0);
     c->launches += launch_ingest(Q, c->dIngest + s0 * imgBytes, n, sc);
+    CU(c, cudaEventRecord(evIngested, sc));
     if ((rc = enqueue_extract(c, Q, n, 0, 0, sc))) break;
     if ((rc = enqueue_glue_match(c, Q, n, p0, nnratio, check_orientation, window_size, sc))) break;
     CU(c, cudaEventRecord(evOut, sc));
     cudaStream_t sd = c->sD2H;
     CU(c, cudaStreamWaitEvent(sd, evOut, 0));
-    CU(c, cudaMemcpyAsync(c->hStatus + s0, Q.status, n * sizeof(int), cudaMemcpyDeviceToHost, sd));
+    CU(c, cudaMemcpyAsync(hStatus + s0, Q.status, n * sizeof(int), cudaMemcpyDeviceToHost, sd));
     if (kps)
       CU(c, cudaMemcpy2DAsync(kps + (size_t)s0 * cap, (size_t)cap * sizeof(orbx_keypoint), Q.outKp,
                               (size_t)P.kpStride * sizeof(orbx_keypoint), w * sizeof(orbx_keypoint), n, cudaMemcpyDeviceToHost, sd));
@@ -402,21 +447,70 @@ extern "C" int orbx_stream_process(orbx_ctx* c, const uint8_t* imgs, int n_img, 
       if (nmatches) CU(c, cudaMemcpyAsync(nmatches + p0, c->dNMatches + p0, np * sizeof(int), cudaMemcpyDeviceToHost, sd));
       if (counters3) CU(c, cudaMemcpyAsync(counters3 + 3 * p0, c->dCounters + 3 * p0, np * 3 * sizeof(int), cudaMemcpyDeviceToHost, sd));
     }
+    CU(c, cudaEventRecord(evD2H, sd));
   }
   c->stageTiming = timing;
-  cudaStreamSynchronize(c->sD2H);
-  cudaStreamSynchronize(c->stream);
-  cudaStreamSynchronize(c->sAlt);
-  cudaStreamSynchronize(c->sSide[0]);
-  cudaStreamSynchronize(c->sSide[1]);
-  cudaStreamSynchronize(c->sH2D);
-  if (rc) return rc;
-  CU(c, cudaGetLastError());
+  // the D2H stream is serial and each of its copies waits for its chunk's kernels: its last event fences the whole step.
+  // The context's stream (lane 0) joins it, so work enqueued on it later -- and orbx_timer_stop -- comes after the step.
+  CU(c, cudaEventRecord(c->evDone[ticket], c->sD2H));
+  CU(c, cudaStreamWaitEvent(c->stream, c->evDone[ticket], 0));
+  c->flight[ticket].active = 1; c->flight[ticket].n = n_img; c->flight[ticket].chunk = chunk;
+  if (rc) { drain_flights(c); return rc; }
   c->lastBatch = n_img;
+  return ORBX_OK;
+}
+
+int wait_ticket(orbx_ctx* c, int ticket) {
+  if (!c->flight[ticket].active) return ORBX_OK;
+  CU(c, cudaEventSynchronize(c->evDone[ticket]));
+  c->flight[ticket].active = 0;
+  CU(c, cudaGetLastError());
   int worst = 0;
-  for (int i = 0; i < n_img; ++i) worst = std::min(worst, c->hStatus[i]);
+  const int* hStatus = c->hStatus + (size_t)ticket * c->P.maxBatch;
+  for (int i = 0; i < c->flight[ticket].n; ++i) worst = std::min(worst, hStatus[i]);
   if (worst) c->err = "device-side status " + std::to_string(worst);
   return worst;
+}
+
+}  // namespace
+
+extern "C" int orbx_stream_process(orbx_ctx* c, const uint8_t* imgs, int n_img, float nnratio, int check_orientation,
+                                   int window_size, int chunk, orbx_keypoint* kps, orbx_keypoint* kps_un, uint8_t* desc,
+                                   int cap, int* n_out, int* matches12, int* nmatches, int* counters3) {
+  if (!c || !imgs || n_img < 1 || n_img > c->P.maxBatch) return ORBX_ERR_ARG;
+  if (!c->cameraSet) return ORBX_ERR_STATE;
+  if ((kps || kps_un || desc || matches12) && cap < 1) return ORBX_ERR_ARG;
+  CU(c, cudaSetDevice(c->device));
+  int rc = drain_flights(c);
+  if (rc) return rc;
+  rc = process_enqueue(c, imgs, n_img, nnratio, check_orientation, window_size, chunk, kps, kps_un, desc, cap, n_out, matches12,
+                       nmatches, counters3, 0);
+  if (rc) return rc;
+  return wait_ticket(c, 0);
+}
+
+// Streaming form: returns a ticket (0 or 1) as soon as the step is enqueued; at most two steps are in flight, and the
+// caller owns two sets of output buffers.  orbx_stream_wait(ticket) blocks until that step's results are on the host.
+extern "C" int orbx_stream_process_async(orbx_ctx* c, const uint8_t* imgs, int n_img, float nnratio, int check_orientation,
+                                         int window_size, int chunk, orbx_keypoint* kps, orbx_keypoint* kps_un, uint8_t* desc,
+                                         int cap, int* n_out, int* matches12, int* nmatches, int* counters3) {
+  if (!c || !imgs || n_img < 1 || n_img > c->P.maxBatch) return ORBX_ERR_ARG;
+  if (!c->cameraSet) return ORBX_ERR_STATE;
+  if ((kps || kps_un || desc || matches12) && cap < 1) return ORBX_ERR_ARG;
+  CU(c, cudaSetDevice(c->device));
+  const int ticket = c->nextTicket;
+  if (c->flight[ticket].active) return ORBX_ERR_STATE;  // wait for this ticket first
+  const int rc = process_enqueue(c, imgs, n_img, nnratio, check_orientation, window_size, chunk, kps, kps_un, desc, cap, n_out,
+                                 matches12, nmatches, counters3, ticket);
+  if (rc) return rc;
+  c->nextTicket = ticket ^ 1;
+  return ticket;
+}
+
+extern "C" int orbx_stream_wait(orbx_ctx* c, int ticket) {
+  if (!c || ticket < 0 || ticket > 1) return ORBX_ERR_ARG;
+  CU(c, cudaSetDevice(c->device));
+  return wait_ticket(c, ticket);
 }
 
 // ---- timing ---------------------------------------------------------------------------------------

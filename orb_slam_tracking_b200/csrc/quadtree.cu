@@ -14,6 +14,8 @@
 //    input order" (:984-1007) is an atomicMax over (response, ~emission order) keys;
 //  * the tie order of std::sort (unstable, observable -- SURVEY.md 7.3-1) is replayed by one thread
 //    with stdsort_emul(); everything else in a pass is CTA-parallel.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace orbx {
@@ -256,7 +258,9 @@ int launch_quadtree(const Params& P, int nSlots, cudaStream_t st) {
   for (int l = 0; l < P.nlevels; ++l) q = q > P.lv[l].quota ? q : P.lv[l].quota;
   const int sortCap = 2 * q < 256 ? 256 : (2 * q > 4096 ? 4096 : 2 * q);
   const size_t smem = (size_t)sortCap * sizeof(u64);
-  if (q < 400) k_quadtree<64><<<grid, 64, smem, st>>>(P, sortCap);
+  // small quotas: 64-thread CTAs give the best throughput when thousands of them share the GPU (whole batches); a chunk of
+  // the pipelined host path has few CTAs and waits for the slowest one (level 0), where 256 threads cut the latency by a third
+  if (q < 400 && nSlots > 128) k_quadtree<64><<<grid, 64, smem, st>>>(P, sortCap);
   else if (q < 1000) k_quadtree<256><<<grid, 256, smem, st>>>(P, sortCap);
   else k_quadtree<512><<<grid, 512, smem, st>>>(P, sortCap);
   return 1;

@@ -273,6 +273,32 @@ class Stream:
                                         ptr(out["matches12"]), ptr(out["nmatches"]), ptr(out["counters"])), self.ex._h)
         return out
 
+    def process_async(self, imgs, chunk=0, full=True):
+        """Streaming form (orbx_stream_process_async): returns a ticket; `wait(ticket)` returns that step's results.  Two
+        steps may be in flight, so the upload of one overlaps the kernels and the download of the other."""
+        imgs = np.ascontiguousarray(imgs, np.uint8)
+        assert imgs.shape[1:] == (self.ex.height, self.ex.width)
+        n, cap = imgs.shape[0], self.ex.cap
+        out = {"n": np.zeros(n, np.int32), "nmatches": np.zeros(max(n // 2, 1), np.int32),
+               "counters": np.zeros((max(n // 2, 1), 3), np.int32),
+               "matches12": np.full((max(n // 2, 1), cap), -1, np.int32)}
+        if full:
+            out["kps"] = np.zeros((n, cap), KP_DTYPE)
+            out["kps_un"] = np.zeros((n, cap), KP_DTYPE)
+            out["desc"] = np.zeros((n, cap, 32), np.uint8)
+        t = check(lib().orbx_stream_process_async(self.ex._h, ptr(imgs), n, self.nnratio, int(self.checkOri), self.window, chunk,
+                                                  ptr(out.get("kps")), ptr(out.get("kps_un")), ptr(out.get("desc")), cap,
+                                                  ptr(out["n"]), ptr(out["matches12"]), ptr(out["nmatches"]),
+                                                  ptr(out["counters"])), self.ex._h)
+        if not hasattr(self, "_flight"):
+            self._flight = {}
+        self._flight[t] = (imgs, out)   # the buffers stay alive until the step has been waited for
+        return t
+
+    def wait(self, ticket):
+        check(lib().orbx_stream_wait(self.ex._h, ticket), self.ex._h)
+        return self._flight.pop(ticket)[1]
+
     def score_models(self, n_pairs, H21=None, H12=None, F21=None, sigma=1.0):
         """CheckHomography / CheckFundamental for [n_pairs, n_hyp, 9] hypothesis sets on the resident pairs."""
         cap = self.ex.cap

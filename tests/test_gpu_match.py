@@ -216,3 +216,54 @@ def test_stream_process_chunked(fe, oracle, synth, chunk):
         for k in ("nmatches", "counters", "matches12"):
             assert np.array_equal(out[k][:n // 2], ref[k][:n // 2]), (k, n)
     E.close()
+
+
+def test_stream_process_async_two_in_flight(fe, oracle, synth):
+    """orbx_stream_process_async: two steps in flight (upload of one over the kernels / download of the other) return
+    exactly what the synchronous call returns, also when the schedule changes between steps and after other calls."""
+    W, H, nf, B = 640, 480, 1000, 12
+    K4, D4 = synth.camera_for(W, H)
+    E = fe.ORBextractor(nf, 1.2, 8, 20, 7, W, H, max_batch=B)
+    E.set_camera(K4, D4)
+    S = fe.Stream(E, 0.9, True, 100)
+    sets = [synth.frames(B, W, H, first_pair=70 + 6 * i) for i in range(4)]
+    want = [S.process(x, chunk=4) for x in sets]
+
+    def same(a, b, n):
+        for k in ("n", "kps", "kps_un", "desc"):
+            assert np.array_equal(a[k][:n].view(np.uint8), b[k][:n].view(np.uint8)), k
+        for k in ("nmatches", "counters", "matches12"):
+            assert np.array_equal(a[k][:n // 2], b[k][:n // 2]), k
+
+    # a stream of steps, always two in flight
+    order = [0, 1, 2, 3, 0, 2, 1, 3]
+    tickets = []
+    for i, j in enumerate(order):
+        tickets.append((S.process_async(sets[j], chunk=4), j))
+        if len(tickets) == 2:
+            t, jj = tickets.pop(0)
+            same(S.wait(t), want[jj], B)
+    t, jj = tickets.pop(0)
+    same(S.wait(t), want[jj], B)
+    # a third step without waiting is refused
+    t0 = S.process_async(sets[0], chunk=4)
+    t1 = S.process_async(sets[1], chunk=4)
+    with pytest.raises(Exception):
+        S.process_async(sets[2], chunk=4)
+    same(S.wait(t0), want[0], B)
+    same(S.wait(t1), want[1], B)
+    # a different schedule drains the pipeline first
+    t0 = S.process_async(sets[0], chunk=4)
+    o0 = S._flight[t0][1]
+    t1 = S.process_async(sets[1][:6], chunk=2)
+    same(o0, want[0], B)            # already complete: the second call had to wait for it
+    same(S.wait(t1), want[1], 6)
+    same(S.wait(t0), want[0], B)
+    # other entry points after in-flight steps are ordered behind them
+    t0 = S.process_async(sets[3], chunk=4)
+    S.upload(sets[2]); S.run(B)
+    got = S.download(B)
+    same(got, want[2], B)
+    same(S.wait(t0), want[3], B)
+    S.sync()
+    E.close()
