@@ -38,6 +38,7 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
   const int* ycoef = yofs + D.h;
   // lane constants
   int a0[4], a1[4], e0[4], e1[4];
+  u32 acoef[4], sel[4];
   int sx0 = 0;
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
@@ -46,38 +47,55 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
     if (k == 0) sx0 = sx;
     a0[k] = (short)(ac & 0xffff); a1[k] = ac >> 16;
     e0[k] = sx - sx0; e1[k] = min(sx + 1, S.w - 1) - sx0;
+    acoef[k] = (u32)ac;                                        // a0 | a1 << 16: the two 16-bit operands of dp2a
+    sel[k] = 0x4400u | (u32)(e0[k] & 7) | ((u32)(e1[k] & 7) << 4);  // bytes (S[sx], S[sx + 1], 0, 0) out of the 8-byte window
   }
   const int A = sx0 & ~3, sh = 8 * (sx0 & 3);
-  const u32 sel0 = (u32)e0[0] | ((u32)e0[1] << 4) | ((u32)e0[2] << 8) | ((u32)e0[3] << 12);
-  const u32 sel1 = (u32)e1[0] | ((u32)e1[1] << 4) | ((u32)e1[2] << 8) | ((u32)e1[3] << 12);
   const bool need3 = (sx0 & 3) + e1[3] >= 8;
   const u8* __restrict__ colp = src + A;
 
   // WIDE: scale factors above 2 spread a lane's taps over more than the 8 bytes the permutes can reach -> byte loads
-  // horizontally interpolated row r, pre-shifted: (S[sx] * a0 + S[sx + 1] * a1) >> 4
-  auto hrow = [&](int r, int (&hs)[4]) {
+  // horizontally interpolated row r, pre-shifted: (S[sx] * a0 + S[sx + 1] * a1) >> 4; the two taps are adjacent source
+  // bytes, so one byte permute puts them side by side and one dp2a (2 x u16 . 2 x u8) is the whole interpolation
+  auto hrow = [&](int r, u32 (&hs)[4]) {
     if (WIDE) {
       const u8* rowp = src + r * S.pitch + sx0;
 #pragma unroll
-      for (int k = 0; k < 4; ++k) hs[k] = (int)((u32)__ldg(rowp + e0[k]) * (u32)a0[k] + (u32)__ldg(rowp + e1[k]) * (u32)a1[k]) >> 4;
+      for (int k = 0; k < 4; ++k) hs[k] = ((u32)__ldg(rowp + e0[k]) * (u32)a0[k] + (u32)__ldg(rowp + e1[k]) * (u32)a1[k]) >> 4;
       return;
     }
     const u32* rp = reinterpret_cast<const u32*>(colp + r * S.pitch);
     const u32 w0 = __ldg(rp), w1 = __ldg(rp + 1), w2 = need3 ? __ldg(rp + 2) : 0u;
     const u32 q0 = __funnelshift_r(w0, w1, sh), q1 = __funnelshift_r(w1, w2, sh);
-    const u32 p0 = __byte_perm(q0, q1, sel0), p1 = __byte_perm(q0, q1, sel1);
 #pragma unroll
-    for (int k = 0; k < 4; ++k)
-      hs[k] = (int)(__byte_perm(p0, 0u, 0x4440u + k) * (u32)a0[k] + __byte_perm(p1, 0u, 0x4440u + k) * (u32)a1[k]) >> 4;
+    for (int k = 0; k < 4; ++k) {
+      u32 d;
+      asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(acoef[k]), "r"(__byte_perm(q0, q1, sel[k])), "r"(0u));
+      hs[k] = d >> 4;
+    }
   };
 
-  int hPrev[4] = {0, 0, 0, 0}, rPrev = -1;
+  u32 hPrev[4] = {0, 0, 0, 0};
+  int rPrev = -1;
   const int dyEnd = min(dy0 + rows, D.h);
+  {
+    // the strip's source rows are consumed one after the other (a dependent chain of loads per lane): pull its
+    // 128-byte lines into L2 up front, one line per lane and round
+    const int rFirst = min(max(__ldg(yofs + dy0), 0), S.h - 1), rLast = min(max(__ldg(yofs + dyEnd - 1) + 1, 0), S.h - 1);
+    const int xb = __shfl_sync(0xffffffffu, sx0, 0) & ~127;
+    const int nLines = (min(__shfl_sync(0xffffffffu, sx0 + e1[3], 31), S.pitch - 1) - xb) / 128 + 1;
+    const int total = (rLast - rFirst + 1) * nLines;
+    for (int i = lane; i < total; i += 32) {
+      const int r = i / nLines, ln = i - r * nLines;
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(src + (size_t)(rFirst + r) * S.pitch + xb + 128 * ln));
+    }
+  }
   for (int dy = dy0; dy < dyEnd; ++dy) {
     const int sy = __ldg(yofs + dy), bc = __ldg(ycoef + dy);
-    const int b0 = (short)(bc & 0xffff), b1 = bc >> 16;
+    // (b * h) >> 16 == umulhi(b << 16, h): coefficients are in [0, 2048], h < 2^15
+    const u32 B0 = (u32)(bc & 0xffff) << 16, B1 = (u32)bc & 0xffff0000u;
     const int r0 = min(max(sy, 0), S.h - 1), r1 = min(max(sy + 1, 0), S.h - 1);
-    int h0[4], h1[4];
+    u32 h0[4], h1[4];
     if (r0 == rPrev) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) h0[k] = hPrev[k];
@@ -93,8 +111,8 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
     u32 packed = 0;
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
-      const int v = (((b0 * h0[k]) >> 16) + ((b1 * h1[k]) >> 16) + 2) >> 2;
-      packed |= (u32)(v & 0xff) << (8 * k);
+      const u32 v = (__umulhi(B0, h0[k]) + __umulhi(B1, h1[k]) + 2u) >> 2;
+      packed |= (v & 0xffu) << (8 * k);
       hPrev[k] = h1[k];
     }
     rPrev = r1;
