@@ -85,13 +85,6 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) k_describe(const __grid_con
     const int x = (int)(xy & 0xffff), y = (int)(xy >> 16);
     const int xa = (x - kHalfPatch) & ~3;  // 9 aligned words cover [x-15, x+15]
     const u8* __restrict__ img = level_ptr((const u8*)P.pyr, P, slot, l) + (size_t)(y - kHalfPatch) * L.pitch + xa;
-    {  // phase 3 reads the 37 x 37 blurred patch of this keypoint: pull its lines into L2 now
-      const u8* bl = level_ptr((const u8*)P.blur, P, slot, l) + (size_t)(y - 18) * L.pitch + ((x - 18) & ~3);
-      for (int r = lane; r < kPatchRows; r += 32) {
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(bl + (size_t)r * L.pitch));
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(bl + (size_t)r * L.pitch + 4 * kPatchWords - 1));
-      }
-    }
     int m10 = 0, m01 = 0;
     // lanes 0..26 = 3 rows x 9 words; a lane keeps its word column, so its four column offsets u_j are fixed
     // and only the row's half-width d = umax[|v|] changes: byte j counts iff |u_j| <= d
