@@ -10,8 +10,8 @@
 // output, lanes 0 and 31 only carry the halo.  Walking down the rows, a lane loads its word (rows are
 // fetched 7 at a time so that the loads of a block are in flight together), takes the neighbouring words
 // from the adjacent lanes by shuffle, runs the row pass with funnel shifts and dp4a, and keeps the last 7
-// row-pass results of its 4 columns in registers for the column pass (symmetric taps: 3 adds + 4
-// multiply-adds per pixel).  BORDER_REFLECT_101 in x costs nothing in the loop: a word that touches or
+// row-pass results of its 4 columns in registers for the column pass (rows paired in 16-bit halves:
+// 3 dp2a + 1 multiply-add per pixel).  BORDER_REFLECT_101 in x costs nothing in the loop: a word that touches or
 // lies beyond the level's border is a lane-constant byte permutation of two aligned words inside the level.
 #include "common.cuh"
 
@@ -50,9 +50,13 @@ __global__ void __launch_bounds__(kBlurWarps * 32) k_blur(const __grid_constant_
   const bool emit = lane >= 1 && lane <= 30 && xw < L.w;
   constexpr u32 kA = 18u | (34u << 8) | (48u << 16) | (56u << 24);  // taps 0..3
   constexpr u32 kB = 48u | (34u << 8) | (18u << 16);                // taps 4..6 (+ one ignored byte)
-  u32 h[7][4];
+  // column pass window: the row-pass results (<= 65280, 16 bits) of consecutive rows are kept PAIRED per pixel,
+  // pr[q][j] = h(row q) | h(row q + 1) << 16, so that dp2a (2 x u16 . 2 x u8) applies two taps per instruction
+  constexpr u32 kT01 = 18u | (34u << 8), kT23 = 48u | (56u << 8), kT45 = 48u | (34u << 8);
+  u32 pr[5][4], hl[4];
 #pragma unroll
-  for (int k = 0; k < 7; ++k) { h[k][0] = h[k][1] = h[k][2] = h[k][3] = 0; }
+  for (int k = 0; k < 5; ++k) { pr[k][0] = pr[k][1] = pr[k][2] = pr[k][3] = 0; }
+  hl[0] = hl[1] = hl[2] = hl[3] = 0;
   const u8* __restrict__ colp = src + A;
   for (int rb = 0; rb < kTH + 6; rb += 7) {
     if (t.y0 + rb - 6 >= L.h) break;  // nothing left to emit in this strip
@@ -77,18 +81,24 @@ __global__ void __launch_bounds__(kBlurWarps * 32) k_blur(const __grid_constant_
       const u32 n1 = __dp4a(__funnelshift_r(w0, w1, 16), kA, __dp4a(__funnelshift_r(w1, w2, 16), kB, 0u));
       const u32 n2 = __dp4a(__funnelshift_r(w0, w1, 24), kA, __dp4a(__funnelshift_r(w1, w2, 24), kB, 0u));
       const u32 n3 = __dp4a(w1, kA, __dp4a(w2, kB, 0u));
-#pragma unroll
-      for (int q = 0; q < 6; ++q) { h[q][0] = h[q + 1][0]; h[q][1] = h[q + 1][1]; h[q][2] = h[q + 1][2]; h[q][3] = h[q + 1][3]; }
-      h[6][0] = n0; h[6][1] = n1; h[6][2] = n2; h[6][3] = n3;
+      const u32 nn[4] = {n0, n1, n2, n3};
       const int yo = t.y0 + rb + k - 6;
-      if (emit && rb + k >= 6 && yo < L.h) {
-        u32 px[4];
+      u32 px[4];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const u32 v = 18u * (h[0][j] + h[6][j]) + 34u * (h[1][j] + h[5][j]) + 48u * (h[2][j] + h[4][j]) + 56u * h[3][j] + 32768u;
-          px[j] = v >> 16;
-        }
-        *reinterpret_cast<u32*>(dst + yo * L.pitch + xw) = px[0] | (px[1] << 8) | (px[2] << 16) | (px[3] << 24);
+      for (int j = 0; j < 4; ++j) {
+        // rows 0..6 of the window = pr[0] (0,1), pr[2] (2,3), pr[4] (4,5) and the new row
+        u32 v;
+        asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(v) : "r"(pr[0][j]), "r"(kT01), "r"(18u * nn[j] + 32768u));
+        asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(v) : "r"(pr[2][j]), "r"(kT23), "r"(v));
+        asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(v) : "r"(pr[4][j]), "r"(kT45), "r"(v));
+        px[j] = v;  // < 2^24: the output pixel is byte 2
+        const u32 pn = __byte_perm(hl[j], nn[j], 0x5410);  // (previous row, new row)
+        pr[0][j] = pr[1][j]; pr[1][j] = pr[2][j]; pr[2][j] = pr[3][j]; pr[3][j] = pr[4][j]; pr[4][j] = pn;
+        hl[j] = nn[j];
+      }
+      if (emit && rb + k >= 6 && yo < L.h) {
+        *reinterpret_cast<u32*>(dst + yo * L.pitch + xw) =
+            __byte_perm(__byte_perm(px[0], px[1], 0x0062), __byte_perm(px[2], px[3], 0x0062), 0x5410);
       }
     }
   }
