@@ -47,7 +47,7 @@ constexpr int kPatchRows = 37, kPatchWords = 10;  // blurred patch [-18, 18]^2 s
 //      instruction stream of the kernel; a warp per keypoint would run them 32x redundantly).
 //   3. steered BRIEF, one warp per keypoint: the 37 x 37 blurred patch is staged into shared memory with
 //      coalesced word loads, then lane = descriptor byte gathers its 16 samples from shared memory.
-__global__ void __launch_bounds__(kWarpsPerCta * 32) k_describe(const __grid_constant__ Params P) {
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 6) k_describe(const __grid_constant__ Params P) {
   __shared__ float4 sPat[256];  // pattern pair (x0, y0, x1, y1) as floats, [i * 32 + byte]: conflict-free for lane = byte
   __shared__ u32 sDD[32];       // per patch row: 0x80808080 | umax[|v|] * 0x01010101 (byte-wise column limit of IC_Angle)
   __shared__ u32 sPatch[kWarpsPerCta][kPatchRows * kPatchWords];
