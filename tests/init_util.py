@@ -1,5 +1,7 @@
 """Synthetic inputs for the Initializer scoring tests: undistorted keys of two frames related by a homography plus
 noise and outliers, a match vector, and hypothesis sets around the true model (test infrastructure)."""
+from pathlib import Path
+
 import numpy as np
 
 from oracle.orb_oracle import KP_DTYPE
@@ -57,3 +59,7 @@ def same_scores(a, b):
     a, b = np.asarray(a, np.float32), np.asarray(b, np.float32)
     na, nb = np.isnan(a), np.isnan(b)
     return a.shape == b.shape and np.array_equal(na, nb) and np.array_equal(a[~na].view(np.uint32), b[~nb].view(np.uint32))
+
+
+def golden_scoring():
+    return np.load(Path(__file__).resolve().parent / "golden" / "init_scoring_demo.npz", allow_pickle=True)

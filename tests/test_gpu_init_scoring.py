@@ -6,7 +6,7 @@ hypothesis, the list length and the RANSAC selection (:205-209, :257-261), inclu
 import numpy as np
 import pytest
 
-from init_util import hypotheses, same_scores, scene
+from init_util import golden_scoring, hypotheses, same_scores, scene
 
 pytestmark = pytest.mark.gpu
 
@@ -98,4 +98,18 @@ def test_stream_score_models(fe, oracle):
     # one model at a time
     only = S.score_models(nP, F21=F21)
     assert only["scores_h"] is None and same_scores(only["scores_f"], res["scores_f"])
+    E.close()
+
+
+@pytest.mark.parametrize("tag,sigma", [("s10", 1.0), ("s5", 0.5)])
+def test_golden_demo_pair(fe, tag, sigma):
+    """CUDA against the committed outputs of the reference's own scoring bodies on its demo pair (no oracle involved)."""
+    g = golden_scoring()
+    E = fe.ORBextractor(2000, 1.2, 8, 0, 0, 752, 480)
+    I = fe.Initializer(_F(E, g["kps_un0"]), sigma, len(g["H21"]))
+    s, i, b = I.CheckHomography(_F(E, g["kps_un1"]), g["matches12"], g["H21"], g["H12"])
+    assert same_scores(s, g["scoresH_" + tag]) and np.array_equal(np.packbits(i, axis=1), g["inliersH_" + tag])
+    assert b == 0 or s[b] > s[0]
+    s, i, b = I.CheckFundamental(_F(E, g["kps_un1"]), g["matches12"], g["F21"])
+    assert same_scores(s, g["scoresF_" + tag]) and np.array_equal(np.packbits(i, axis=1), g["inliersF_" + tag])
     E.close()

@@ -5,7 +5,7 @@ import pytest
 
 from oracle import orb_oracle as orc
 from oracle import ref_orb
-from init_util import hypotheses, scene
+from init_util import golden_scoring, hypotheses, same_scores, scene
 
 needs_ref = pytest.mark.skipif(not (ref_orb.available() and hasattr(ref_orb.lib(), "ref_check_homography")),
                                reason="oracle/_ref not built (no /root/reference on this box)")
@@ -41,3 +41,14 @@ def test_no_matches():
     assert s.tolist() == [0, 0, 0, 0] and i.shape == (4, 0)
     s, i = orc.check_fundamental(k1, k2, m12, F21)
     assert s.tolist() == [0, 0, 0, 0]
+
+
+@pytest.mark.parametrize("tag,sigma", [("s10", 1.0), ("s5", 0.5)])
+def test_oracle_matches_golden_demo_pair(tag, sigma):
+    """tests/golden/init_scoring_demo.npz: the reference's own scoring bodies on its demo pair (tools/gen_golden_init.py)."""
+    g = golden_scoring()
+    with np.errstate(all="ignore"):
+        s, i = orc.check_homography(g["kps_un0"], g["kps_un1"], g["matches12"], g["H21"], g["H12"], sigma)
+        assert same_scores(s, g["scoresH_" + tag]) and np.array_equal(np.packbits(i, axis=1), g["inliersH_" + tag])
+        s, i = orc.check_fundamental(g["kps_un0"], g["kps_un1"], g["matches12"], g["F21"], sigma)
+        assert same_scores(s, g["scoresF_" + tag]) and np.array_equal(np.packbits(i, axis=1), g["inliersF_" + tag])
