@@ -49,10 +49,16 @@ __device__ __forceinline__ u32 ring_pack(int vb, int p) { return (u32)(vb - p) *
 // bit 7 of each byte of the result = (that byte of a) > t  OR  (that byte of b) > t.
 //   t < 128:  K = (127 - t) * 0x01010101; (x & 0x7f) + K carries into bit 7 iff (x & 0x7f) > t, and x >= 128 > t.
 //   t >= 128: K = (255 - t) * 0x01010101; x > t iff bit 7 of x is set and (x & 0x7f) + K carries.
-template <bool HI>
+// MODE 0: t < 128 and t + 1 a power of two (the defaults 7 and 0): a <= t and b <= t  <=>  (a | b) <= t, one compare for both
+// MODE 1: any t < 128;  MODE 2: t >= 128
+template <int MODE>
 __device__ __forceinline__ u32 any_gt(u32 a, u32 b, u32 K) {
+  if (MODE == 0) {
+    const u32 x = a | b;
+    return ((x & 0x7f7f7f7fu) + K) | x;
+  }
   const u32 sa = (a & 0x7f7f7f7fu) + K, sb = (b & 0x7f7f7f7fu) + K;
-  if (HI) return (sa & a) | (sb & b);
+  if (MODE == 2) return (sa & a) | (sb & b);
   return sa | sb | a | b;
 }
 // 4 bytes starting at byte offset 4g + DX (DX in [-3, 3]) given the words g-1, g, g+1 of a staged row
@@ -69,7 +75,7 @@ struct Row3 { u32 l, c, r; };  // words g-1, g, g+1 of one staged row
 __device__ __forceinline__ Row3 load3(const u32* __restrict__ row, int g) { return Row3{row[g - 1], row[g], row[g + 1]}; }
 
 // pairs on rows {-3, 0, +3}: (dy,dx) = (3,0), (0,3), (3,1), (-3,1) and their opposites
-template <bool HI>
+template <int HI>
 __device__ __forceinline__ u32 pairs_rows_0_3(u32 alive, const Row3& m, const Row3& c, const Row3& p, u32 K) {
   const u32 cc = c.c;
   alive &= any_gt<HI>(__vabsdiffu4(cc, p.c), __vabsdiffu4(cc, m.c), K);
@@ -79,7 +85,7 @@ __device__ __forceinline__ u32 pairs_rows_0_3(u32 alive, const Row3& m, const Ro
   return alive;
 }
 // pairs on rows +-2: (2,2)/(-2,-2), (-2,2)/(2,-2) and rows +-1: (1,3)/(-1,-3), (-1,3)/(1,-3)
-template <bool HI>
+template <int HI>
 __device__ __forceinline__ u32 pairs_rows_1_2(u32 alive, u32 cc, const Row3& b2, const Row3& b1, const Row3& a1, const Row3& a2, u32 K) {
   alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<2>(a2.l, a2.c, a2.r)), __vabsdiffu4(cc, word_at<-2>(b2.l, b2.c, b2.r)), K);
   alive &= any_gt<HI>(__vabsdiffu4(cc, word_at<2>(b2.l, b2.c, b2.r)), __vabsdiffu4(cc, word_at<-2>(a2.l, a2.c, a2.r)), K);
@@ -91,7 +97,7 @@ __device__ __forceinline__ u32 pairs_rows_1_2(u32 alive, u32 cc, const Row3& b2,
 // Two vertically adjacent words (rows y and y+1 of the same word column) per call: the 8 staged rows y-3 .. y+4
 // serve both.  r0 points at row y.  The pairs of rows {-3,0,+3} go first; the other four rows are only
 // evaluated for a word that still has a pixel alive.
-template <bool HI>
+template <int HI>
 __device__ __forceinline__ void pass1_words(const u32* __restrict__ r0, int SW, int g, u32& aliveA, u32& aliveB, u32 K) {
   const Row3 rm3 = load3(r0 - 3 * SW, g), r00 = load3(r0, g), rp3 = load3(r0 + 3 * SW, g);
   const Row3 rm2 = load3(r0 - 2 * SW, g), rp1 = load3(r0 + SW, g), rp4 = load3(r0 + 4 * SW, g);
@@ -177,8 +183,9 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ P
         aliveA = m;
         aliveB = ry + 1 < nR ? m : 0u;  // the row below the last interior row is staged (apron) but not tested
         const u32* r0 = sImgW + (ry + 3) * SW;
-        if (tq < 128) pass1_words<false>(r0, SW, gw, aliveA, aliveB, K);
-        else pass1_words<true>(r0, SW, gw, aliveA, aliveB, K);
+        if (tq >= 128) pass1_words<2>(r0, SW, gw, aliveA, aliveB, K);
+        else if ((tq & (tq + 1)) == 0) pass1_words<0>(r0, SW, gw, aliveA, aliveB, K);
+        else pass1_words<1>(r0, SW, gw, aliveA, aliveB, K);
       }
       // warp-aggregated append: one shared-memory atomic per warp and iteration
       if (__ballot_sync(0xffffffffu, (aliveA | aliveB) != 0) == 0) continue;

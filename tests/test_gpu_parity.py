@@ -13,6 +13,9 @@ CONFIGS = {
     "euroc": (752, 480, 1200, 20, 7),
     "demo_th0": (752, 480, 2000, 0, 0),      # Settings.yaml as the reference parses it: tie-heavy
     "kitti": (1241, 376, 2000, 20, 7),
+    "th_25_12": (640, 480, 1000, 25, 12),    # min threshold not of the form 2^k - 1: the general byte compare of k_fast pass 1
+    "th_200_150": (640, 480, 1000, 200, 150),  # thresholds >= 128: the third compare form; almost no corners
+    "th_7_20": (640, 480, 600, 7, 20),       # ini below min: the pre-test runs at the smaller of the two
     "uhd": (3840, 2160, 8000, 20, 7),        # config 5: 19 737 FAST cells, level quotas up to 1737
 }
 
@@ -35,6 +38,8 @@ def _bits(a):
 
 def _assert_kps_equal(a, b, what=""):
     assert len(a) == len(b), (what, len(a), len(b))
+    if len(a) == 0:
+        return
     for f in a.dtype.names:
         ok = _bits(a[f]).reshape(len(a), -1) == _bits(b[f]).reshape(len(b), -1)
         if not ok.all():
@@ -134,6 +139,30 @@ def test_flat_and_sparse_images(fe, oracle):
     rk, rd, _ = R(noise)
     _assert_kps_equal(kps, rk, "noise")
     assert np.array_equal(desc, rd)
+    E.close()
+
+
+@pytest.mark.parametrize("ini,mn", [(180, 140), (250, 128), (140, 100), (255, 255)])
+def test_high_thresholds(fe, oracle, ini, mn):
+    """Thresholds of 128 and above take their own byte-compare form in k_fast pass 1: black / white shapes and noise."""
+    W, H = 640, 480
+    rng = np.random.default_rng(ini)
+    img = np.zeros((H, W), np.uint8)
+    for _ in range(150):
+        x, y, w, h = rng.integers(20, W - 60), rng.integers(20, H - 60), rng.integers(6, 40), rng.integers(6, 40)
+        img[y:y + h, x:x + w] = rng.choice([0, 255, 255, 200, 90])
+    img[:, W // 2:] = np.where(rng.integers(0, 4, (H, W - W // 2)) == 0, 255, img[:, W // 2:])  # salt noise on the right half
+    E = fe.ORBextractor(1000, 1.2, 8, ini, mn, W, H)
+    R = oracle.Extractor(1000, 1.2, 8, ini, mn)
+    kps, desc, _ = E(img)
+    rk, rd, _ = R(img)
+    for l in range(8):
+        gc, rc = E.candidates(l), R.candidates(l)
+        assert gc.shape == rc.shape and np.array_equal(gc, rc), ("FAST candidates", l, len(gc), len(rc))
+    _assert_kps_equal(kps, rk, "high thresholds")
+    assert np.array_equal(desc, rd)
+    if ini < 255:
+        assert len(kps) > 100
     E.close()
 
 
