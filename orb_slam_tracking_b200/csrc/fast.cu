@@ -34,14 +34,18 @@ constexpr int kFastThreads = 128;
 // low half-word and 512 - e_k = p_k - v + 256 in the high one, so the min-of-9 / max-of-16 ladder below
 // (VIMNMX.U16x2) yields A + 256 and B + 256 together.
 __device__ __forceinline__ int arc_value(const u32 (&x)[16]) {
-  u32 mn2[16], mn4[16];
+  // min over 9 consecutive ring positions = min3 of three min3 (DPX VIMNMX3.U16x2), then a max3 tree over the 16 arcs
+  u32 mn3[16];
 #pragma unroll
-  for (int k = 0; k < 16; ++k) mn2[k] = __vminu2(x[k], x[(k + 1) & 15]);
+  for (int k = 0; k < 16; ++k) mn3[k] = __vimin3_u16x2(x[k], x[(k + 1) & 15], x[(k + 2) & 15]);
+  u32 a[16];
 #pragma unroll
-  for (int k = 0; k < 16; ++k) mn4[k] = __vminu2(mn2[k], mn2[(k + 2) & 15]);
-  u32 best = 0;
+  for (int k = 0; k < 16; ++k) a[k] = __vimin3_u16x2(mn3[k], mn3[(k + 3) & 15], mn3[(k + 6) & 15]);
+  u32 b[6];
 #pragma unroll
-  for (int k = 0; k < 16; ++k) best = __vmaxu2(best, __vminu2(__vminu2(mn4[k], mn4[(k + 4) & 15]), x[(k + 8) & 15]));
+  for (int k = 0; k < 5; ++k) b[k] = __vimax3_u16x2(a[3 * k], a[3 * k + 1], a[3 * k + 2]);
+  b[5] = a[15];
+  const u32 best = __vimax3_u16x2(__vimax3_u16x2(b[0], b[1], b[2]), __vimax3_u16x2(b[3], b[4], b[5]), 0u);
   return (int)max(best & 0xffffu, best >> 16) - 256;
 }
 __device__ __forceinline__ u32 ring_pack(int vb, int p) { return (u32)(vb - p) * 0xFFFF0001u + 0x02000000u; }
