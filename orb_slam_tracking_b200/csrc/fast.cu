@@ -48,7 +48,8 @@ __device__ __forceinline__ int arc_value(const u32 (&x)[16]) {
   const u32 best = __vimax3_u16x2(__vimax3_u16x2(b[0], b[1], b[2]), __vimax3_u16x2(b[3], b[4], b[5]), 0u);
   return (int)max(best & 0xffffu, best >> 16) - 256;
 }
-__device__ __forceinline__ u32 ring_pack(int vb, int p) { return (u32)(vb - p) * 0xFFFF0001u + 0x02000000u; }
+// base = (256 - v) << 16 | (v + 256); adding p * 0xFFFF moves p from the low half to the high one: one multiply-add
+__device__ __forceinline__ u32 ring_pack(u32 base, u32 p) { return p * 0xFFFFu + base; }
 
 // bit 7 of each byte of the result = (that byte of a) > t  OR  (that byte of b) > t.
 //   t < 128:  K = (127 - t) * 0x01010101; (x & 0x7f) + K carries into bit 7 iff (x & 0x7f) > t, and x >= 128 > t.
@@ -221,7 +222,7 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ P
   for (int i = tid; i < n; i += kFastThreads) {
     const int e = sList[i], ry = e >> 8, b = e & 255;
     const u8* p = sImg + ry * SB + b;
-    const int vb = (int)p[0] + 256;
+    const u32 vb = ((256u - (u32)p[0]) << 16) | ((u32)p[0] + 256u);
     u32 x[16];
     x[0] = ring_pack(vb, p[3 * SB]); x[1] = ring_pack(vb, p[3 * SB + 1]); x[2] = ring_pack(vb, p[2 * SB + 2]); x[3] = ring_pack(vb, p[SB + 3]);
     x[4] = ring_pack(vb, p[3]); x[5] = ring_pack(vb, p[-SB + 3]); x[6] = ring_pack(vb, p[-2 * SB + 2]); x[7] = ring_pack(vb, p[-3 * SB + 1]);
