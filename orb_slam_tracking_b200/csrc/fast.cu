@@ -192,18 +192,11 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ P
         else if ((tq & (tq + 1)) == 0) pass1_words<0>(r0, SW, gw, aliveA, aliveB, K);
         else pass1_words<1>(r0, SW, gw, aliveA, aliveB, K);
       }
-      // warp-aggregated append: one shared-memory atomic per warp and iteration
-      if (__ballot_sync(0xffffffffu, (aliveA | aliveB) != 0) == 0) continue;
+      // append: the list order is irrelevant (pass 2 / 3 take any order, the emission carries its own order key), so a
+      // lane with survivors just reserves its slots
       const int cnt = __popc(aliveA) + __popc(aliveB);
-      int inc = cnt;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int v = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= o) inc += v;
-      }
-      int base = 0;
-      if (lane == 31) base = atomicAdd(&sN, inc);
-      base = __shfl_sync(0xffffffffu, base, 31) + inc - cnt;
+      if (cnt == 0) continue;
+      int base = atomicAdd(&sN, cnt);
       while (aliveA) {
         const int j = (__ffs((int)aliveA) - 1) >> 3;
         aliveA &= aliveA - 1;
