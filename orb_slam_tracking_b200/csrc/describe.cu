@@ -67,12 +67,15 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 6) k_describe(const __grid_
     const int g = gBase + tid;
     int l = -1;
     if (g < P.kpStride) {
+      // the slot's coordinates are fetched whether or not it is occupied: the load then runs beside the count's
+      // instead of behind it (the other seven warps wait for this one at the barrier)
+      const u32 xy = __ldg(P.lvlXY + (size_t)slot * P.kpStride + g);
       l = 0;
       while (l + 1 < P.nlevels && g >= P.lv[l + 1].kpOff) ++l;
       if (g - P.lv[l].kpOff >= P.lvlCount[(size_t)slot * kMaxLevels + l]) l = -1;
+      sXY[tid] = xy;
     }
     sLevel[tid] = (signed char)l;
-    if (l >= 0) sXY[tid] = P.lvlXY[(size_t)slot * P.kpStride + g];
   }
   __syncthreads();
 
