@@ -357,7 +357,7 @@ def run_ours(args, wl):
                        "sharding": "independent frame pairs per rank, no collective"},
             "e2e": {"value": fps_e2e, "unit": UNIT, "h2d_bytes_per_step": int(nbytes_in), "d2h_bytes_per_step": int(nbytes_out),
                     "ms_per_step": ms_e2e / args.steps, "api": "orbx_stream_process_async + orbx_stream_wait, 2 steps in flight",
-                    "chunk_frames": args.chunk,
+                    "chunk_frames": args.chunk if args.chunk > 0 else "auto: 3 equal chunks per step on 3 compute lanes",
                     "blocking_call": {"value": world * B * args.steps / (ms_e2e_call * 1e-3), "ms_per_step": ms_e2e_call / args.steps,
                                       "api": "orbx_stream_process (one step at a time)"}},
             "gpu_launches": int(launches),
@@ -396,7 +396,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="tum", choices=sorted(WORKLOADS))
     ap.add_argument("--batch", type=int, default=0)
-    ap.add_argument("--chunk", type=int, default=128, help="frames per pipelined chunk of the e2e path")
+    ap.add_argument("--chunk", type=int, default=0,
+                    help="frames per pipelined chunk of the e2e path (0 = the library's default: 3 equal chunks per step when streaming, 128 ramped when blocking)")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]

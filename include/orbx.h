@@ -182,7 +182,7 @@ int orbx_stream_process(orbx_ctx* ctx, const uint8_t* imgs, int n_img, float nnr
                         int window_size, int chunk, orbx_keypoint* kps, orbx_keypoint* kps_un, uint8_t* desc, int cap,
                         int* n_out, int* matches12, int* nmatches, int* counters3);
 /* Streaming form of orbx_stream_process: returns a ticket (0 or 1; negative = error) as soon as the step is enqueued.
- * Up to two steps are in flight, so the upload of step s+1 overlaps the kernels and the download of step s; the caller
+ * chunk <= 0 cuts the step into three equal chunks, one per compute lane.  Up to two steps are in flight, so the upload of step s+1 overlaps the kernels and the download of step s; the caller
  * keeps one set of input / output buffers per ticket untouched until orbx_stream_wait(ticket) has returned (it blocks
  * until that step's results are on the host and returns its status).  Other orbx_stream_* calls are ordered after the
  * steps in flight; orbx_stream_sync waits for all of them. */

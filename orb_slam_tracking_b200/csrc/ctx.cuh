@@ -37,7 +37,7 @@ struct orbx_ctx {
   cudaStream_t sSide[kLanes];      // blur runs here, beside the quadtree of the same lane
   cudaEvent_t evFork[kLanes], evJoin[kLanes], evLane[kLanes];
   cudaStream_t sH2D, sD2H;         // copy streams of the pipelined host path (orbx_stream_process)
-  std::vector<cudaEvent_t> evChunk; // 4 per chunk: images landed, kernels done, staging consumed, results on the host
+  std::vector<cudaEvent_t> evChunk; // 5 per chunk: images landed, kernels done, staging consumed, results on the host, status on the host
   orbx::u8* dIngest;               // dense [maxBatch][H][W] staging of uploaded frames
   orbx::u8* dIngestColor;          // dense [maxBatch][H][W][3], allocated on the first colour upload
   int* hStatus;                    // pinned [2][maxBatch]: one block per step in flight

@@ -51,7 +51,9 @@ Params shifted(const orbx_ctx* c, int s0) {
 }
 
 // Enqueues extraction for the n slots of P (level 0 of each slot must already hold the image).
-int enqueue_extract(orbx_ctx* c, const Params& P, int n, int lap0, int lap1, cudaStream_t st = nullptr) {
+// beforeOut (optional): an event the stream waits for right before the kernels that overwrite the arrays a previous
+// step's download reads (packed keypoints / descriptors, then the frame store and the match lists)
+int enqueue_extract(orbx_ctx* c, const Params& P, int n, int lap0, int lap1, cudaStream_t st = nullptr, cudaEvent_t beforeOut = nullptr) {
   if (!st) st = c->stream;
   CU(c, cudaMemsetAsync(P.candCount, 0, (size_t)n * kMaxLevels * sizeof(u32), st));
   CU(c, cudaMemsetAsync(P.status, 0, (size_t)n * sizeof(int), st));
@@ -78,6 +80,7 @@ int enqueue_extract(orbx_ctx* c, const Params& P, int n, int lap0, int lap1, cud
   if (fork) CU(c, cudaStreamWaitEvent(st, c->evJoin[side], 0));
   else c->launches += launch_blur(P, n, st);
   mark(c, 4);
+  if (beforeOut) CU(c, cudaStreamWaitEvent(st, beforeOut, 0));
   c->launches += launch_describe(P, n, lap0, lap1, st);
   mark(c, 5);
   CU(c, cudaGetLastError());
@@ -370,7 +373,8 @@ extern "C" int orbx_stream_download(orbx_ctx* c, int n_img, orbx_keypoint* kps, 
 // the upload of step s+1 overlaps the kernels and the download of step s.  What keeps two steps apart on the device:
 //   * chunk j of every step runs on compute lane j % lanes: stream order separates its kernels from the previous step's;
 //   * the H2D stream waits for evIngested[j] (the previous step's k_ingest has consumed the staging area of chunk j);
-//   * the lane waits for evD2H[j] (the previous step's results of chunk j have left the device) before it overwrites them.
+//   * the lane waits for evStatus[j] before it clears the status words, and for evD2H[j] (the previous step's results of
+//     chunk j have left the device) right before the kernels that overwrite them (k_pack, k_glue, k_match).
 // A step with another chunk schedule than the one in flight drains the pipeline first.
 namespace {
 
@@ -379,7 +383,9 @@ int process_enqueue(orbx_ctx* c, const uint8_t* imgs, int n_img, float nnratio, 
                     int chunk, orbx_keypoint* kps, orbx_keypoint* kps_un, uint8_t* desc, int cap, int* n_out, int* matches12,
                     int* nmatches, int* counters3, int ticket, bool streaming) {
   const Params& P = c->P;
-  if (chunk <= 0) chunk = 128;
+  // default chunking: a blocking call 128 frames (ramped, below); a stream of steps three equal chunks, one per lane
+  // (measured at 512 x 640x480: 3 x 172 on 3 lanes 145.7 k frames/s, 2 x 256 on 2 lanes 145.0 k, 4 x 128 on 2 lanes 133.4 k)
+  if (chunk <= 0) chunk = streaming ? ((n_img + 2) / 3 + 1) & ~1 : 128;
   chunk = std::max(2, chunk & ~1);
   // chunk boundaries.  A blocking call starts with short chunks (chunk / 4, then chunk / 2) so that the kernels start
   // early; in a stream of steps the ramp is hidden behind the previous step and equal chunks run the kernels better
@@ -390,7 +396,7 @@ int process_enqueue(orbx_ctx* c, const uint8_t* imgs, int n_img, float nnratio, 
     const int rc = drain_flights(c);
     if (rc) return rc;
   }
-  while ((int)c->evChunk.size() < 4 * nChunks) {
+  while ((int)c->evChunk.size() < 5 * nChunks) {
     cudaEvent_t e;
     CU(c, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     c->evChunk.push_back(e);
@@ -404,34 +410,40 @@ int process_enqueue(orbx_ctx* c, const uint8_t* imgs, int n_img, float nnratio, 
   c->launches = 0;
   int* hStatus = c->hStatus + (size_t)ticket * P.maxBatch;
   static const int lanesEnv = std::getenv("ORBX_LANES") ? std::atoi(std::getenv("ORBX_LANES")) : 0;
-  // measured at 512 x 640x480: blocking call best with 3 lanes (107 k frames/s), stream of steps with 2 (134 k)
-  const int lanes = std::min(orbx_ctx::kLanes, std::max(1, lanesEnv > 0 ? lanesEnv : (streaming ? 2 : 3)));
+  // A stream of steps stays off lane 0: lane 0 is the context's stream, which joins every step's fence (below) so that
+  // later calls on it come after the step -- as a compute lane it would stall the next step behind this step's download.
+  const int lane0 = streaming ? 1 : 0;
+  const int lanes = std::min(orbx_ctx::kLanes - lane0, std::max(1, lanesEnv > 0 ? lanesEnv : 3));
   int rc = ORBX_OK;
   if (!chained) {  // whatever the caller enqueued on the context's stream (orbx_stream_run ...) comes first
     CU(c, cudaEventRecord(c->evLane[0], c->stream));
-    for (int i = 1; i < lanes; ++i) CU(c, cudaStreamWaitEvent(c->sLane[i], c->evLane[0], 0));
+    for (int i = 0; i < lanes; ++i)
+      if (lane0 + i) CU(c, cudaStreamWaitEvent(c->sLane[lane0 + i], c->evLane[0], 0));
     CU(c, cudaStreamWaitEvent(c->sH2D, c->evLane[0], 0));
   }
   for (int k = 0; k < nChunks && rc == ORBX_OK; ++k) {
     const int s0 = cut[k], n = cut[k + 1] - s0, p0 = s0 / 2, np = n / 2;
-    cudaEvent_t evIn = c->evChunk[4 * k], evOut = c->evChunk[4 * k + 1], evIngested = c->evChunk[4 * k + 2], evD2H = c->evChunk[4 * k + 3];
+    cudaEvent_t evIn = c->evChunk[5 * k], evOut = c->evChunk[5 * k + 1], evIngested = c->evChunk[5 * k + 2], evD2H = c->evChunk[5 * k + 3],
+                evStatus = c->evChunk[5 * k + 4];
     if (chained) CU(c, cudaStreamWaitEvent(c->sH2D, evIngested, 0));
     CU(c, cudaMemcpyAsync(c->dIngest + s0 * imgBytes, imgs + s0 * imgBytes, n * imgBytes, cudaMemcpyHostToDevice, c->sH2D));
     CU(c, cudaEventRecord(evIn, c->sH2D));
     // consecutive chunks rotate over the compute lanes: the latency-bound tail of a chunk (quadtree, matcher: few
     // CTAs) overlaps the issue-bound head of the next ones; chunks touch disjoint slots
-    cudaStream_t sc = c->sLane[k % lanes];
+    cudaStream_t sc = c->sLane[lane0 + k % lanes];
     CU(c, cudaStreamWaitEvent(sc, evIn, 0));
-    if (chained) CU(c, cudaStreamWaitEvent(sc, evD2H, 0));
+    if (chained) CU(c, cudaStreamWaitEvent(sc, evStatus, 0));  // the previous step's status words of these slots are on the host
     const Params Q = shifted(c, s0);
     c->launches += launch_ingest(Q, c->dIngest + s0 * imgBytes, n, sc);
     CU(c, cudaEventRecord(evIngested, sc));
-    if ((rc = enqueue_extract(c, Q, n, 0, 0, sc))) break;
+    // the previous step's results of these slots must have left the device before k_pack / k_glue / k_match overwrite them
+    if ((rc = enqueue_extract(c, Q, n, 0, 0, sc, chained ? evD2H : nullptr))) break;
     if ((rc = enqueue_glue_match(c, Q, n, p0, nnratio, check_orientation, window_size, sc))) break;
     CU(c, cudaEventRecord(evOut, sc));
     cudaStream_t sd = c->sD2H;
     CU(c, cudaStreamWaitEvent(sd, evOut, 0));
     CU(c, cudaMemcpyAsync(hStatus + s0, Q.status, n * sizeof(int), cudaMemcpyDeviceToHost, sd));
+    CU(c, cudaEventRecord(evStatus, sd));
     if (kps)
       CU(c, cudaMemcpy2DAsync(kps + (size_t)s0 * cap, (size_t)cap * sizeof(orbx_keypoint), Q.outKp,
                               (size_t)P.kpStride * sizeof(orbx_keypoint), w * sizeof(orbx_keypoint), n, cudaMemcpyDeviceToHost, sd));
