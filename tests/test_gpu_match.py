@@ -245,6 +245,12 @@ def test_stream_process_async_two_in_flight(fe, oracle, synth):
             same(S.wait(t), want[jj], B)
     t, jj = tickets.pop(0)
     same(S.wait(t), want[jj], B)
+    # the default schedule of the streaming form (three equal chunks), odd batch sizes included
+    for n in (B, 7, 1):
+        ta = S.process_async(sets[0][:n])
+        tb = S.process_async(sets[1][:n])
+        same(S.wait(ta), want[0], n)
+        same(S.wait(tb), want[1], n)
     # a third step without waiting is refused
     t0 = S.process_async(sets[0], chunk=4)
     t1 = S.process_async(sets[1], chunk=4)
