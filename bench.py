@@ -176,6 +176,29 @@ def run_reference(args, wl):
     }), flush=True)
 
 
+def bind_near_gpu(local):
+    """Pin this rank to the CPUs next to its GPU (sysfs local_cpulist of the PCI device) before any page-locked buffer is
+    allocated, so that the frames it uploads live on the GPU's own NUMA node.  Returns a short description."""
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(local)
+        dev = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        txt = open("/sys/bus/pci/devices/%s/local_cpulist" % dev).read().strip()
+        cpus = set()
+        for part in txt.split(","):
+            if part:
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return "no local cpus visible (%s)" % txt
+        os.sched_setaffinity(0, cpus)
+        node = open("/sys/bus/pci/devices/%s/numa_node" % dev).read().strip()
+        return "numa node %s, %d cpus" % (node, len(cpus))
+    except Exception as e:  # sysfs not exposed: stay unbound
+        return "unbound (%s)" % type(e).__name__
+
+
 def run_ours(args, wl):
     import ctypes as C
     import torch
@@ -185,6 +208,7 @@ def run_ours(args, wl):
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
     use_dist = world > 1
     torch.cuda.set_device(local)
+    binding = bind_near_gpu(local) if world > 1 and not os.environ.get("ORBX_BENCH_NO_BIND") else "not bound"
     if use_dist:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -354,7 +378,7 @@ def run_ours(args, wl):
             "config": {"workload": wl["desc"], "frames_per_step_per_gpu": B, "pairs_per_step_per_gpu": B // 2,
                        "nlevels": 8, "scale": 1.2, "fast_th": [wl["ini"], wl["mn"]], "nnratio": NNRATIO, "window": WINDOW,
                        "l2": "batch working set (%.0f MB of pyramids) exceeds the 126 MB L2; no flush" % (2 * B * 1.25 * W * H / 307200),
-                       "sharding": "independent frame pairs per rank, no collective"},
+                       "sharding": "independent frame pairs per rank, no collective", "host_binding_rank0": binding},
             "e2e": {"value": fps_e2e, "unit": UNIT, "h2d_bytes_per_step": int(nbytes_in), "d2h_bytes_per_step": int(nbytes_out),
                     "ms_per_step": ms_e2e / args.steps, "api": "orbx_stream_process_async + orbx_stream_wait, 2 steps in flight",
                     "chunk_frames": args.chunk if args.chunk > 0 else "auto: 3 equal chunks per step on 3 compute lanes",
