@@ -804,34 +804,43 @@ static int match_list(const KeyPoint* k1, const KeyPoint* k2, const int* m12, in
     }
   return (int)(uv.size() / 4);
 }
+namespace {
+// squared transfer error of point (px, py) mapped by the row-major 3x3 M against (qx, qy); the reciprocal of the
+// third coordinate is a double division narrowed to float, as `1.0 / (...)` in the reference (:314, :331)
+inline float transfer_err2(const float* M, float px, float py, float qx, float qy) {
+  const float wInv = 1.0 / (M[6] * px + M[7] * py + M[8]);
+  const float mx = (M[0] * px + M[1] * py + M[2]) * wInv;
+  const float my = (M[3] * px + M[4] * py + M[5]) * wInv;
+  return (qx - mx) * (qx - mx) + (qy - my) * (qy - my);
+}
+// squared distance of (qx, qy) to the line (l0, l1, l2)
+inline float line_err2(float l0, float l1, float l2, float qx, float qy) {
+  const float num = l0 * qx + l1 * qy + l2;
+  return num * num / (l0 * l0 + l1 * l1);
+}
+}  // namespace
+
 int orc_check_homography(const KeyPoint* k1, const KeyPoint* k2, const int* m12, int n1, const float* H21s, const float* H12s,
                          int nHyp, float sigma, float* scores, u8* inliers) {
   std::vector<float> uv;
   const int N = match_list(k1, k2, m12, n1, uv);
-  const float th = 5.991;                                // :291
-  const float invSigmaSquare = 1.0 / (sigma * sigma);    // :293
+  const float chi2Limit = 5.991;                       // :291
+  const float invSigma2 = 1.0 / (sigma * sigma);       // :293
   for (int h = 0; h < nHyp; ++h) {
-    const float* A = H21s + 9 * h;
-    const float* B = H12s + 9 * h;
-    float score = 0;
+    const float* fwd = H21s + 9 * h;   // frame 1 -> frame 2
+    const float* bwd = H12s + 9 * h;   // frame 2 -> frame 1
+    float total = 0;
     for (int i = 0; i < N; ++i) {
-      bool bIn = true;
-      const float u1 = uv[4 * i], v1 = uv[4 * i + 1], u2 = uv[4 * i + 2], v2 = uv[4 * i + 3];
-      const float w2in1inv = 1.0 / (B[6] * u2 + B[7] * v2 + B[8]);   // :314
-      const float u2in1 = (B[0] * u2 + B[1] * v2 + B[2]) * w2in1inv;
-      const float v2in1 = (B[3] * u2 + B[4] * v2 + B[5]) * w2in1inv;
-      const float squareDist1 = (u1 - u2in1) * (u1 - u2in1) + (v1 - v2in1) * (v1 - v2in1);
-      const float chiSquare1 = squareDist1 * invSigmaSquare;
-      if (chiSquare1 > th) bIn = false; else score += th - chiSquare1;
-      const float w1in2inv = 1.0 / (A[6] * u1 + A[7] * v1 + A[8]);   // :331
-      const float u1in2 = (A[0] * u1 + A[1] * v1 + A[2]) * w1in2inv;
-      const float v1in2 = (A[3] * u1 + A[4] * v1 + A[5]) * w1in2inv;
-      const float squareDist2 = (u2 - u1in2) * (u2 - u1in2) + (v2 - v1in2) * (v2 - v1in2);
-      const float chiSquare2 = squareDist2 * invSigmaSquare;
-      if (chiSquare2 > th) bIn = false; else score += th - chiSquare2;
-      if (inliers) inliers[(size_t)h * N + i] = bIn ? 1 : 0;
+      const float* q = &uv[4 * i];     // u1, v1, u2, v2
+      bool ok = true;
+      // frame 2 into frame 1 first (:309-325), then frame 1 into frame 2 (:327-343); two separate additions
+      const float c1 = transfer_err2(bwd, q[2], q[3], q[0], q[1]) * invSigma2;
+      if (c1 > chi2Limit) ok = false; else total += chi2Limit - c1;
+      const float c2 = transfer_err2(fwd, q[0], q[1], q[2], q[3]) * invSigma2;
+      if (c2 > chi2Limit) ok = false; else total += chi2Limit - c2;
+      if (inliers) inliers[(size_t)h * N + i] = ok ? 1 : 0;
     }
-    scores[h] = score;
+    scores[h] = total;
   }
   return N;
 }
@@ -839,32 +848,26 @@ int orc_check_fundamental(const KeyPoint* k1, const KeyPoint* k2, const int* m12
                           float* scores, u8* inliers) {
   std::vector<float> uv;
   const int N = match_list(k1, k2, m12, n1, uv);
-  const float th = 3.841;        // :372
-  const float thScore = 5.991;   // :374
-  const float invSigmaSquare = 1.0 / (sigma * sigma);
+  const float chi2Limit = 3.841;   // :372, one degree of freedom for the test
+  const float chi2Score = 5.991;   // :374, the score keeps the homography's constant
+  const float invSigma2 = 1.0 / (sigma * sigma);
   for (int h = 0; h < nHyp; ++h) {
     const float* F = F21s + 9 * h;
-    float score = 0;
+    float total = 0;
     for (int i = 0; i < N; ++i) {
-      bool bIn = true;
-      const float u1 = uv[4 * i], v1 = uv[4 * i + 1], u2 = uv[4 * i + 2], v2 = uv[4 * i + 3];
-      const float a2 = F[0] * u1 + F[1] * v1 + F[2];                 // l2 = F21 x1 (:392-394)
-      const float b2 = F[3] * u1 + F[4] * v1 + F[5];
-      const float c2 = F[6] * u1 + F[7] * v1 + F[8];
-      const float num2 = a2 * u2 + b2 * v2 + c2;
-      const float squareDist1 = num2 * num2 / (a2 * a2 + b2 * b2);
-      const float chiSquare1 = squareDist1 * invSigmaSquare;
-      if (chiSquare1 > th) bIn = false; else score += thScore - chiSquare1;
-      const float a1 = F[0] * u2 + F[3] * v2 + F[6];                 // l1 = F21^T x2 (:414-416)
-      const float b1 = F[1] * u2 + F[4] * v2 + F[7];
-      const float c1 = F[2] * u2 + F[5] * v2 + F[8];
-      const float num1 = a1 * u1 + b1 * v1 + c1;
-      const float squareDist2 = num1 * num1 / (a1 * a1 + b1 * b1);
-      const float chiSquare2 = squareDist2 * invSigmaSquare;
-      if (chiSquare2 > th) bIn = false; else score += thScore - chiSquare2;
-      if (inliers) inliers[(size_t)h * N + i] = bIn ? 1 : 0;
+      const float* q = &uv[4 * i];
+      bool ok = true;
+      // epipolar line of point 1 in image 2: F x1 (:392-404)
+      const float c1 = line_err2(F[0] * q[0] + F[1] * q[1] + F[2], F[3] * q[0] + F[4] * q[1] + F[5],
+                                 F[6] * q[0] + F[7] * q[1] + F[8], q[2], q[3]) * invSigma2;
+      if (c1 > chi2Limit) ok = false; else total += chi2Score - c1;
+      // epipolar line of point 2 in image 1: F^T x2 (:414-426)
+      const float c2 = line_err2(F[0] * q[2] + F[3] * q[3] + F[6], F[1] * q[2] + F[4] * q[3] + F[7],
+                                 F[2] * q[2] + F[5] * q[3] + F[8], q[0], q[1]) * invSigma2;
+      if (c2 > chi2Limit) ok = false; else total += chi2Score - c2;
+      if (inliers) inliers[(size_t)h * N + i] = ok ? 1 : 0;
     }
-    scores[h] = score;
+    scores[h] = total;
   }
   return N;
 }

@@ -22,49 +22,45 @@ namespace orbx {
 
 constexpr int kScoreThreads = 256;
 
+// squared transfer error of (px, py) mapped by the row-major 3x3 M against (qx, qy) (:314-319, :331-336)
+__device__ __forceinline__ float transfer_err2(const float (&M)[9], float px, float py, float qx, float qy) {
+  const float wInv = 1.0f / (M[6] * px + M[7] * py + M[8]);
+  const float mx = (M[0] * px + M[1] * py + M[2]) * wInv;
+  const float my = (M[3] * px + M[4] * py + M[5]) * wInv;
+  return (qx - mx) * (qx - mx) + (qy - my) * (qy - my);
+}
+// squared distance of (qx, qy) to the line (l0, l1, l2) (:396-402, :418-424)
+__device__ __forceinline__ float line_err2(float l0, float l1, float l2, float qx, float qy) {
+  const float num = l0 * qx + l1 * qy + l2;
+  return num * num / (l0 * l0 + l1 * l1);
+}
+
 // One hypothesis over the list.  The two `score +=` of a match are separate float additions in the reference, so they
-// are kept separate here.
+// are kept separate here.  A = H21 or F21, B = H12.
 template <bool FUND>
 __device__ __forceinline__ float walk(const float (&A)[9], const float (&B)[9], const float4* __restrict__ sUV, int N,
-                                      float invSigmaSquare, u8* inl) {
-  const float thH = (float)5.991, thF = (float)3.841;  // :291 / :372,374
-  float score = 0.f;
+                                      float invSigma2, u8* inl) {
+  const float limH = (float)5.991, limF = (float)3.841;  // :291 / :372,374
+  float total = 0.f;
   for (int i = 0; i < N; ++i) {
-    const float4 m = sUV[i];
-    const float u1 = m.x, v1 = m.y, u2 = m.z, v2 = m.w;
-    bool bIn = true;
+    const float4 m = sUV[i];  // u1, v1, u2, v2
+    bool ok = true;
     if (!FUND) {
-      const float w2in1inv = 1.0f / (B[6] * u2 + B[7] * v2 + B[8]);
-      const float u2in1 = (B[0] * u2 + B[1] * v2 + B[2]) * w2in1inv;
-      const float v2in1 = (B[3] * u2 + B[4] * v2 + B[5]) * w2in1inv;
-      const float d1 = (u1 - u2in1) * (u1 - u2in1) + (v1 - v2in1) * (v1 - v2in1);
-      const float chi1 = d1 * invSigmaSquare;
-      if (chi1 > thH) bIn = false; else score += thH - chi1;
-      const float w1in2inv = 1.0f / (A[6] * u1 + A[7] * v1 + A[8]);
-      const float u1in2 = (A[0] * u1 + A[1] * v1 + A[2]) * w1in2inv;
-      const float v1in2 = (A[3] * u1 + A[4] * v1 + A[5]) * w1in2inv;
-      const float d2 = (u2 - u1in2) * (u2 - u1in2) + (v2 - v1in2) * (v2 - v1in2);
-      const float chi2 = d2 * invSigmaSquare;
-      if (chi2 > thH) bIn = false; else score += thH - chi2;
+      const float c1 = transfer_err2(B, m.z, m.w, m.x, m.y) * invSigma2;  // frame 2 into frame 1 first
+      if (c1 > limH) ok = false; else total += limH - c1;
+      const float c2 = transfer_err2(A, m.x, m.y, m.z, m.w) * invSigma2;
+      if (c2 > limH) ok = false; else total += limH - c2;
     } else {
-      const float a2 = A[0] * u1 + A[1] * v1 + A[2];
-      const float b2 = A[3] * u1 + A[4] * v1 + A[5];
-      const float c2 = A[6] * u1 + A[7] * v1 + A[8];
-      const float num2 = a2 * u2 + b2 * v2 + c2;
-      const float d1 = num2 * num2 / (a2 * a2 + b2 * b2);
-      const float chi1 = d1 * invSigmaSquare;
-      if (chi1 > thF) bIn = false; else score += thH - chi1;
-      const float a1 = A[0] * u2 + A[3] * v2 + A[6];
-      const float b1 = A[1] * u2 + A[4] * v2 + A[7];
-      const float c1 = A[2] * u2 + A[5] * v2 + A[8];
-      const float num1 = a1 * u1 + b1 * v1 + c1;
-      const float d2 = num1 * num1 / (a1 * a1 + b1 * b1);
-      const float chi2 = d2 * invSigmaSquare;
-      if (chi2 > thF) bIn = false; else score += thH - chi2;
+      const float c1 = line_err2(A[0] * m.x + A[1] * m.y + A[2], A[3] * m.x + A[4] * m.y + A[5], A[6] * m.x + A[7] * m.y + A[8],
+                                 m.z, m.w) * invSigma2;  // F x1 against x2
+      if (c1 > limF) ok = false; else total += limH - c1;
+      const float c2 = line_err2(A[0] * m.z + A[3] * m.w + A[6], A[1] * m.z + A[4] * m.w + A[7], A[2] * m.z + A[5] * m.w + A[8],
+                                 m.x, m.y) * invSigma2;  // F^T x2 against x1
+      if (c2 > limF) ok = false; else total += limH - c2;
     }
-    if (inl) inl[i] = bIn ? 1 : 0;
+    if (inl) inl[i] = ok ? 1 : 0;
   }
-  return score;
+  return total;
 }
 
 template <bool FUND>
