@@ -47,14 +47,14 @@ if rep.exists():
         b = float(r[ir]) * unit[rr[1][ir]] + float(r[iw]) * unit[rr[1][iw]]
         g = per.setdefault(k, {})
         g[r[ig]] = max(g.get(r[ig], 0.0), b)
-    traffic = {k: (sum(g.values()) if k == "k_resize" else max(g.values())) for k, g in per.items()}
+    traffic = {k: (sum(g.values()) if "k_resize" in k else max(g.values())) for k, g in per.items()}
     (P / f"{tag}_traffic.json").write_text(json.dumps({"source": f"ncu --set full, {tag}_full.ncu-rep, dram__bytes_read.sum + dram__bytes_write.sum per launch "
                                                        "(k_resize: sum over its 7 launches of a step)", "bytes_per_launch": traffic}, indent=1))
     seen = {}
     for r in rr[2:]:
         k = r[idx[0][0]].split("(")[0]
         seen[k] = seen.get(k, 0) + 1
-        if seen[k] > (7 if k == "k_resize" else 1): continue
+        if seen[k] > (7 if "k_resize" in k else 1): continue
         scale = {"ns": 1e-6, "us": 1e-3, "usecond": 1e-3, "msecond": 1.0, "ms": 1.0, "s": 1e3, "byte": 1e-6, "Kbyte": 1e-3, "Mbyte": 1.0, "Gbyte": 1e3}
         vals = [k]
         for i, _ in idx[1:]:
