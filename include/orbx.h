@@ -78,6 +78,11 @@ void orbx_destroy(orbx_ctx* ctx);
 const char* orbx_last_error(const orbx_ctx* ctx); /* never NULL */
 /* 0: (float)cos((double)a) [default, pinned by the oracle]; 1: cosf(a).  See DESIGN.md. */
 int orbx_set_trig_mode(orbx_ctx* ctx, int mode);
+/* Schedule options of a context (they never change results).  The environment is read ONCE, in orbx_create
+ * (ORBX_SINGLE_STREAM, ORBX_RUN_PARTS, ORBX_LANES, ORBX_RESIZE_ROWS, ORBX_MATCH_SERIAL, ORBX_FAST_TILE); this call
+ * changes an option of a live context: name = "single_stream" | "run_parts" | "lanes" | "resize_rows" | "match_serial".
+ * No launch path reads the environment.  Returns ORBX_ERR_ARG for an unknown name. */
+int orbx_set_option(orbx_ctx* ctx, const char* name, int value);
 
 /* ---- extractor tables (host arithmetic of the reference constructor) -------------------- */
 /* Any output pointer may be NULL.  Arrays have nlevels entries; umax has 16.  Returns nlevels. */

@@ -30,13 +30,14 @@ constexpr int kHalfPatch = 15;  // HALF_PATCH_SIZE, :74
 constexpr int kPatch = 31;      // PATCH_SIZE, :72
 constexpr int kMinBorder = 16;  // EDGE_THRESHOLD - 3, :1056
 constexpr int kGridCols = ORBX_GRID_COLS, kGridRows = ORBX_GRID_ROWS, kGridCells = ORBX_GRID_CELLS;
+constexpr int kFastWarps = 8;   // warps of a k_fast CTA (its per-warp list segments are sized on the host)
 constexpr int kMaxCellDim = 80;  // cell ROI (wCell + 6) is < 76 for every image size
 
 struct LevelInfo {
   int w, h, pitch;    // unpadded size, row pitch in bytes (multiple of 128)
   u32 imgOff;         // byte offset of the level in a slot's slab
   int nCols, nRows, wCell, hCell;  // FAST cell grid, :1066-1075
-  int cellBase;       // first entry of this level in the cell table
+  int fastBoxW, fastBoxH;  // TMA box of k_fast at this level: bytes per staged row (an odd multiple of 16), rows
   int quota;          // mnFeaturesPerLevel[l]
   int candCap;        // capacity of the candidate arrays of this level
   u32 candOff;        // first candidate of this level in a slot's candidate arrays
@@ -51,12 +52,25 @@ struct LevelInfo {
   int distW, distH;   // maxBorderX - minBorderX, maxBorderY - minBorderY
 };
 
-struct CellDesc {     // one FAST cell, Features/ORBextractor.cpp:1078-1141
-  short level, pad;
-  short x0, y0, x1, y1;   // ROI [x0,x1) x [y0,y1) in level coordinates
-  short sx, sy;           // j * wCell, i * hCell: shift applied to ROI-relative coordinates (:1134-1135)
-  int index;              // i * nCols + j
+struct StripDesc {    // one work item of k_fast: a run of consecutive FAST cells of one cell row, Features/ORBextractor.cpp:1078-1141.
+                      // Everything a CTA needs about the strip and its level, derived on the host (48 bytes, three 16-byte loads).
+  short level, nCells;
+  short tmaX, y0;         // tile origin: x in 32-bit elements (a 16-byte aligned column <= x0 - 1), first row of the cells' ROIs
+  short SB;               // staged row stride in bytes = lv[level].fastBoxW
+  short bLo, bHi;         // interior byte columns [bLo, bHi) of a staged row: level columns [x0 + 3, x1 - 3) of the cells' ROIs [x0, x1);
+                          // cell j of the strip tests the columns [bLo + j * wCell, min(bLo + (j + 1) * wCell, bHi))
+  short nR;               // interior rows: tile rows [3, 3 + nR)
+  short wCell;
+  short sx, sy;           // j0 * wCell, i * hCell: shift applied to ROI-relative coordinates (:1134-1135)
+  short nIniM1;           // lv[level].nIni - 1
+  int tileBytes;          // fastBoxW * fastBoxH of the level: what the tile copy delivers
+  u32 cellMul;            // (xb * cellMul) >> 16 == xb / wCell for every interior column xb of a strip
+  int index0;             // i * nCols + j0: row-major index of the strip's first cell
+  u32 candOff;            // lv[level].candOff, candCap, rootTabOff
+  int candCap;
+  u32 rootTabOff;
 };
+static_assert(sizeof(StripDesc) == 48, "StripDesc is loaded as three 16-byte words");
 
 struct BlurTile {
   short level, pad;
@@ -64,7 +78,8 @@ struct BlurTile {
 };
 
 // TMA descriptors (cuTensorMapEncodeTiled, built once in orbx_create): level l of the pyramid slab as a
-// u8 tensor {x: w, y: h, slot: maxBatch} with strides {pitch, slabBytes}; box = fastBoxW x fastBoxH x 1.
+// u32 tensor {x: pitch / 4, y: h, slot: maxBatch} with strides {pitch, slabBytes}; box = lv[l].fastBoxW / 4 x lv[l].fastBoxH x 1
+// (32-bit elements: a box dimension is limited to 256 elements, and a strip row is wider than 256 bytes).
 struct TmaMaps {
   CUtensorMap lvl[kMaxLevels];
 };
@@ -73,9 +88,11 @@ struct Params {
   int W, H, nlevels, nfeatures, iniTh, minTh, maxBatch;
   int kpStride;        // keypoint slots per frame = max(nfeatures, sum of quotas)
   int trigMode;
-  int nCells, nBlurTiles;
+  int nStrips, nBlurTiles;
   int slot0;               // first slot of this launch inside the context's slot arrays (TMA z origin; pointers below are pre-shifted)
-  int fastBoxW, fastBoxH;  // TMA box of k_fast: bytes per staged row (multiple of 16, >= widest cell ROI + 8), rows
+  int fastTileMax;         // k_fast shared memory: bytes of one staged tile (largest level box, multiple of 128)
+  int fastSegW, fastSegP;  // per-warp capacities (entries) of the word and the pixel segments: the worst case of any strip
+  int fastGrid;            // persistent CTAs of a full k_fast launch (SMs x resident CTAs per SM)
   u32 slabBytes, candTotal, nodeTotal;
   int umax[16];
   LevelInfo lv[kMaxLevels];
@@ -86,7 +103,7 @@ struct Params {
   u32* candXY;
   u32* candNode;
   u32* candCount;      // [slot][kMaxLevels]
-  const CellDesc* cells;
+  const StripDesc* strips;
   const BlurTile* blurTiles;
   const u8* rootTab;
   // quadtree node tables [slot][nodeTotal]
@@ -120,6 +137,14 @@ struct Params {
   int bounds[4];
   float gridWInv, gridHInv;
   int undistort;       // mDistCoef(0) != 0
+  // host-side schedule options (kernels ignore them): read ONCE in orbx_create from the environment (ORBX_SINGLE_STREAM,
+  // ORBX_RUN_PARTS, ORBX_LANES, ORBX_RESIZE_ROWS, ORBX_MATCH_SERIAL, ORBX_FAST_TILE) or set with orbx_set_option
+  int optSingleStream;   // profiling aid: whole-batch launches in order on one stream
+  int optRunParts;       // pieces of orbx_stream_run (0 = default)
+  int optLanes;          // compute lanes of the chunked host path (0 = default)
+  int optResizeRows;     // rows per warp of k_resize (0 = default)
+  int optMatchSerial;    // test hook: force the one-warp-per-pair matcher
+  int optFastTileBudget; // bytes of one staged k_fast tile (creation time only)
 };
 
 __device__ __forceinline__ const u8* level_ptr(const u8* base, const Params& P, int slot, int l) {

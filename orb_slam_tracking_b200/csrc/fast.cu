@@ -2,33 +2,43 @@
 // (ORBextractor::ComputeKeyPointsOctTree cell loop, Features/ORBextractor.cpp:1051-1141, calling
 // cv::FAST(roi, kps, th, true) at :1109 and :1119; arithmetic in SURVEY.md appendix A3).
 //
-// One CTA of 128 threads per (cell, slot); the cells of ALL levels are in one table, so one launch
-// covers a batch.  The cell ROI (from the 16-byte aligned column left of it) is staged into shared memory by ONE TMA
-// tile copy (cp.async.bulk.tensor.3d over a per-level {x, y, slot} tensor map, completion on an
-// mbarrier); out-of-image box bytes are zero-filled by the hardware and never tested.
+// Work item = STRIP: a run of consecutive cells of one cell row of one (level, slot); the strips of all levels are in one
+// table, so one launch covers a batch.  The kernel is persistent: gridDim.x = SMs x resident CTAs, each CTA walks the
+// items blockIdx.x, blockIdx.x + gridDim.x, ... with a two-stage tile ring: while it works on the tile in one buffer, the
+// next item's tile is in flight into the other one (ONE cp.async.bulk.tensor.3d per tile over a per-level {x, y, slot}
+// tensor map, completion on the buffer's mbarrier; rows beyond the level are zero-filled by the hardware and never tested).
 //
-// The segment-test value m(p) = max over the 16 arcs of 9 of min(v - ring) / min(ring - v) does not
-// depend on the threshold: p is a corner at t iff m > t and its NMS score is m - 1.  A corner
-// survives NMS at t iff m >= 2 and m is a strict 3x3 maximum of the m-map restricted to the
-// cell's tested interior (a neighbour that is not a corner at t has m' <= t < m anyway).  So the
-// CTA computes the peaks once and then applies the reference's rule: keep the peaks with
-// m > iniTh, or, if the cell has none, the peaks with m > minTh.
+// The segment-test value m(p) = max over the 16 arcs of 9 of min(v - ring) / min(ring - v) does not depend on the
+// threshold: p is a corner at t iff m > t and its NMS score is m - 1.  A corner survives NMS at t iff m >= 2 and m is a
+// strict 3x3 maximum among the corners at t of ITS cell's tested interior (everything else counts as 0).  The reference's
+// schedule is kept: the whole strip runs at iniThFAST; the cells without a keypoint then run again at minThFAST (:1109-1119).
 //
-// Pass 1 is the hot loop: the opposing-pair rejection (every arc of 9 contains one pixel of each
-// opposing ring pair, so a pair with both |d| <= t proves m <= t) runs on 2 x 4 pixels per thread (two vertically
-// adjacent words, which share 6 of their 8 staged rows) with byte-SWAR arithmetic on 32-bit words of the staged ROI: VABSDIFF4 per ring word, then a
-// carry-free "byte > t" in bit 7 of each byte.  The four pairs that live on rows {-3, 0, +3} go
-// first; only words with a pixel still alive touch the other four rows, and only the few
-// surviving pixels get the exact arc value (pass 2).
-//
-// Survivors are appended to the level's candidate list with an atomic cursor; each carries its
-// position in the reference's emission order (cell row-major, then y, then x) inside its key, which
-// is all the quadtree needs ("first strict maximum" == max response, then min order).
+// One run = four data-parallel phases over compacted lists in shared memory (each phase keeps all lanes busy):
+//   A   every aligned word pair (8 pixels) of the interior: the vertical opposing pair (0,+-3) only -- two byte-SWAR
+//       absolute differences per word (VABSDIFF4) and a carry-free "byte > t" -- needs nothing but aligned 64-bit loads;
+//       words with a pixel alive go to the word list (warp-aggregated append).  Flat image areas end here.
+//   BC  one thread per listed word: all 8 opposing pairs (every arc of 9 contains one pixel of each pair, so a pair with
+//       both |d| <= t proves m <= t); rows {-3, 0, +3} first, the other four rows only for words still alive; survivors
+//       go to the pixel list.
+//   P2  one thread per listed pixel: the exact m (both polarities in 16-bit halves, VIMNMX3 min/max ladder); m > t is
+//       written to the m-map (zero everywhere else).
+//   P3  one thread per listed pixel with m > t: strict 3x3 maximum inside its cell -> the keypoint is appended to the
+//       level's candidate list in HBM right away, carrying its position in the reference's emission order (cell
+//       row-major, then y, then x) inside its key, which is all the quadtree needs ("first strict maximum" == max
+//       response, then min order); per-cell keypoint counters decide the minThFAST retry.
+// The m-map entries written by a run are cleared through the pixel list afterwards (no per-strip zero fill).
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace orbx {
 
-constexpr int kFastThreads = 128;
+constexpr int kFastThreads = 32 * kFastWarps;
+#ifndef ORBX_FAST_STAGES
+#define ORBX_FAST_STAGES 2
+#endif
+constexpr int kFastStages = ORBX_FAST_STAGES;  // tile buffers of the ring
+constexpr int kFastCtasPerSm = kFastStages == 1 ? 4 : 3;   // register cap: 65536 / (3 * 256) = 85
 
 // m(p) for one pixel.  Both polarities ride in one register per ring position: e_k = v - p_k + 256 in the
 // low half-word and 512 - e_k = p_k - v + 256 in the high one, so the min-of-9 / max-of-16 ladder below
@@ -51,20 +61,16 @@ __device__ __forceinline__ int arc_value(const u32 (&x)[16]) {
 // base = (256 - v) << 16 | (v + 256); adding p * 0xFFFF moves p from the low half to the high one: one multiply-add
 __device__ __forceinline__ u32 ring_pack(u32 base, u32 p) { return p * 0xFFFFu + base; }
 
-// bit 7 of each byte of the result = (that byte of a) > t  OR  (that byte of b) > t.
-//   t < 128:  K = (127 - t) * 0x01010101; (x & 0x7f) + K carries into bit 7 iff (x & 0x7f) > t, and x >= 128 > t.
-//   t >= 128: K = (255 - t) * 0x01010101; x > t iff bit 7 of x is set and (x & 0x7f) + K carries.
-// MODE 0: t < 128 and t + 1 a power of two (the defaults 7 and 0): a <= t and b <= t  <=>  (a | b) <= t, one compare for both
-// MODE 1: any t < 128;  MODE 2: t >= 128
-template <int MODE>
+// Bit 7 of each byte of the result is set if that byte of a OR that byte of b is > t -- and possibly when neither is:
+// the compare runs on a | b, which is >= max(a, b) and <= t whenever both are <= t and t + 1 is a power of two (the
+// defaults 7 and 0).  For other thresholds a few more pixels pass the pair tests; the tests are only a filter in front of
+// the exact segment-test value, whose comparison with t decides.
+//   t < 128  (HI = 0): K = (127 - t) * 0x01010101; (x & 0x7f) + K carries into bit 7 iff (x & 0x7f) > t, and x >= 128 > t.
+//   t >= 128 (HI = 1): K = (255 - t) * 0x01010101; x > t iff bit 7 of x is set and (x & 0x7f) + K carries.
+template <int HI>
 __device__ __forceinline__ u32 any_gt(u32 a, u32 b, u32 K) {
-  if (MODE == 0) {
-    const u32 x = a | b;
-    return ((x & 0x7f7f7f7fu) + K) | x;
-  }
-  const u32 sa = (a & 0x7f7f7f7fu) + K, sb = (b & 0x7f7f7f7fu) + K;
-  if (MODE == 2) return (sa & a) | (sb & b);
-  return sa | sb | a | b;
+  const u32 s = ((a | b) & 0x7f7f7f7fu) + K;
+  return HI ? s & (a | b) : s | a | b;
 }
 // 4 bytes starting at byte offset 4g + DX (DX in [-3, 3]) given the words g-1, g, g+1 of a staged row
 template <int DX>
@@ -99,121 +105,125 @@ __device__ __forceinline__ u32 pairs_rows_1_2(u32 alive, u32 cc, const Row3& b2,
   return alive;
 }
 
-// Two vertically adjacent words (rows y and y+1 of the same word column) per call: the 8 staged rows y-3 .. y+4
-// serve both.  r0 points at row y.  The pairs of rows {-3,0,+3} go first; the other four rows are only
-// evaluated for a word that still has a pixel alive.
-template <int HI>
-__device__ __forceinline__ void pass1_words(const u32* __restrict__ r0, int SW, int g, u32& aliveA, u32& aliveB, u32 K) {
-  const Row3 rm3 = load3(r0 - 3 * SW, g), r00 = load3(r0, g), rp3 = load3(r0 + 3 * SW, g);
-  const Row3 rm2 = load3(r0 - 2 * SW, g), rp1 = load3(r0 + SW, g), rp4 = load3(r0 + 4 * SW, g);
-  aliveA = pairs_rows_0_3<HI>(aliveA, rm3, r00, rp3, K);
-  aliveB = pairs_rows_0_3<HI>(aliveB, rm2, rp1, rp4, K);
-  if (aliveA | aliveB) {
-    const Row3 rm1 = load3(r0 - SW, g), rp2 = load3(r0 + 2 * SW, g);
-    if (aliveA) aliveA = pairs_rows_1_2<HI>(aliveA, r00.c, rm2, rm1, rp1, rp2, K);
-    if (aliveB) aliveB = pairs_rows_1_2<HI>(aliveB, rp1.c, rm1, r00, rp2, rp3, K);
-  }
+
+// dynamic shared memory of k_fast: two tile buffers, the m-map, and per warp a word / peak segment (32-bit entries) and a
+// pixel segment (16-bit entries)
+static size_t fast_smem_bytes(const Params& P) {
+  return (size_t)(kFastStages + 1) * P.fastTileMax + (size_t)kFastWarps * (4 * (size_t)P.fastSegW + 2 * (size_t)P.fastSegP);
 }
 
-__global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ Params P, const __grid_constant__ TmaMaps M) {
-  extern __shared__ __align__(128) u8 smem[];
-  __shared__ __align__(8) u64 sBar;
-  __shared__ int sN, sPeaks, sIni, sMin, sBase, sCursor;
+struct StripCtx {
+  const u32* imgW;        // staged tile as words
+  u8* mm;                 // m-map, same geometry as the tile
+  u32* segW;              // this warp's word segment: alive bits (7, 15, 23, 31) | row << 8 | word; reused for its peaks as 16-bit pixel entries
+                          // (at most every other pixel of a row is a peak: two per word)
+  unsigned short* segP;   // this warp's pixel segment: row << 9 | byte column
+  int* cellIni;           // per cell of the strip: set by a keypoint of the iniThFAST run
+  int SB, SW;             // staged row stride in bytes / words
+  int bLo, bHi;           // interior byte columns [bLo, bHi) of a staged row
+  int nR;                 // interior rows: tile rows [3, 3 + nR)
+  int wCell;
+  u32 cellMul;
+  // emission
+  int slot, level, sx, sy, index0, nIniM1, candCap;
+  u32 candOff, rootTabOff;
+};
 
-  const CellDesc c = P.cells[blockIdx.x];
-  const int slot = blockIdx.y;
-  const LevelInfo& L = P.lv[c.level];
-  const int cw = c.x1 - c.x0, ch = c.y1 - c.y0;
-  const int tid = threadIdx.x;
-  const int SB = P.fastBoxW, SW = SB >> 2;  // staged row stride in bytes / words
-  // TMA tile origins must be 16-byte aligned in the innermost dimension: the tile starts at the aligned column
-  // xs <= x0 - 1, so byte b of a staged row <-> level column xs + b and ROI column rx <-> byte rx + off, off in [1, 16]
-  const int xs = (c.x0 - 1) & ~15, off = c.x0 - xs;
-  const int tileBytes = SB * P.fastBoxH;
-  u8* const sImg = smem;
-  u8* const sM = smem + tileBytes;            // m-map, same geometry, zero outside the interior
-  unsigned short* const sList = reinterpret_cast<unsigned short*>(smem + 2 * tileBytes);
-  const u32* const sImgW = reinterpret_cast<const u32*>(sImg);
+// bytes of word g (bit 7 each) that lie inside [bLo, bHi)
+__device__ __forceinline__ u32 interior_mask(int g, int bLo, int bHi) {
+  u32 m = 0x80808080u;
+  if (4 * g + 4 <= bLo || 4 * g >= bHi) return 0u;
+  if (4 * g < bLo) m &= 0xffffffffu << (8 * (bLo - 4 * g));
+  if (4 * g + 4 > bHi) m &= 0xffffffffu >> (8 * (4 * g + 4 - bHi));
+  return m;
+}
+// bytes of word g (any bits) whose cell is in `cells` (retry run); a word spans at most two cells
+__device__ __forceinline__ u32 cell_mask(const StripCtx& S, int g, u32 cells) {
+  const int xa = max(4 * g - S.bLo, 0), xb = max(4 * g + 3 - S.bLo, 0);
+  const int ja = (int)(((u32)xa * S.cellMul) >> 16), jb = (int)(((u32)xb * S.cellMul) >> 16);
+  const u32 ka = (cells >> ja) & 1 ? 0xffffffffu : 0u, kb = (cells >> jb) & 1 ? 0xffffffffu : 0u;
+  if (ja == jb) return ka;
+  const int nb = jb * S.wCell + S.bLo - 4 * g;  // first byte of the word that belongs to cell jb, 1..3
+  const u32 lo = 0xffffffffu >> (8 * (4 - nb));
+  return (ka & lo) | (kb & ~lo);
+}
 
-  if (tid == 0) {
-    sN = 0; sPeaks = 0; sIni = 0; sMin = 0; sCursor = 0;
-    const u32 bar = smem_addr(&sBar);
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(tileBytes) : "memory");
-    asm volatile(
-        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
-        ::"r"(smem_addr(sImg)), "l"(reinterpret_cast<u64>(&M.lvl[c.level])), "r"(xs), "r"((int)c.y0), "r"(slot + P.slot0), "r"(bar)
-        : "memory");
-  }
-  {  // zero the m-map while the tile is in flight
-    uint4* z = reinterpret_cast<uint4*>(sM);
-    for (int i = tid; i < (tileBytes >> 4); i += kFastThreads) z[i] = make_uint4(0, 0, 0, 0);
-  }
-  __syncthreads();  // sBar initialised (and the zeroes visible) before anyone polls
+// One pass of the phases over the strip at threshold t.  `cells`: the cells to test (all of them in the iniThFAST run).
+// The lists are per warp: a warp filters its own rows (A), runs the remaining pair tests on its own word segment (BC) and
+// the exact value on its own pixel segment (P2) without a CTA barrier; the rows of a warp are interleaved over the strip
+// (r = warp, warp + 8, ...), which evens out the segment lengths.  CTA barriers only around the m-map's neighbour reads.
+template <int MODE>
+__device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, const int t, const bool RETRY, const u32 cells) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const u32 lt = (1u << lane) - 1;
+  const int SW = S.SW, SB = S.SB;
+  const u32 K = (u32)(t < 128 ? 127 - t : 255 - t) * 0x01010101u;
+
+  // ---- phase A: a warp per interior row, a lane per aligned word pair (the strip's interior is at most 32 pairs wide) ----
+  int nW = 0;
   {
-    const u32 bar = smem_addr(&sBar);
-    u32 done = 0;
-    while (!done) {
-      asm volatile(
-          "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n selp.u32 %0, 1, 0, p;\n}\n"
-          : "=r"(done) : "r"(bar) : "memory");
+    const int g = ((S.bLo >> 2) & ~1) + 2 * lane;  // first word of this lane's pair
+    u32 m0 = interior_mask(g, S.bLo, S.bHi), m1 = interior_mask(g + 1, S.bLo, S.bHi);
+    if (RETRY) { m0 &= cell_mask(S, g, cells); m1 &= cell_mask(S, g + 1, cells); }
+    const bool act = (m0 | m1) != 0;
+    for (int r = warp; r < S.nR; r += kFastWarps) {
+      u32 a0 = 0, a1 = 0;
+      if (act) {
+        const u32* p = S.imgW + (r + 3) * SW + g;
+        const uint2 c = *reinterpret_cast<const uint2*>(p);
+        const uint2 n = *reinterpret_cast<const uint2*>(p - 3 * SW);
+        const uint2 s = *reinterpret_cast<const uint2*>(p + 3 * SW);
+        const u32 l = p[-1], q = p[2];
+        a0 = m0 & any_gt<MODE>(__vabsdiffu4(c.x, n.x), __vabsdiffu4(c.x, s.x), K);
+        a1 = m1 & any_gt<MODE>(__vabsdiffu4(c.y, n.y), __vabsdiffu4(c.y, s.y), K);
+        a0 &= any_gt<MODE>(__vabsdiffu4(c.x, word_at<3>(l, c.x, c.y)), __vabsdiffu4(c.x, word_at<-3>(l, c.x, c.y)), K);
+        a1 &= any_gt<MODE>(__vabsdiffu4(c.y, word_at<3>(c.x, c.y, q)), __vabsdiffu4(c.y, word_at<-3>(c.x, c.y, q)), K);
+      }
+      const u32 b0 = __ballot_sync(0xffffffffu, a0 != 0), b1 = __ballot_sync(0xffffffffu, a1 != 0);
+      const u32 e = ((u32)(r + 3) << 8) | (u32)g;
+      if (a0) S.segW[nW + __popc(b0 & lt)] = a0 | e;
+      nW += __popc(b0);
+      if (a1) S.segW[nW + __popc(b1 & lt)] = a1 | (e + 1);
+      nW += __popc(b1);
     }
   }
-
-  const int tIni = min(max(P.iniTh, 0), 255), tMin = min(max(P.minTh, 0), 255);
-  const int tq = min(tIni, tMin);
-  const int bLo = off + 3, bHi = off + cw - 3;  // interior bytes [bLo, bHi)
-  const int g0 = bLo >> 2, g1 = (bHi - 1) >> 2;
-  const int nW = g1 - g0 + 1, nR = ch - 6;
-
-  // pass 1: opposing-pair rejection on 4 pixels at a time, items = (interior row, word) flattened over the CTA
-  {
-    const u32 K = (u32)(tq < 128 ? 127 - tq : 255 - tq) * 0x01010101u;
-    // items = (pair of interior rows, word): thread-private indices advance by the CTA size, row-major
-    const int nRP = (nR + 1) >> 1;
-    const int stepR = kFastThreads / nW, stepG = kFastThreads - stepR * nW;
-    const int nIter = (nRP * nW + kFastThreads - 1) / kFastThreads;  // the same trip count for every lane: warp collectives below
-    const int lane = tid & 31;
-    int rp = tid / nW, g = tid - rp * nW;
-    for (int it = 0; it < nIter; ++it, rp += stepR, g += stepG) {
-      if (g >= nW) { g -= nW; ++rp; }
-      u32 aliveA = 0, aliveB = 0;
-      const int gw = g0 + g, ry = 2 * rp;
-      if (ry < nR) {
-        u32 m = 0x80808080u;
-        if (4 * gw < bLo) m &= 0xffffffffu << (8 * (bLo - 4 * gw));
-        if (4 * gw + 4 > bHi) m &= 0xffffffffu >> (8 * (4 * gw + 4 - bHi));
-        aliveA = m;
-        aliveB = ry + 1 < nR ? m : 0u;  // the row below the last interior row is staged (apron) but not tested
-        const u32* r0 = sImgW + (ry + 3) * SW;
-        if (tq >= 128) pass1_words<2>(r0, SW, gw, aliveA, aliveB, K);
-        else if ((tq & (tq + 1)) == 0) pass1_words<0>(r0, SW, gw, aliveA, aliveB, K);
-        else pass1_words<1>(r0, SW, gw, aliveA, aliveB, K);
-      }
-      // append: the list order is irrelevant (pass 2 / 3 take any order, the emission carries its own order key), so a
-      // lane with survivors just reserves its slots
-      const int cnt = __popc(aliveA) + __popc(aliveB);
-      if (cnt == 0) continue;
-      int base = atomicAdd(&sN, cnt);
-      while (aliveA) {
-        const int j = (__ffs((int)aliveA) - 1) >> 3;
-        aliveA &= aliveA - 1;
-        sList[base++] = (unsigned short)(((ry + 3) << 8) | (4 * gw + j));
-      }
-      while (aliveB) {
-        const int j = (__ffs((int)aliveB) - 1) >> 3;
-        aliveB &= aliveB - 1;
-        sList[base++] = (unsigned short)(((ry + 4) << 8) | (4 * gw + j));
+  __syncwarp();
+  // ---- phase BC: a lane per listed word of this warp, the other six opposing pairs ----
+  int nP = 0;
+  for (int i0 = 0; i0 < nW; i0 += 32) {
+    const int i = i0 + lane;
+    u32 alive = 0, e = 0;
+    if (i < nW) {
+      e = S.segW[i];
+      alive = e & 0x80808080u;
+      const int g = e & 0x7f;
+      const u32* r0 = S.imgW + ((e >> 8) & 0x7f) * SW;
+      const Row3 rm3 = load3(r0 - 3 * SW, g), r00 = load3(r0, g), rp3 = load3(r0 + 3 * SW, g);
+      const u32 cc = r00.c;
+      alive &= any_gt<MODE>(__vabsdiffu4(cc, word_at<1>(rp3.l, rp3.c, rp3.r)), __vabsdiffu4(cc, word_at<-1>(rm3.l, rm3.c, rm3.r)), K);
+      alive &= any_gt<MODE>(__vabsdiffu4(cc, word_at<1>(rm3.l, rm3.c, rm3.r)), __vabsdiffu4(cc, word_at<-1>(rp3.l, rp3.c, rp3.r)), K);
+      if (alive) {
+        const Row3 rm2 = load3(r0 - 2 * SW, g), rm1 = load3(r0 - SW, g), rp1 = load3(r0 + SW, g), rp2 = load3(r0 + 2 * SW, g);
+        alive = pairs_rows_1_2<MODE>(alive, cc, rm2, rm1, rp1, rp2, K);
       }
     }
+    __syncwarp();
+    // append the alive pixels: one ballot per byte position
+    const u32 b0 = __ballot_sync(0xffffffffu, alive & 0x80u), b1 = __ballot_sync(0xffffffffu, alive & 0x8000u);
+    const u32 b2 = __ballot_sync(0xffffffffu, alive & 0x800000u), b3 = __ballot_sync(0xffffffffu, alive & 0x80000000u);
+    const int n0 = nP + __popc(b0), n1 = n0 + __popc(b1), n2 = n1 + __popc(b2);
+    const u32 pe = ((e & 0x7f00u) << 1) | ((e & 0x7fu) << 2);  // row << 9 | 4 * word
+    if (alive & 0x80u) S.segP[nP + __popc(b0 & lt)] = (unsigned short)pe;
+    if (alive & 0x8000u) S.segP[n0 + __popc(b1 & lt)] = (unsigned short)(pe + 1);
+    if (alive & 0x800000u) S.segP[n1 + __popc(b2 & lt)] = (unsigned short)(pe + 2);
+    if (alive & 0x80000000u) S.segP[n2 + __popc(b3 & lt)] = (unsigned short)(pe + 3);
+    nP = n2 + __popc(b3);
   }
-  __syncthreads();
-  const int n = sN;
-  // pass 2: exact segment-test value of the surviving pixels (ring offsets in cv::FAST order)
-  for (int i = tid; i < n; i += kFastThreads) {
-    const int e = sList[i], ry = e >> 8, b = e & 255;
+  __syncwarp();
+  // ---- phase P2: exact segment-test value of the surviving pixels (ring offsets in cv::FAST order) ----
+  const u8* sImg = reinterpret_cast<const u8*>(S.imgW);
+  for (int i = lane; i < nP; i += 32) {
+    const int e = S.segP[i], ry = e >> 9, b = e & 511;
     const u8* p = sImg + ry * SB + b;
     const u32 vb = ((256u - (u32)p[0]) << 16) | ((u32)p[0] + 256u);
     u32 x[16];
@@ -222,58 +232,168 @@ __global__ void __launch_bounds__(kFastThreads) k_fast(const __grid_constant__ P
     x[8] = ring_pack(vb, p[-3 * SB]); x[9] = ring_pack(vb, p[-3 * SB - 1]); x[10] = ring_pack(vb, p[-2 * SB - 2]); x[11] = ring_pack(vb, p[-SB - 3]);
     x[12] = ring_pack(vb, p[-3]); x[13] = ring_pack(vb, p[SB - 3]); x[14] = ring_pack(vb, p[2 * SB - 2]); x[15] = ring_pack(vb, p[3 * SB - 1]);
     const int m = arc_value(x);
-    if (m > tq) sM[ry * SB + b] = (u8)m;
+    if (m > t) S.mm[ry * SB + b] = (u8)m;
   }
   __syncthreads();
-  // pass 3: strict 3x3 maxima with m >= 2, written behind the pass-1 list
-  unsigned short* sPk = sList + n;
-  for (int i = tid; i < n; i += kFastThreads) {
-    const int e = sList[i], ry = e >> 8, b = e & 255;
-    const u8* q = sM + ry * SB + b;
-    const int m = q[0];
-    if (m >= 2 && m > q[-1] && m > q[1] && m > q[-SB - 1] && m > q[-SB] && m > q[-SB + 1] &&
-        m > q[SB - 1] && m > q[SB] && m > q[SB + 1]) {
-      sPk[atomicAdd(&sPeaks, 1)] = (unsigned short)e;
-      if (m > tIni) atomicAdd(&sIni, 1);
-      if (m > tMin) atomicAdd(&sMin, 1);
+  // ---- phase P3: strict 3x3 maxima inside the pixel's own cell (branch-free: 60 % of the listed pixels are corners) ----
+  int nK = 0;
+  unsigned short* const segK = reinterpret_cast<unsigned short*>(S.segW);
+  for (int i0 = 0; i0 < nP; i0 += 32) {
+    const int i = i0 + lane;
+    bool peak = false;
+    int e = 0;
+    if (i < nP) {
+      e = S.segP[i];
+      const int ry = e >> 9, b = e & 511;
+      const u8* q = S.mm + ry * SB + b;
+      const int m = q[0];
+      const int xb = b - S.bLo;
+      const int j = (int)(((u32)xb * S.cellMul) >> 16), cs = j * S.wCell;
+      // the columns left of the cell's first and right of its last interior column belong to another cell: they count as 0
+      const int mL = xb != cs ? max(max((int)q[-SB - 1], (int)q[-1]), (int)q[SB - 1]) : 0;
+      const int mR = xb + 1 != cs + S.wCell ? max(max((int)q[-SB + 1], (int)q[1]), (int)q[SB + 1]) : 0;
+      const int mN = max(max((int)q[-SB], (int)q[SB]), max(mL, mR));
+      peak = m >= 2 && m > mN;
+      if (peak && !RETRY) S.cellIni[j] = 1;
+    }
+    const u32 bp = __ballot_sync(0xffffffffu, peak);
+    if (peak) segK[nK + __popc(bp & lt)] = (unsigned short)e;
+    nK += __popc(bp);
+  }
+  __syncwarp();
+  // ---- phase P4: the keypoints of this run go to the level's candidate list ----
+  if (nK > 0) {
+    const size_t co = (size_t)S.slot * P.candTotal + S.candOff;
+    const u8* rootTab = P.rootTab + S.rootTabOff;
+    u32 k0 = 0;  // one global atomic per warp: its keypoints take consecutive slots
+    if (lane == 0) k0 = atomicAdd(P.candCount + (size_t)S.slot * kMaxLevels + S.level, (u32)nK);
+    k0 = __shfl_sync(0xffffffffu, k0, 0);
+    if (k0 + (u32)nK > (u32)S.candCap) {
+      if (lane == 0) atomicMin(P.status + S.slot, ORBX_ERR_CAPACITY);
+    } else {
+      for (int i = lane; i < nK; i += 32) {
+        const u32 pk = segK[i], k = k0 + (u32)i;
+        const int ry = (int)(pk >> 9), b = (int)(pk & 511), xb = b - S.bLo;
+        const int m = S.mm[ry * SB + b];
+        const int j = (int)(((u32)xb * S.cellMul) >> 16);
+        const int rx = xb - j * S.wCell + 3;  // ROI-relative column in the pixel's cell; the reference shifts by the cell origin (:1134-1135)
+        const int x = xb + 3 + S.sx, y = ry + S.sy;  // relative to (16,16)
+        const u32 order = ((u32)(S.index0 + j) << 14) | ((u32)ry << 7) | (u32)rx;
+        P.candKey[co + k] = ((u64)(u32)(m - 1) << 32) | (u64)(~order);
+        P.candXY[co + k] = (u32)x | ((u32)y << 16);
+        P.candNode[co + k] = (u32)(S.nIniM1 - __ldg(rootTab + x));  // root i lives at node nIni-1-i
+      }
     }
   }
-  __syncthreads();
-  const int th = sIni > 0 ? tIni : tMin;
-  const int nEmit = sIni > 0 ? sIni : sMin;
-  if (nEmit == 0) return;
-  u32* cnt = P.candCount + (size_t)slot * kMaxLevels + c.level;
-  if (tid == 0) sBase = (int)atomicAdd(cnt, (u32)nEmit);
-  __syncthreads();
-  const int base = sBase;
-  if (base + nEmit > L.candCap) {
-    if (tid == 0) atomicMin(P.status + slot, ORBX_ERR_CAPACITY);
-    return;
+  __syncthreads();  // every neighbour read of the m-map is done
+  for (int i = lane; i < nP; i += 32) {  // the m-map entries of this run are cleared
+    const int e = S.segP[i];
+    S.mm[(e >> 9) * SB + (e & 511)] = 0;
   }
-  const size_t co = (size_t)slot * P.candTotal + L.candOff + base;
-  const u8* rootTab = P.rootTab + L.rootTabOff;
-  const int np = sPeaks;
-  for (int i = tid; i < np; i += kFastThreads) {
-    const int e = sPk[i], ry = e >> 8, b = e & 255;
-    const int m = sM[ry * SB + b];
-    if (m > th) {
-      const int k = atomicAdd(&sCursor, 1);
-      const int rx = b - off;  // ROI-relative column; the reference shifts by the cell origin (:1134-1135)
-      const int x = rx + c.sx, y = ry + c.sy;  // relative to (16,16)
-      const u32 order = ((u32)c.index << 14) | ((u32)ry << 7) | (u32)rx;
-      P.candKey[co + k] = ((u64)(u32)(m - 1) << 32) | (u64)(~order);
-      P.candXY[co + k] = (u32)x | ((u32)y << 16);
-      P.candNode[co + k] = (u32)(L.nIni - 1 - __ldg(rootTab + x));  // root i lives at node nIni-1-i
+}
+
+__device__ __forceinline__ void fast_run_mode(const Params& P, const StripCtx& S, int t, bool retry, u32 cells) {
+  if (t >= 128) fast_run<1>(P, S, t, retry, cells);
+  else fast_run<0>(P, S, t, retry, cells);
+}
+
+__global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k_fast(const __grid_constant__ Params P, const __grid_constant__ TmaMaps M, const int nItems) {
+  extern __shared__ __align__(128) u8 smem[];
+  __shared__ __align__(8) u64 sBar[2];
+  __shared__ int sCellIni[32];
+  const int tid = threadIdx.x;
+  u8* const sMm = smem + kFastStages * P.fastTileMax;
+  u32* const sSegW = reinterpret_cast<u32*>(sMm + P.fastTileMax) + (tid >> 5) * P.fastSegW;
+  unsigned short* const sSegP = reinterpret_cast<unsigned short*>(reinterpret_cast<u32*>(sMm + P.fastTileMax) + kFastWarps * P.fastSegW) + (tid >> 5) * P.fastSegP;
+
+  {
+    uint4* z = reinterpret_cast<uint4*>(sMm);  // the m-map starts out zero and every run leaves it zero
+    for (int i = tid; i < (P.fastTileMax >> 4); i += kFastThreads) z[i] = make_uint4(0, 0, 0, 0);
+  }
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&sBar[0])));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&sBar[1])));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+
+  // The items of this CTA are blockIdx.x, blockIdx.x + gridDim.x, ...; item = slot * nStrips + strip, walked without divisions.
+  const int stepSlot = (int)gridDim.x / P.nStrips, stepStrip = (int)gridDim.x - stepSlot * P.nStrips;
+  int item = blockIdx.x, slot = item / P.nStrips, strip = item - slot * P.nStrips;
+  auto load_desc = [&](int st) {
+    union { uint4 q[3]; StripDesc d; } u;
+    const uint4* g = reinterpret_cast<const uint4*>(P.strips + st);
+    u.q[0] = __ldg(g); u.q[1] = __ldg(g + 1); u.q[2] = __ldg(g + 2);
+    return u.d;
+  };
+  // thread 0: one TMA tile copy of a strip of a slot into ring buffer `buf`
+  auto issue = [&](int sl, const StripDesc& d, int buf) {
+    const u32 bar = smem_addr(&sBar[buf]);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(d.tileBytes) : "memory");
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+        ::"r"(smem_addr(smem + buf * P.fastTileMax)), "l"(reinterpret_cast<u64>(&M.lvl[d.level])), "r"((int)d.tmaX), "r"((int)d.y0),
+          "r"(sl + P.slot0), "r"(bar)
+        : "memory");
+  };
+
+  const int tIni = min(max(P.iniTh, 0), 255), tMin = min(max(P.minTh, 0), 255);
+  if (tid == 0 && item < nItems) issue(slot, load_desc(strip), 0);
+  for (int k = 0; item < nItems; ++k) {
+    const int buf = kFastStages == 1 ? 0 : k & 1;
+    int nslot = slot + stepSlot, nstrip = strip + stepStrip;
+    if (nstrip >= P.nStrips) { nstrip -= P.nStrips; ++nslot; }
+    // the other buffer was last read during item k - 1, which every thread has left (barrier at the end of the loop body)
+    if (kFastStages > 1 && tid == 0 && item + (int)gridDim.x < nItems) issue(nslot, load_desc(nstrip), buf ^ 1);
+    if (tid < 32) sCellIni[tid] = 0;
+    const StripDesc d = load_desc(strip);
+    StripCtx S;
+    S.imgW = reinterpret_cast<const u32*>(smem + buf * P.fastTileMax);
+    S.mm = sMm; S.segW = sSegW; S.segP = sSegP; S.cellIni = sCellIni;
+    S.SB = d.SB; S.SW = S.SB >> 2;
+    S.bLo = d.bLo; S.bHi = d.bHi; S.nR = d.nR;
+    S.wCell = d.wCell; S.cellMul = d.cellMul;
+    S.slot = slot; S.level = d.level; S.sx = d.sx; S.sy = d.sy; S.index0 = d.index0;
+    S.nIniM1 = d.nIniM1; S.candCap = d.candCap; S.candOff = d.candOff; S.rootTabOff = d.rootTabOff;
+    {
+      const u32 bar = smem_addr(&sBar[buf]);
+      const u32 parity = (u32)(kFastStages == 1 ? k : k >> 1) & 1u;
+      u32 done = 0;
+      while (!done) {
+        asm volatile(
+            "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
+            : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+      }
     }
+    fast_run_mode(P, S, tIni, false, 0xffffffffu);
+    if (tMin < tIni) {  // cells without a keypoint at iniThFAST run again at minThFAST (:1119)
+      __syncthreads();  // the cell flags of phase P3 and the cleared m-map
+      const int ln = tid & 31;
+      const u32 retry = __ballot_sync(0xffffffffu, ln < d.nCells && sCellIni[ln] == 0);
+      if (retry) fast_run_mode(P, S, tMin, true, retry);
+    }
+    __syncthreads();
+    if (kFastStages == 1 && tid == 0 && item + (int)gridDim.x < nItems) issue(nslot, load_desc(nstrip), 0);
+    item += gridDim.x; slot = nslot; strip = nstrip;
   }
 }
 
 int launch_fast(const Params& P, const TmaMaps& M, int nSlots, cudaStream_t st) {
-  dim3 grid(P.nCells, nSlots);
-  // image tile + m-map + pass-1 list and peak list (<= 1.25 entries per staged byte, u16 each)
-  const size_t smem = (size_t)P.fastBoxW * P.fastBoxH * 9 / 2 + 64;
-  k_fast<<<grid, kFastThreads, smem, st>>>(P, M);
+  const int nItems = P.nStrips * nSlots;
+  k_fast<<<std::min(nItems, P.fastGrid), kFastThreads, fast_smem_bytes(P), st>>>(P, M, nItems);
   return 1;
+}
+
+// Called once per context (after cudaSetDevice): opts k_fast into its dynamic shared memory and sizes the persistent grid.
+int configure_fast(Params& P) {
+  const size_t smem = fast_smem_bytes(P);
+  if (cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return ORBX_ERR_CUDA;
+  int dev = 0, sms = 0, perSm = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return ORBX_ERR_CUDA;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_fast, kFastThreads, smem) != cudaSuccess || perSm < 1) return ORBX_ERR_CUDA;
+  P.fastGrid = sms * perSm;
+  return ORBX_OK;
 }
 
 }  // namespace orbx

@@ -520,8 +520,7 @@ int launch_match(const Params& P, const MatchArgs& A, int nPairs, int pairStep, 
                  int window, cudaStream_t st) {
   if (nPairs <= 0) return 0;
   const MatchSmem LY = match_smem_layout(A.stride);
-  static const bool forceSerial = std::getenv("ORBX_MATCH_SERIAL") != nullptr;  // test hook for the fallback kernel
-  if (!forceSerial && A.stride < 65535 && LY.total <= 200 * 1024) {
+  if (!P.optMatchSerial && A.stride < 65535 && LY.total <= 200 * 1024) {
     if (cudaFuncSetAttribute(k_match_cta, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess) return 0;
     k_match_cta<<<nPairs, MT, LY.total, st>>>(P, A, pairStep, nnratio, checkOri, window);
   } else {

@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -11,8 +12,9 @@
 
 namespace orbx {
 void build_resize_tab(int sw, int sh, int dw, int dh, std::vector<int>& tab);
-int build_geometry(Params& P, const HostTables& T, std::vector<CellDesc>& cells, std::vector<BlurTile>& tiles,
+int build_geometry(Params& P, const HostTables& T, int fastTileBudget, std::vector<StripDesc>& strips, std::vector<BlurTile>& tiles,
                    std::vector<u8>& rootTab, std::vector<int>& rootEdges);
+int configure_fast(Params& P);
 }
 using namespace orbx;
 
@@ -46,11 +48,13 @@ static int build_tensor_maps(orbx_ctx* c) {
   const Params& P = c->P;
   for (int l = 0; l < P.nlevels; ++l) {
     const LevelInfo& L = P.lv[l];
-    cuuint64_t dims[3] = {(cuuint64_t)L.w, (cuuint64_t)L.h, (cuuint64_t)P.maxBatch};
+    // 32-bit elements (a box dimension is limited to 256 elements); columns between w and the pitch are slab padding
+    // that no tested pixel's ring reaches, rows beyond h are zero-filled
+    cuuint64_t dims[3] = {(cuuint64_t)(L.pitch / 4), (cuuint64_t)L.h, (cuuint64_t)P.maxBatch};
     cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)P.slabBytes};
-    cuuint32_t box[3] = {(cuuint32_t)P.fastBoxW, (cuuint32_t)P.fastBoxH, 1};
+    cuuint32_t box[3] = {(cuuint32_t)(L.fastBoxW / 4), (cuuint32_t)L.fastBoxH, 1};
     cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = ((EncodeFn)fn)(&c->tma.lvl[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, P.pyr + L.imgOff, dims, strides, box, estr,
+    CUresult r = ((EncodeFn)fn)(&c->tma.lvl[l], CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, P.pyr + L.imgOff, dims, strides, box, estr,
                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { c->err = "cuTensorMapEncodeTiled failed: " + std::to_string((int)r); return ORBX_ERR_CUDA; }
@@ -67,12 +71,24 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   std::memset(&P, 0, sizeof(P));
   P.W = width; P.H = height; P.nlevels = nlevels; P.nfeatures = nfeatures;
   P.iniTh = iniTh; P.minTh = minTh; P.maxBatch = maxBatch; P.trigMode = 0;
+  // the only place the environment is read: schedule options of this context
+  auto env_int = [](const char* name, int dflt) {
+    const char* v = std::getenv(name);
+    if (!v) return dflt;
+    return *v ? std::atoi(v) : 1;
+  };
+  P.optSingleStream = env_int("ORBX_SINGLE_STREAM", 0) != 0;
+  P.optRunParts = env_int("ORBX_RUN_PARTS", 0);
+  P.optLanes = env_int("ORBX_LANES", 0);
+  P.optResizeRows = env_int("ORBX_RESIZE_ROWS", 0);
+  P.optMatchSerial = env_int("ORBX_MATCH_SERIAL", 0) != 0;
+  P.optFastTileBudget = std::max(4096, env_int("ORBX_FAST_TILE", 15360));
   std::memcpy(P.umax, c->T.umax, sizeof(P.umax));
-  std::vector<CellDesc> cells;
+  std::vector<StripDesc> strips;
   std::vector<BlurTile> tiles;
   std::vector<u8> rootTab;
   std::vector<int> rootEdges;
-  rc = build_geometry(P, c->T, cells, tiles, rootTab, rootEdges);
+  rc = build_geometry(P, c->T, P.optFastTileBudget, strips, tiles, rootTab, rootEdges);
   if (rc) return rc;
   int kp = 0;
   for (int l = 0; l < nlevels; ++l) kp += P.lv[l].quota;
@@ -101,12 +117,12 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   for (int i = 0; i < 10; ++i) CU(c, cudaEventCreate(&c->evStage[i]));
 
   const size_t B = (size_t)maxBatch;
-  CellDesc* dCells; BlurTile* dTiles; u8* dRootTab; int* dRootEdges;
-  if ((rc = dupload(c, &dCells, cells))) return rc;
+  StripDesc* dStrips; BlurTile* dTiles; u8* dRootTab; int* dRootEdges;
+  if ((rc = dupload(c, &dStrips, strips))) return rc;
   if ((rc = dupload(c, &dTiles, tiles))) return rc;
   if ((rc = dupload(c, &dRootTab, rootTab))) return rc;
   if ((rc = dupload(c, &dRootEdges, rootEdges))) return rc;
-  P.cells = dCells; P.blurTiles = dTiles; P.rootTab = dRootTab; P.rootEdges = dRootEdges;
+  P.strips = dStrips; P.blurTiles = dTiles; P.rootTab = dRootTab; P.rootEdges = dRootEdges;
   c->dResizeTabs.assign(nlevels, nullptr);
   c->hTabPtrs = new const int*[nlevels];
   c->hTabPtrs[0] = nullptr;
@@ -162,6 +178,7 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   if ((rc = dalloc(c, &c->hfScratch, 3 * (size_t)c->hfCap))) return rc;
   if ((rc = dalloc(c, &c->dIngest, B * (size_t)width * height))) return rc;
   if ((rc = build_tensor_maps(c))) return rc;
+  if ((rc = configure_fast(P))) { c->err = "k_fast: shared memory / occupancy configuration failed"; return rc; }
   CU(c, cudaMemset(P.status, 0, B * sizeof(int)));
   CU(c, cudaMemset(P.outN, 0, B * sizeof(int)));
   CU(c, cudaMemset(P.pyr, 0, B * P.slabBytes));
@@ -221,6 +238,17 @@ extern "C" const char* orbx_last_error(const orbx_ctx* c) { return c ? c->err.c_
 extern "C" int orbx_set_trig_mode(orbx_ctx* c, int mode) {
   if (!c || (mode != 0 && mode != 1)) return ORBX_ERR_ARG;
   c->P.trigMode = mode;
+  return ORBX_OK;
+}
+extern "C" int orbx_set_option(orbx_ctx* c, const char* name, int value) {
+  if (!c || !name) return ORBX_ERR_ARG;
+  const std::string n(name);
+  if (n == "single_stream") c->P.optSingleStream = value != 0;
+  else if (n == "run_parts") c->P.optRunParts = value;
+  else if (n == "lanes") c->P.optLanes = value;
+  else if (n == "resize_rows") c->P.optResizeRows = value;
+  else if (n == "match_serial") c->P.optMatchSerial = value != 0;
+  else return ORBX_ERR_ARG;
   return ORBX_OK;
 }
 extern "C" void* orbx_get_stream(orbx_ctx* c) { return c ? (void*)c->stream : nullptr; }

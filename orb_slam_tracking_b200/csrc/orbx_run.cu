@@ -65,8 +65,7 @@ int enqueue_extract(orbx_ctx* c, const Params& P, int n, int lap0, int lap1, cud
   // everything stays on one stream so that the stage events bracket one kernel each.
   int side = 0;
   for (int i = 1; i < orbx_ctx::kLanes; ++i) if (st == c->sLane[i]) side = i;
-  static const bool singleStream = std::getenv("ORBX_SINGLE_STREAM") != nullptr;
-  const bool fork = !c->stageTiming && !singleStream;
+  const bool fork = !c->stageTiming && !P.optSingleStream;
   c->launches += launch_fast(P, c->tma, n, st);
   mark(c, 2);
   if (fork) {  // forked AFTER FAST (itself issue-bound): the blur then shares the SMs with the quadtree only
@@ -285,10 +284,8 @@ extern "C" int orbx_stream_run(orbx_ctx* c, int n_img, float nnratio, int check_
   CU(c, cudaSetDevice(c->device));
   c->launches = 0;
   int rc;
-  static const bool single = std::getenv("ORBX_SINGLE_STREAM") != nullptr;  // profiling aid: whole-batch launches in order
-  static const int partsEnv = std::getenv("ORBX_RUN_PARTS") ? std::atoi(std::getenv("ORBX_RUN_PARTS")) : 0;
-  const int parts = std::min(orbx_ctx::kLanes, std::max(1, partsEnv > 0 ? partsEnv : 2));
-  if (n_img >= 64 * parts && parts > 1 && !c->stageTiming && !single) {
+  const int parts = std::min(orbx_ctx::kLanes, std::max(1, P.optRunParts > 0 ? P.optRunParts : 2));
+  if (n_img >= 64 * parts && parts > 1 && !c->stageTiming && !P.optSingleStream) {
     // the batch in `parts` pieces (each a whole number of pairs), one per compute lane: the latency-bound kernels of
     // one piece (quadtree, matcher) overlap the issue-bound ones of the others; all pieces fence on the context's stream
     CU(c, cudaEventRecord(c->evLane[0], c->stream));
@@ -409,7 +406,7 @@ int process_enqueue(orbx_ctx* c, const uint8_t* imgs, int n_img, float nnratio, 
   c->stageTiming = 0;  // per-stage events belong to the unchunked orbx_stream_run
   c->launches = 0;
   int* hStatus = c->hStatus + (size_t)ticket * P.maxBatch;
-  static const int lanesEnv = std::getenv("ORBX_LANES") ? std::atoi(std::getenv("ORBX_LANES")) : 0;
+  const int lanesEnv = P.optLanes;
   // A stream of steps stays off lane 0: lane 0 is the context's stream, which joins every step's fence (below) so that
   // later calls on it come after the step -- as a compute lane it would stall the next step behind this step's download.
   const int lane0 = streaming ? 1 : 0;

@@ -196,8 +196,7 @@ int launch_pyramid(const Params& P, const int* const* dTabs, int nSlots, cudaStr
   int n = 0;
   for (int l = 1; l < P.nlevels; ++l) {
     dim3 block(32, kResizeWarps);
-    static const int rowsEnv = std::getenv("ORBX_RESIZE_ROWS") ? std::atoi(std::getenv("ORBX_RESIZE_ROWS")) : 0;
-    const int rows = rowsEnv > 0 ? rowsEnv : kResizeRows;
+    const int rows = P.optResizeRows > 0 ? P.optResizeRows : kResizeRows;
     dim3 grid((P.lv[l].w + 127) / 128, (P.lv[l].h + rows * kResizeWarps - 1) / (rows * kResizeWarps), nSlots);
     // taps of 4 adjacent output columns span 3 * scale + 2 source bytes
     if (P.lv[l - 1].w > 2 * P.lv[l].w + 1) k_resize<true><<<grid, block, 0, st>>>(P, l, dTabs[l], rows);

@@ -88,12 +88,12 @@ static inline u32 align_up(u32 v, u32 a) { return (v + a - 1) / a * a; }
 // Returns ORBX_ERR_ARG for shapes on which the reference itself is undefined (a level narrower
 // than 67 px gives nCols == 0 and a division by zero at :1073) and ORBX_ERR_ASPECT where
 // DistributeOctTree would index an empty root vector (:706, aspect ratio rounding to 0).
-int build_geometry(Params& P, const HostTables& T, std::vector<CellDesc>& cells, std::vector<BlurTile>& tiles,
+int build_geometry(Params& P, const HostTables& T, int fastTileBudget, std::vector<StripDesc>& strips, std::vector<BlurTile>& tiles,
                    std::vector<u8>& rootTab, std::vector<int>& rootEdges) {
   u32 imgOff = 0, candOff = 0, nodeOff = 0;
   int kpOff = 0;
-  cells.clear(); tiles.clear(); rootTab.clear(); rootEdges.clear();
-  int maxCw = 7, maxCh = 7;
+  strips.clear(); tiles.clear(); rootTab.clear(); rootEdges.clear();
+  int tileMax = 0, listW = 0, listP = 0;
   for (int l = 0; l < P.nlevels; ++l) {
     LevelInfo& L = P.lv[l];
     L.w = cv_round_f((float)P.W * T.invScale[l]);  // :1662-1663
@@ -118,29 +118,77 @@ int build_geometry(Params& P, const HostTables& T, std::vector<CellDesc>& cells,
     L.wCell = (int)std::ceil(width / L.nCols);
     L.hCell = (int)std::ceil(height / L.nRows);
     if (L.wCell + 6 > kMaxCellDim || L.hCell + 6 > kMaxCellDim) return ORBX_ERR_ARG;
-    L.cellBase = (int)cells.size();
+    const u32 cellMul = 65535u / (u32)L.wCell + 1;  // exact floor(xb / wCell) for xb * wCell < 65536 (strip interiors are < 1024 wide)
+    // The cells of a cell row that cv::FAST can find anything in are j = 0 .. nValid - 1 (the skipped and the
+    // degenerate ones are at the end, :1101); their tested interiors tile [19, maxBX - 3) without gaps.
+    int nValid = 0, lastMaxX = 0;
+    for (int j = 0; j < L.nCols; ++j) {
+      const float iniX = (float)(minBX + j * L.wCell);
+      float maxX = iniX + L.wCell + 6;
+      if (iniX >= maxBX - 6) continue;  // :1101
+      if (maxX > maxBX) maxX = (float)maxBX;
+      if ((int)maxX - (int)iniX - 6 < 1) continue;  // cv::FAST yields nothing for ROIs under 7 px
+      if (j != nValid) return ORBX_ERR_ARG;  // cannot happen: skipped cells only follow valid ones
+      nValid = j + 1;
+      lastMaxX = (int)maxX;
+    }
+    // k_fast works on strips: a cell row cut into nSplit runs of cells whose staged tile fits the shared-memory budget.
+    // Staged row: up to 16 bytes of alignment apron + ROI + the word right of the last interior word, as an odd multiple
+    // of 16 bytes (rows 8 apart then share a bank instead of every row).
+    const int boxH = std::min(L.hCell + 6, maxBY - minBY);
+    int nSplit = 1, perStrip = nValid;
+    auto box_w = [&](int nc) {
+      u32 w = align_up((u32)(nc * L.wCell + 6 + 20), 16);
+      if (((w / 16) & 1) == 0) w += 16;
+      return (int)w;
+    };
+    for (;; ++nSplit) {
+      perStrip = (nValid + nSplit - 1) / nSplit;
+      // phase A of k_fast gives one lane to each aligned pair of interior words: at most 32 pairs (244 + 6 columns) per strip
+      if (perStrip <= 1 || (perStrip <= 24 && perStrip * L.wCell <= 244 && box_w(perStrip) * boxH <= fastTileBudget)) break;
+    }
+    if (nValid < 1) return ORBX_ERR_ARG;
+    L.fastBoxW = box_w(perStrip);
+    L.fastBoxH = boxH;
+    if (L.fastBoxW > 508 || boxH > 127 || perStrip * L.wCell > 244) return ORBX_ERR_ARG;  // list entries: 9 bits of byte column, 7 bits of row
+    tileMax = std::max(tileMax, L.fastBoxW * L.fastBoxH);
     int cap = 0;
     for (int i = 0; i < L.nRows; ++i) {
       const float iniY = (float)(minBY + i * L.hCell);
       float maxY = iniY + L.hCell + 6;
       if (iniY >= maxBY - 3) continue;  // :1088
       if (maxY > maxBY) maxY = (float)maxBY;
-      for (int j = 0; j < L.nCols; ++j) {
-        const float iniX = (float)(minBX + j * L.wCell);
-        float maxX = iniX + L.wCell + 6;
-        if (iniX >= maxBX - 6) continue;  // :1101
-        if (maxX > maxBX) maxX = (float)maxBX;
-        CellDesc c;
-        c.level = (short)l; c.pad = 0;
-        c.x0 = (short)iniX; c.y0 = (short)iniY; c.x1 = (short)maxX; c.y1 = (short)maxY;
-        c.sx = (short)(j * L.wCell); c.sy = (short)(i * L.hCell);
-        c.index = i * L.nCols + j;
-        const int iw = c.x1 - c.x0 - 6, ih = c.y1 - c.y0 - 6;
-        if (iw < 1 || ih < 1) continue;  // cv::FAST yields nothing for ROIs under 7 px
-        cells.push_back(c);
-        maxCw = std::max(maxCw, c.x1 - c.x0);
-        maxCh = std::max(maxCh, c.y1 - c.y0);
-        cap += ((iw + 1) / 2) * ((ih + 1) / 2);  // NMS survivors are never 8-adjacent
+      const int ih = (int)maxY - (int)iniY - 6;
+      if (ih < 1) continue;
+      for (int j0 = 0; j0 < nValid; j0 += perStrip) {
+        const int j1 = std::min(nValid, j0 + perStrip);
+        StripDesc s;
+        const int x0 = minBX + j0 * L.wCell;
+        const int x1 = j1 == nValid ? lastMaxX : minBX + (j1 - 1) * L.wCell + L.wCell + 6;
+        // the tile starts at the 16-byte aligned column xs <= x0 - 1 of the level, so byte b of a staged row <-> level
+        // column xs + b, and the word left of the first interior word is always staged
+        const int xs = (x0 - 1) & ~15, off = x0 - xs;
+        s.level = (short)l; s.nCells = (short)(j1 - j0);
+        s.tmaX = (short)(xs >> 2); s.y0 = (short)iniY;
+        s.SB = (short)L.fastBoxW;
+        s.bLo = (short)(off + 3); s.bHi = (short)(off + (x1 - x0) - 3);
+        s.nR = (short)ih;
+        s.wCell = (short)L.wCell;
+        s.sx = (short)(j0 * L.wCell); s.sy = (short)(i * L.hCell);
+        s.nIniM1 = 0;  // level fields that are not known yet are filled in below
+        s.tileBytes = L.fastBoxW * L.fastBoxH;
+        s.cellMul = cellMul;
+        s.index0 = i * L.nCols + j0;
+        s.candOff = 0; s.candCap = 0; s.rootTabOff = 0;
+        strips.push_back(s);
+        // per-warp list segments of k_fast (rows r = warp, warp + kFastWarps, ...): every word / pixel of its rows may be listed
+        const int iwS = x1 - x0 - 6, rowsPerWarp = (ih + kFastWarps - 1) / kFastWarps;
+        listW = std::max(listW, rowsPerWarp * (iwS / 4 + 4));
+        listP = std::max(listP, rowsPerWarp * iwS);
+        for (int j = j0; j < j1; ++j) {
+          const int iw = std::min(L.wCell, x1 - 3 - (x0 + 3 + (j - j0) * L.wCell));
+          cap += ((iw + 1) / 2) * ((ih + 1) / 2);  // NMS survivors are never 8-adjacent
+        }
       }
     }
     if ((u32)(L.nCols * L.nRows) >= (1u << 18)) return ORBX_ERR_ARG;  // order key has 18 cell bits
@@ -163,6 +211,8 @@ int build_geometry(Params& P, const HostTables& T, std::vector<CellDesc>& cells,
     L.nodeCap = 8 * L.quota + 64 + 4 * L.nIni;
     if (L.nodeCap >= (1 << 24) || L.candCap >= (1 << 24)) return ORBX_ERR_ARG;  // packed sort words: 24-bit count and node id
     L.nodeOff = nodeOff;
+    for (StripDesc& sd : strips)
+      if (sd.level == l) { sd.nIniM1 = (short)(L.nIni - 1); sd.candOff = L.candOff; sd.candCap = L.candCap; sd.rootTabOff = L.rootTabOff; }
     nodeOff += align_up((u32)L.nodeCap, 32);
     // blur strips of 120 x 64 (one warp each)
     for (int y = 0; y < L.h; y += 64)
@@ -175,9 +225,10 @@ int build_geometry(Params& P, const HostTables& T, std::vector<CellDesc>& cells,
   P.slabBytes = imgOff;
   P.candTotal = candOff;
   P.nodeTotal = nodeOff;
-  P.nCells = (int)cells.size();
-  P.fastBoxW = (int)align_up((u32)maxCw + 20, 16);  // up to 16 bytes of alignment apron + ROI + the word right of the last interior word
-  P.fastBoxH = maxCh;
+  P.nStrips = (int)strips.size();
+  P.fastTileMax = (int)align_up((u32)tileMax, 128);
+  P.fastSegW = (listW + 7) & ~7;
+  P.fastSegP = (listP + 7) & ~7;
   P.nBlurTiles = (int)tiles.size();
   return ORBX_OK;
 }

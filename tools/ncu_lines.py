@@ -26,7 +26,7 @@ for l in dis.splitlines():
     m = re.search(r'//## File "([^"]+)", line (\d+)', l)
     if m:
         cur = (os.path.basename(m.group(1)), int(m.group(2))); continue
-    if re.match(r"\s+/\*[0-9a-f]{4}\*/", l):
+    if re.match(r"\s+/\*[0-9a-f]{4,}\*/", l):
         lines.append(cur)
 n = min(len(lines), len(sass))
 if len(lines) != len(sass): print("warning: %d disasm vs %d ncu instructions" % (len(lines), len(sass)))
