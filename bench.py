@@ -30,11 +30,13 @@ WORKLOADS = {
     "tum": dict(W=640, H=480, nfeatures=1000, ini=20, mn=7, batch=512, desc="synthetic TUM-shape 640x480, 1000 kp"),
     "euroc": dict(W=752, H=480, nfeatures=1200, ini=20, mn=7, batch=512, desc="synthetic EuRoC-shape 752x480, 1200 kp"),
     "kitti": dict(W=1241, H=376, nfeatures=2000, ini=20, mn=7, batch=256, desc="synthetic KITTI-shape 1241x376, 2000 kp"),
-    "uhd": dict(W=3840, H=2160, nfeatures=8000, ini=20, mn=7, batch=64, desc="synthetic 3840x2160, 8000 kp"),
+    # configs[4]: brute-force matching = SearchForInitialization with a window that covers the image
+    "uhd": dict(W=3840, H=2160, nfeatures=8000, ini=20, mn=7, batch=64, window=8192,
+                desc="synthetic 3840x2160, 8000 kp, all-pairs window"),
 }
 METRIC = "ORB frames/s (extract+match, 640x480, 1k kp)"
 UNIT = "frames/s"
-NNRATIO, WINDOW = 0.9, 100
+NNRATIO, WINDOW = 0.9, 100  # WINDOW: default; a workload may carry its own
 STAGES = ["pyramid", "fast", "quadtree", "blur", "describe", "pack", "glue", "match"]
 
 
@@ -134,7 +136,7 @@ def cpu_baseline(wl, n_frames, threads, target_s=12.0, repeats=None):
     impl, kind = cpu_impl()
     imgs = synth.tile_frames(n_frames, wl["W"], wl["H"], unique_pairs=min(8, n_frames // 2))
     K4, D4 = synth.camera_for(wl["W"], wl["H"])
-    a = (wl["nfeatures"], 1.2, 8, wl["ini"], wl["mn"], K4, D4, WINDOW, NNRATIO, threads)
+    a = (wl["nfeatures"], 1.2, 8, wl["ini"], wl["mn"], K4, D4, wl.get("window", WINDOW), NNRATIO, threads)
     t = time.perf_counter()
     impl.run_stream(imgs, *a)  # warm-up pass, also calibrates the repeat count
     once = time.perf_counter() - t
@@ -170,7 +172,7 @@ def run_reference(args, wl):
         "impl": "reference", "metric": METRIC, "value": fps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": wl["desc"], "frames_per_step": per_step, "nnratio": NNRATIO, "window": WINDOW},
+        "config": {"workload": wl["desc"], "frames_per_step": per_step, "nnratio": NNRATIO, "window": wl.get("window", WINDOW)},
         "cpu_baseline": {"value": fps, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": fps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }), flush=True)
@@ -214,6 +216,7 @@ def run_ours(args, wl):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     B = args.batch or wl["batch"]
     B -= B % 2
+    WINDOW = wl.get("window", 100)
     W, H, nf = wl["W"], wl["H"], wl["nfeatures"]
     L = capi.lib()
     E = fe.ORBextractor(nf, 1.2, 8, wl["ini"], wl["mn"], W, H, max_batch=B, device=local)
@@ -353,6 +356,17 @@ def run_ours(args, wl):
             dt = time.perf_counter() - t0
             scoring["cpu"] = {"hypothesis_match_evals_per_s": ev / dt, "cores": 1, "kind": "reference" if use_ref else "port",
                               "sample": "%d pairs x %d hypotheses x 2 models" % (min(nP, 8), nh)}
+    # raw all-pairs Hamming best / second best, 8000 x 8000 descriptors (the matcher's distance matrix at
+    # BASELINE.json configs[4] without geometry), outside every timed region above
+    brute = None
+    if rank == 0:
+        rng = np.random.default_rng(7)
+        da = rng.integers(0, 256, (8000, 32), dtype=np.uint8)
+        db = rng.integers(0, 256, (8000, 32), dtype=np.uint8)
+        _, _, _, bf_ms = E.hamming_best2(da, db, repeats=20)
+        brute = {"queries": 8000, "candidates": 8000, "kernel": "k_hamming_topk", "kernel_ms": round(bf_ms, 4),
+                 "pairs_per_s": 64e6 / (bf_ms * 1e-3), "popc32_per_s": 8 * 64e6 / (bf_ms * 1e-3),
+                 "note": "integer / popc pipe utilisation of this kernel: profiles/ (ncu)"}
     L.orbx_set_stage_timing(E._h, 0)
     # sanity of the work done: every frame produced keypoints and pairs produced matches
     n_out = np.ctypeslib.as_array(C.cast(res["n"], C.POINTER(C.c_int32)), shape=(B,)).copy()
@@ -394,7 +408,7 @@ def run_ours(args, wl):
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "launches_per_step": n_launch_dom,
                          "ms_per_step": dom_ms, "algorithmic_bytes_per_step": int(ab[dom] * B)},
         }
-        line["next_rows"] = {"init_scoring": scoring}
+        line["next_rows"] = {"init_scoring": scoring, "brute_force_hamming": brute}
         if world == 1 and not args.no_cpu:
             threads = host_threads()
             n_cpu = max(16 * threads, 64) if W * H < 2_000_000 else 2 * threads

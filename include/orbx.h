@@ -115,6 +115,28 @@ int orbx_get_candidates(orbx_ctx* ctx, int slot, int level, float* xyr, int cap)
 /* keypoints of one level after distribution + orientation (+ descriptors), level coordinates */
 int orbx_get_level_keypoints(orbx_ctx* ctx, int slot, int level, orbx_keypoint* kps, uint8_t* desc, int cap);
 
+/* ---- brute-force matching: the distance matrix of one pair sharded by query rows ---------- */
+/* SearchForInitialization(F1, F2) with a window that makes most of F2 a candidate of every query is a
+ * (level-0 keys of F1) x (level-0 keys of F2) Hamming matrix.  orbx_search_for_initialization computes it on
+ * all SMs of one GPU; these two calls split it over GPUs by query rows (north_star: "Hamming matrix sharded by
+ * query rows", no collective -- F2's descriptors are uploaded to every rank):
+ *   orbx_match_rows     rows [q0, q1) of the matrix, reduced to each query's sorted list of its 7 best
+ *                       candidates: rows_out[(q1 - q0)][8] words (7 keys = distance << 20 | visiting position,
+ *                       1 info word).  *n_queries = number of level-0 keys of F1.  Returns the rows written.
+ *   orbx_match_resolve  the reference's ordered loop (ORBmatcher.cpp:36-141) from the complete table
+ *                       rows[n_queries][8] gathered from the ranks; results are identical to
+ *                       orbx_search_for_initialization(F1, F2, ...). */
+int orbx_match_rows(orbx_ctx* ctx, const orbx_frame* F1, const orbx_frame* F2, int window_size, int q0, int q1,
+                    uint32_t* rows_out, int* n_queries);
+int orbx_match_resolve(orbx_ctx* ctx, const orbx_frame* F1, const orbx_frame* F2, float nnratio, int check_orientation,
+                       int window_size, const uint32_t* rows, int n_queries, int* matches12, int* nmatches,
+                       int counters[3]);
+/* Raw all-pairs 256-bit Hamming (FORB::distance over a matrix): for each of n_a descriptors the nearest of n_b
+ * (first minimum in index order), its distance and the second smallest distance (-1 if n_b == 1).  Output
+ * pointers may be NULL.  kernel_ms (may be NULL): device time of one pass, averaged over `repeats` passes. */
+int orbx_hamming_best2(orbx_ctx* ctx, const uint8_t* a, int n_a, const uint8_t* b, int n_b, int* best_idx, int* best_dist,
+                       int* second_dist, int repeats, float* kernel_ms);
+
 /* ---- Frame glue ---------------------------------------------------------------------------- */
 /* K4 = fx, fy, cx, cy; dist4 = k1, k2, p1, p2 (float32, as the reference's CV_32F matrices).
  * bounds = mnMinX, mnMaxX, mnMinY, mnMaxY or NULL to compute them as ComputeImageBounds does

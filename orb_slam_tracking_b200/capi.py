@@ -53,6 +53,9 @@ SIGNATURES = {
     "orbx_frame_glue": (ci, [vp, vp, ci, vp, vp, vp]),
     "orbx_features_in_area": (ci, [vp, vp, cf, cf, cf, ci, ci, vp, ci]),
     "orbx_search_for_initialization": (ci, [vp, vp, vp, cf, ci, ci, vp, vp, vp]),
+    "orbx_match_rows": (ci, [vp, vp, vp, ci, ci, ci, vp, vp]),
+    "orbx_match_resolve": (ci, [vp, vp, vp, cf, ci, ci, vp, ci, vp, vp, vp]),
+    "orbx_hamming_best2": (ci, [vp, vp, ci, vp, ci, vp, vp, vp, ci, vp]),
     "orbx_descriptor_distance": (ci, [vp, vp]),
     "orbx_descriptor_distance_batch": (ci, [vp, vp, vp, ci, vp]),
     "orbx_check_homography": (ci, [vp, vp, ci, vp, ci, vp, vp, vp, ci, cf, vp, vp, vp, vp]),

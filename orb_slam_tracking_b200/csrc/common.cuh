@@ -144,6 +144,7 @@ struct Params {
   int optLanes;          // compute lanes of the chunked host path (0 = default)
   int optResizeRows;     // rows per warp of k_resize (0 = default)
   int optMatchSerial;    // test hook: force the one-warp-per-pair matcher
+  int optMatchPath;      // 0 = choose by window and capacity, 1 = k_match_cta, 2 = k_match, 3 = brute force (match_bf.cu)
   int optFastTileBudget; // bytes of one staged k_fast tile (creation time only)
 };
 
@@ -169,6 +170,14 @@ int launch_fast(const Params& P, const TmaMaps& M, int nSlots, cudaStream_t st);
 int launch_quadtree(const Params& P, int nSlots, cudaStream_t st);
 int launch_describe(const Params& P, int nSlots, int lap0, int lap1, cudaStream_t st);
 int launch_glue(const Params& P, int nSlots, cudaStream_t st);
+// scratch of the brute-force matcher (match_bf.cu), per pair; topk == nullptr: not available
+struct BfScratch {
+  u32* cand;        // [pair][stride]  level-0 keys of F2 in visiting order: index | cell ix << 16 | cell iy << 22
+  float2* candXY;   // [pair][stride]  their undistorted positions
+  int* qIdx;        // [pair][stride]  level-0 keys of F1, ascending
+  int* counts;      // [pair][4]       number of candidates, number of queries
+  u32* topk;        // [pair][stride][8]  per query: 7 keys (distance << 20 | visiting position), info word
+};
 struct MatchArgs {
   const orbx_keypoint* keysUn;  // [slot][nfeatures]
   const u8* desc;
@@ -180,9 +189,18 @@ struct MatchArgs {
   int* nmatches;                // [pair]
   int* counters;                // [pair][3]
   int* scratch;                 // [pair][2*stride + ...]
+  BfScratch bf;                 // already advanced to the first pair of the launch
 };
 int launch_match(const Params& P, const MatchArgs& A, int nPairs, int pairStep, float nnratio, int checkOri,
                  int window, cudaStream_t st);
+int launch_match_bf(const Params& P, const MatchArgs& A, const BfScratch& B, int nPairs, int pairStep, float nnratio, int checkOri,
+                    int window, cudaStream_t st);
+int launch_bf_prep(const Params& P, const MatchArgs& A, const BfScratch& B, int nPairs, int pairStep, cudaStream_t st);
+int launch_bf_rows(const Params& P, const MatchArgs& A, const BfScratch& B, int nPairs, int pairStep, int window, int q0, int q1,
+                   cudaStream_t st);
+int launch_bf_resolve(const Params& P, const MatchArgs& A, const BfScratch& B, int nPairs, int pairStep, float nnratio, int checkOri,
+                      int window, cudaStream_t st);
+int launch_hamming_topk(const u8* a, int nA, const u8* b, int nB, u32* topk, cudaStream_t st);
 
 // Initializer::CheckHomography / CheckFundamental over hypothesis sets (score.cu)
 struct ScoreArgs {

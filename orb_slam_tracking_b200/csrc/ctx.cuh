@@ -56,6 +56,8 @@ struct orbx_ctx {
   int* dNMatches;
   int* dCounters;
   int* dMatchScratch;
+  orbx::BfScratch dBf;      // brute-force matcher scratch of the stream path ([pair] arrays)
+  orbx::BfScratch hfBf;     // the same for host-frame calls (one pair)
   // staging store for host-frame calls (2 frames): keysUn, desc, gridOff, gridIdx, n
   orbx_keypoint* hfKeys;
   orbx::u8* hfDesc;

@@ -13,20 +13,13 @@
 // Descriptors are read as two 128-bit loads and compared with 8 x __popc.
 #include <limits.h>
 
+#include <algorithm>
+
 #include <cstdlib>
 
-#include "common.cuh"
+#include "match_common.cuh"
 
 namespace orbx {
-
-constexpr int TH_LOW = 50, HISTO_LENGTH = 30;
-
-__device__ __forceinline__ int hamming256(const uint4 a0, const uint4 a1, const u8* __restrict__ d) {
-  const uint4 b0 = __ldg(reinterpret_cast<const uint4*>(d));
-  const uint4 b1 = __ldg(reinterpret_cast<const uint4*>(d) + 1);
-  return __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
-         __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
-}
 
 // One warp per pair.  Per query: the <= 64 grid columns of the search window are spread over the
 // lanes (their CSR ranges are loaded in parallel and prefix-summed), then the flattened candidate
@@ -223,21 +216,6 @@ __host__ __device__ inline MatchSmem match_smem_layout(int stride) {
   L.ent = take(L.entCap * 4);
   L.total = o;
   return L;
-}
-
-// the window's cell rectangle, Frame::GetFeaturesInArea :167-185; false = empty result
-__device__ __forceinline__ bool cell_rect(const Params& P, float x, float y, float r, int& minCX, int& maxCX, int& minCY,
-                                          int& maxCY) {
-  const float minX = (float)P.bounds[0], minY = (float)P.bounds[2];
-  minCX = max(0, (int)floorf(__fmul_rn(x - minX - r, P.gridWInv)));
-  if (minCX >= kGridCols) return false;
-  maxCX = min(kGridCols - 1, (int)ceilf(__fmul_rn(x - minX + r, P.gridWInv)));
-  if (maxCX < 0) return false;
-  minCY = max(0, (int)floorf(__fmul_rn(y - minY - r, P.gridHInv)));
-  if (minCY >= kGridRows) return false;
-  maxCY = min(kGridRows - 1, (int)ceilf(__fmul_rn(y - minY + r, P.gridHInv)));
-  if (maxCY < 0) return false;
-  return maxCX >= minCX && maxCY >= minCY;
 }
 
 __global__ void __launch_bounds__(MT) k_match_cta(const __grid_constant__ Params P, const MatchArgs A, int pairStep, float nnratio,
@@ -516,11 +494,27 @@ __global__ void __launch_bounds__(MT) k_match_cta(const __grid_constant__ Params
   }
 }
 
+// Which matcher runs (same results, bit for bit; P.optMatchPath forces one for the tests):
+//   1  k_match_cta   windows with a few dozen candidates per query (the demo's 100 px): all candidates of a chunk of queries
+//                    in shared memory;
+//   3  brute force   (match_bf.cu) windows that cover most of the image, or keypoint capacities beyond k_match_cta's
+//                    shared memory: distance matrix sharded by query rows over all SMs, ordered resolve from top-k lists;
+//   2  k_match       one warp per pair, the plain ordered walk (needs no scratch).
 int launch_match(const Params& P, const MatchArgs& A, int nPairs, int pairStep, float nnratio, int checkOri,
                  int window, cudaStream_t st) {
   if (nPairs <= 0) return 0;
   const MatchSmem LY = match_smem_layout(A.stride);
-  if (!P.optMatchSerial && A.stride < 65535 && LY.total <= 200 * 1024) {
+  const bool ctaFits = A.stride < 65535 && LY.total <= 200 * 1024;
+  const bool bfFits = A.bf.topk != nullptr && A.stride < 45000;
+  // expected candidates per query: the level-0 keys (about a fifth of the capacity at scale 1.2) in a (2 window)^2 box
+  const double frac = std::min(1.0, 4.0 * (double)window * window / ((double)std::max(1, P.bounds[1] - P.bounds[0]) * std::max(1, P.bounds[3] - P.bounds[2])));
+  const bool wide = 0.22 * A.stride * frac > 256.0;
+  int path = P.optMatchSerial ? 2 : P.optMatchPath;
+  if (path == 0) path = (bfFits && (wide || !ctaFits)) ? 3 : ctaFits ? 1 : 2;
+  if (path == 3 && !bfFits) path = ctaFits ? 1 : 2;
+  if (path == 1 && !ctaFits) path = 2;
+  if (path == 3) return launch_match_bf(P, A, A.bf, nPairs, pairStep, nnratio, checkOri, window, st);
+  if (path == 1) {
     if (cudaFuncSetAttribute(k_match_cta, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) != cudaSuccess) return 0;
     k_match_cta<<<nPairs, MT, LY.total, st>>>(P, A, pairStep, nnratio, checkOri, window);
   } else {

@@ -82,6 +82,7 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   P.optLanes = env_int("ORBX_LANES", 0);
   P.optResizeRows = env_int("ORBX_RESIZE_ROWS", 0);
   P.optMatchSerial = env_int("ORBX_MATCH_SERIAL", 0) != 0;
+  P.optMatchPath = env_int("ORBX_MATCH_PATH", 0);
   P.optFastTileBudget = std::max(4096, env_int("ORBX_FAST_TILE", 15360));
   std::memcpy(P.umax, c->T.umax, sizeof(P.umax));
   std::vector<StripDesc> strips;
@@ -165,6 +166,16 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   if ((rc = dalloc(c, &c->dNMatches, nPairs))) return rc;
   if ((rc = dalloc(c, &c->dCounters, nPairs * 3))) return rc;
   if ((rc = dalloc(c, &c->dMatchScratch, nPairs * 3 * P.kpStride))) return rc;
+  auto bf_alloc = [&](BfScratch& b, size_t np, size_t stride) {
+    int r;
+    if ((r = dalloc(c, &b.cand, np * stride))) return r;
+    if ((r = dalloc(c, &b.candXY, np * stride))) return r;
+    if ((r = dalloc(c, &b.qIdx, np * stride))) return r;
+    if ((r = dalloc(c, &b.counts, np * 4))) return r;
+    return dalloc(c, &b.topk, np * stride * 8);
+  };
+  if ((rc = bf_alloc(c->dBf, nPairs, (size_t)P.kpStride))) return rc;
+  if ((rc = bf_alloc(c->hfBf, 1, (size_t)P.kpStride))) return rc;
   // host-frame staging (2 frames)
   c->hfCap = P.kpStride;
   if ((rc = dalloc(c, &c->hfKeys, 2 * (size_t)c->hfCap))) return rc;
@@ -248,6 +259,7 @@ extern "C" int orbx_set_option(orbx_ctx* c, const char* name, int value) {
   else if (n == "lanes") c->P.optLanes = value;
   else if (n == "resize_rows") c->P.optResizeRows = value;
   else if (n == "match_serial") c->P.optMatchSerial = value != 0;
+  else if (n == "match_path") c->P.optMatchPath = value;
   else return ORBX_ERR_ARG;
   return ORBX_OK;
 }

@@ -100,6 +100,9 @@ int enqueue_glue_match(orbx_ctx* c, const Params& P, int n, int pair0, float nnr
   A.nmatches = c->dNMatches + pair0;
   A.counters = c->dCounters + (size_t)pair0 * 3;
   A.scratch = c->dMatchScratch + (size_t)pair0 * 3 * P.kpStride;
+  A.bf = c->dBf;
+  A.bf.cand += (size_t)pair0 * P.kpStride; A.bf.candXY += (size_t)pair0 * P.kpStride; A.bf.qIdx += (size_t)pair0 * P.kpStride;
+  A.bf.counts += (size_t)pair0 * 4; A.bf.topk += (size_t)pair0 * P.kpStride * 8;
   c->launches += launch_match(P, A, n / 2, 2, nnratio, checkOri, window, st);
   mark(c, 7);
   CU(c, cudaGetLastError());

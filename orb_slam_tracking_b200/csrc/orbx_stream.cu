@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <vector>
 
 #include "ctx.cuh"
 
@@ -136,6 +137,7 @@ extern "C" int orbx_search_for_initialization(orbx_ctx* c, const orbx_frame* F1,
   A.keysUn = c->hfKeys; A.desc = c->hfDesc; A.gridOff = c->hfGridOff; A.gridIdx = c->hfGridIdx; A.n = c->hfN;
   A.stride = c->hfCap; A.matches12 = c->hfMatches; A.nmatches = c->hfNMatches; A.counters = c->hfCounters;
   A.scratch = c->hfScratch;
+  A.bf = c->hfBf;
   c->launches = launch_match(c->P, A, 1, 2, nnratio, check_orientation, window_size, c->stream);
   CU(c, cudaGetLastError());
   int nm = 0, cnt[3] = {0, 0, 0};
@@ -147,6 +149,116 @@ extern "C" int orbx_search_for_initialization(orbx_ctx* c, const orbx_frame* F1,
   if (nmatches) *nmatches = nm;
   if (counters) std::memcpy(counters, cnt, sizeof(cnt));
   return ORBX_OK;
+}
+
+// ---- the distance matrix of one pair sharded by query rows (multi-GPU brute-force matching) ------------------------
+static MatchArgs host_pair_args(orbx_ctx* c) {
+  MatchArgs A;
+  A.keysUn = c->hfKeys; A.desc = c->hfDesc; A.gridOff = c->hfGridOff; A.gridIdx = c->hfGridIdx; A.n = c->hfN;
+  A.stride = c->hfCap; A.matches12 = c->hfMatches; A.nmatches = c->hfNMatches; A.counters = c->hfCounters;
+  A.scratch = c->hfScratch;
+  A.bf = c->hfBf;
+  return A;
+}
+
+extern "C" int orbx_match_rows(orbx_ctx* c, const orbx_frame* F1, const orbx_frame* F2, int window_size, int q0, int q1,
+                               uint32_t* rows_out, int* n_queries) {
+  if (!c || !F1 || !F2 || q0 < 0 || q1 < q0) return ORBX_ERR_ARG;
+  if (!c->cameraSet) return ORBX_ERR_STATE;
+  if (c->hfCap >= 45000) return ORBX_ERR_CAPACITY;
+  CU(c, cudaSetDevice(c->device));
+  int rc = stage_frame(c, F1, 0);
+  if (rc) return rc;
+  if ((rc = stage_frame(c, F2, 1))) return rc;
+  const MatchArgs A = host_pair_args(c);
+  c->launches = launch_bf_prep(c->P, A, A.bf, 1, 2, c->stream);
+  int cnt[4] = {0, 0, 0, 0};
+  CU(c, cudaMemcpyAsync(cnt, A.bf.counts, sizeof(cnt), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  if (n_queries) *n_queries = cnt[1];
+  q1 = std::min(q1, cnt[1]);
+  if (q1 > q0) {
+    c->launches += launch_bf_rows(c->P, A, A.bf, 1, 2, window_size, q0, q1, c->stream);
+    CU(c, cudaGetLastError());
+    if (rows_out)
+      CU(c, cudaMemcpyAsync(rows_out, A.bf.topk + (size_t)q0 * 8, (size_t)(q1 - q0) * 8 * sizeof(u32), cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+  }
+  return std::max(0, q1 - q0);
+}
+
+extern "C" int orbx_match_resolve(orbx_ctx* c, const orbx_frame* F1, const orbx_frame* F2, float nnratio, int check_orientation,
+                                  int window_size, const uint32_t* rows, int n_queries, int* matches12, int* nmatches,
+                                  int counters[3]) {
+  if (!c || !F1 || !F2 || n_queries < 0 || (n_queries > 0 && !rows)) return ORBX_ERR_ARG;
+  if (!c->cameraSet) return ORBX_ERR_STATE;
+  if (c->hfCap >= 45000 || n_queries > c->hfCap) return ORBX_ERR_CAPACITY;
+  CU(c, cudaSetDevice(c->device));
+  int rc = stage_frame(c, F1, 0);
+  if (rc) return rc;
+  if ((rc = stage_frame(c, F2, 1))) return rc;
+  const MatchArgs A = host_pair_args(c);
+  c->launches = launch_bf_prep(c->P, A, A.bf, 1, 2, c->stream);
+  if (n_queries) CU(c, cudaMemcpyAsync(A.bf.topk, rows, (size_t)n_queries * 8 * sizeof(u32), cudaMemcpyHostToDevice, c->stream));
+  int cnt[4] = {0, 0, 0, 0};
+  CU(c, cudaMemcpyAsync(cnt, A.bf.counts, sizeof(cnt), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  if (cnt[1] != n_queries) return ORBX_ERR_ARG;  // the row table does not belong to this pair
+  c->launches += launch_bf_resolve(c->P, A, A.bf, 1, 2, nnratio, check_orientation, window_size, c->stream);
+  CU(c, cudaGetLastError());
+  int nm = 0, cn[3] = {0, 0, 0};
+  if (matches12 && F1->n)
+    CU(c, cudaMemcpyAsync(matches12, c->hfMatches, (size_t)F1->n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaMemcpyAsync(&nm, c->hfNMatches, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaMemcpyAsync(cn, c->hfCounters, 3 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  if (nmatches) *nmatches = nm;
+  if (counters) std::memcpy(counters, cn, sizeof(cn));
+  return ORBX_OK;
+}
+
+// Raw all-pairs Hamming best / second best (micro-benchmark of the brute-force configuration; DescriptorDistance over a matrix)
+extern "C" int orbx_hamming_best2(orbx_ctx* c, const uint8_t* a, int n_a, const uint8_t* b, int n_b, int* best_idx, int* best_dist,
+                                  int* second_dist, int repeats, float* kernel_ms) {
+  if (!c || n_a < 1 || n_b < 1 || n_b >= (1 << 20) || !a || !b) return ORBX_ERR_ARG;
+  CU(c, cudaSetDevice(c->device));
+  u8 *da = nullptr, *db = nullptr;
+  u32* dt = nullptr;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  int rc = ORBX_OK;
+  std::vector<u32> rows((size_t)n_a * 8);
+  auto fail = [&](cudaError_t e) { if (e != cudaSuccess && rc == ORBX_OK) { c->err = cudaGetErrorString(e); rc = ORBX_ERR_CUDA; } };
+  fail(cudaMalloc(&da, (size_t)n_a * 32));
+  fail(cudaMalloc(&db, (size_t)n_b * 32));
+  fail(cudaMalloc(&dt, (size_t)n_a * 8 * sizeof(u32)));
+  fail(cudaEventCreate(&e0));
+  fail(cudaEventCreate(&e1));
+  if (rc == ORBX_OK) {
+    fail(cudaMemcpyAsync(da, a, (size_t)n_a * 32, cudaMemcpyHostToDevice, c->stream));
+    fail(cudaMemcpyAsync(db, b, (size_t)n_b * 32, cudaMemcpyHostToDevice, c->stream));
+    launch_hamming_topk(da, n_a, db, n_b, dt, c->stream);  // warm-up
+    fail(cudaEventRecord(e0, c->stream));
+    const int reps = std::max(1, repeats);
+    for (int i = 0; i < reps; ++i) launch_hamming_topk(da, n_a, db, n_b, dt, c->stream);
+    fail(cudaEventRecord(e1, c->stream));
+    fail(cudaMemcpyAsync(rows.data(), dt, rows.size() * sizeof(u32), cudaMemcpyDeviceToHost, c->stream));
+    fail(cudaStreamSynchronize(c->stream));
+    c->launches = reps + 1;
+    float ms = 0.f;
+    if (rc == ORBX_OK) fail(cudaEventElapsedTime(&ms, e0, e1));
+    if (kernel_ms) *kernel_ms = ms / reps;
+  }
+  if (rc == ORBX_OK)
+    for (int q = 0; q < n_a; ++q) {
+      const u32 k0 = rows[(size_t)q * 8], k1 = rows[(size_t)q * 8 + 1];
+      if (best_idx) best_idx[q] = (int)(k0 & 0xfffffu);
+      if (best_dist) best_dist[q] = (int)(k0 >> 20);
+      if (second_dist) second_dist[q] = k1 == 0xffffffffu ? -1 : (int)(k1 >> 20);
+    }
+  if (e0) cudaEventDestroy(e0);
+  if (e1) cudaEventDestroy(e1);
+  cudaFree(da); cudaFree(db); cudaFree(dt);
+  return rc;
 }
 
 extern "C" int orbx_descriptor_distance_batch(orbx_ctx* c, const uint8_t* a, const uint8_t* b, int n, int* out) {

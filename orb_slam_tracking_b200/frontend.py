@@ -53,6 +53,20 @@ class ORBextractor:
     def set_trig_mode(self, mode):
         check(lib().orbx_set_trig_mode(self._h, mode), self._h)
 
+    def set_option(self, name, value):
+        """Schedule options (orbx_set_option): they never change results."""
+        check(lib().orbx_set_option(self._h, name.encode(), int(value)), self._h)
+
+    def hamming_best2(self, a, b, repeats=1):
+        """Raw all-pairs Hamming: -> (best_idx[nA], best_dist[nA], second_dist[nA], kernel_ms)."""
+        a = np.ascontiguousarray(a, np.uint8).reshape(-1, 32)
+        b = np.ascontiguousarray(b, np.uint8).reshape(-1, 32)
+        bi, bd, sd = (np.zeros(len(a), np.int32) for _ in range(3))
+        ms = C.c_float(0)
+        check(lib().orbx_hamming_best2(self._h, ptr(a), len(a), ptr(b), len(b), ptr(bi), ptr(bd), ptr(sd), repeats,
+                                       C.addressof(ms)), self._h)
+        return bi, bd, sd, ms.value
+
     def __call__(self, image, mask=None, vLappingArea=(0, 0)):
         """-> (keypoints[KP_DTYPE], descriptors[n,32], monoIndex).  `mask` is ignored as in the
         reference (Features/ORBextractor.cpp:1537)."""
@@ -178,6 +192,26 @@ class ORBmatcher:
         check(lib().orbx_search_for_initialization(F1.ex._h, C.addressof(f1), C.addressof(f2), self.mfNNratio,
                                                    int(self.mbCheckOrientation), windowSize, ptr(m12),
                                                    C.addressof(nm), ptr(cnt)), F1.ex._h)
+        return nm.value, m12[:F1.N].copy(), cnt
+
+    def match_rows(self, F1, F2, windowSize, q0, q1):
+        """Rows [q0, q1) of the pair's distance matrix as top lists -> (rows[n, 8] uint32, number of level-0 queries)."""
+        f1, f2 = F1._pod(), F2._pod()
+        rows = np.zeros((max(q1 - q0, 1), 8), np.uint32)
+        nq = C.c_int(0)
+        n = check(lib().orbx_match_rows(F1.ex._h, C.addressof(f1), C.addressof(f2), windowSize, q0, q1, ptr(rows),
+                                        C.addressof(nq)), F1.ex._h)
+        return rows[:n].copy(), nq.value
+
+    def match_resolve(self, F1, F2, rows, windowSize=100):
+        """The ordered resolve from a complete row table -> (nmatches, vnMatches12, counters[3])."""
+        rows = np.ascontiguousarray(rows, np.uint32).reshape(-1, 8)
+        m12 = np.full(max(F1.N, 1), -1, np.int32)
+        nm = C.c_int(0)
+        cnt = np.zeros(3, np.int32)
+        f1, f2 = F1._pod(), F2._pod()
+        check(lib().orbx_match_resolve(F1.ex._h, C.addressof(f1), C.addressof(f2), self.mfNNratio, int(self.mbCheckOrientation),
+                                       windowSize, ptr(rows), len(rows), ptr(m12), C.addressof(nm), ptr(cnt)), F1.ex._h)
         return nm.value, m12[:F1.N].copy(), cnt
 
     @staticmethod

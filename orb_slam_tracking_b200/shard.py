@@ -12,6 +12,13 @@ def shard_pairs(n_pairs, world, rank):
     return lo, lo + base + (1 if rank < extra else 0)
 
 
+def shard_rows(n_queries, world, rank):
+    """Query-row block [q0, q1) of ONE pair's Hamming matrix for `rank` (brute-force matching of BASELINE.json configs[4]:
+    F2's descriptors go to every rank by H2D copy, each rank computes the top lists of its rows with orbx_match_rows, the
+    row tables are gathered on the host and one rank runs orbx_match_resolve; no collective on the data path)."""
+    return shard_pairs(n_queries, world, rank)
+
+
 def shard_frames(n_pairs, world, rank):
     """Frame index range [2*lo, 2*hi) of the pairs of `rank` (pair k = frames 2k, 2k+1)."""
     lo, hi = shard_pairs(n_pairs, world, rank)
