@@ -356,6 +356,40 @@ def run_ours(args, wl):
             dt = time.perf_counter() - t0
             scoring["cpu"] = {"hypothesis_match_evals_per_s": ev / dt, "cores": 1, "kind": "reference" if use_ref else "port",
                               "sample": "%d pairs x %d hypotheses x 2 models" % (min(nP, 8), nh)}
+    # single-frame latency through the reference's own call shape ("report both single-frame latency and
+    # batched throughput"): one Frame::Frame per image (orbx_frame_construct: host image in, keypoints / descriptors /
+    # undistorted keys / grid out, ONE CUDA graph launch and ONE synchronisation) and one SearchForInitialization per pair
+    # (host frames in, matches out), wall clock per call, outside every timed region above
+    latency = None
+    if rank == 0:
+        import time
+        fr = synth.frames(8, W, H, first_pair=pair_lo)
+        Fs = [fe.Frame(E, im, fused=True) for im in fr]        # warm-up: builds the graph
+        tf, tm = [], []
+        M = fe.ORBmatcher(NNRATIO, True)
+        for it in range(60):
+            im = fr[it % 8]
+            t0 = time.perf_counter()
+            F = fe.Frame(E, im, fused=True)
+            t1 = time.perf_counter()
+            M.SearchForInitialization(Fs[(it % 8) & ~1], F, WINDOW)
+            t2 = time.perf_counter()
+            if it >= 10:
+                tf.append((t1 - t0) * 1e6)
+                tm.append((t2 - t1) * 1e6)
+        latency = {"frame_us": {"p50": round(float(np.percentile(tf, 50)), 1), "p99": round(float(np.percentile(tf, 99)), 1)},
+                   "pair_match_us": {"p50": round(float(np.percentile(tm, 50)), 1), "p99": round(float(np.percentile(tm, 99)), 1)},
+                   "api": "orbx_frame_construct (CUDA graph per context) / orbx_search_for_initialization, host buffers, "
+                          "ctypes call overhead included", "samples": len(tf)}
+        if world == 1 and not args.no_cpu:
+            impl, kind = cpu_impl()
+            a1 = (wl["nfeatures"], 1.2, 8, wl["ini"], wl["mn"], K4, D4, WINDOW, NNRATIO, 1)
+            impl.run_stream(fr[:2], *a1)
+            t0 = time.perf_counter()
+            for _ in range(5):
+                impl.run_stream(fr[:2], *a1)
+            latency["cpu_reference_pair_us"] = {"value": round((time.perf_counter() - t0) / 5 * 1e6, 1), "kind": kind, "cores": 1,
+                                                "what": "2 x Frame::Frame + SearchForInitialization on one host core"}
     # raw all-pairs Hamming best / second best, 8000 x 8000 descriptors (the matcher's distance matrix at
     # BASELINE.json configs[4] without geometry), outside every timed region above
     brute = None
@@ -408,6 +442,7 @@ def run_ours(args, wl):
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "launches_per_step": n_launch_dom,
                          "ms_per_step": dom_ms, "algorithmic_bytes_per_step": int(ab[dom] * B)},
         }
+        line["latency"] = latency
         line["next_rows"] = {"init_scoring": scoring, "brute_force_hamming": brute}
         if world == 1 and not args.no_cpu:
             threads = host_threads()

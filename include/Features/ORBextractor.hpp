@@ -5,8 +5,11 @@
 // The reference binds an extractor to no image size; this one creates its device context lazily
 // for the first image's size (and again if the size changes).
 #pragma once
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
+#include <iostream>
 #include <list>
 #include <vector>
 
@@ -29,13 +32,30 @@ inline void releaseOut(cv::OutputArray o) { o.release(); }
 #endif
 }  // namespace orbx_detail
 
-// Declaration kept for source compatibility (reference Features/ORBextractor.hpp:32-53); the
-// quadtree itself runs on the device (csrc/quadtree.cu).
+// Public type of the reference (Features/ORBextractor.hpp:32-53), kept for source compatibility with the same members.
+// The extractor's own quadtree runs on the device (csrc/quadtree.cu) and does not use it.
 class ExtractorNode {
  public:
   ExtractorNode() : bNoMore(false) {}
+
+  // Features/ORBextractor.cpp:617-676: four children at ceil(w / 2), ceil(h / 2); a key goes left / top when its
+  // coordinate is below the split line; a child with exactly one key is final.
+  void DivideNode(ExtractorNode& n1, ExtractorNode& n2, ExtractorNode& n3, ExtractorNode& n4) {
+    const int hx = (int)std::ceil(static_cast<float>(UR.x - UL.x) / 2), hy = (int)std::ceil(static_cast<float>(BR.y - UL.y) / 2);
+    const cv::Point2i mid(UL.x + hx, UL.y + hy);
+    n1.UL = UL;                         n1.UR = cv::Point2i(mid.x, UL.y); n1.BL = cv::Point2i(UL.x, mid.y);  n1.BR = mid;
+    n2.UL = n1.UR;                      n2.UR = UR;                       n2.BL = mid;                       n2.BR = cv::Point2i(UR.x, mid.y);
+    n3.UL = n1.BL;                      n3.UR = mid;                      n3.BL = BL;                        n3.BR = cv::Point2i(mid.x, BL.y);
+    n4.UL = mid;                        n4.UR = n2.BR;                    n4.BL = n3.BR;                     n4.BR = BR;
+    ExtractorNode* child[4] = {&n1, &n2, &n3, &n4};
+    for (ExtractorNode* c : child) c->vKeys.reserve(vKeys.size());
+    for (const cv::KeyPoint& kp : vKeys) child[(kp.pt.x < mid.x ? 0 : 1) + (kp.pt.y < mid.y ? 0 : 2)]->vKeys.push_back(kp);
+    for (ExtractorNode* c : child)
+      if (c->vKeys.size() == 1) c->bNoMore = true;
+  }
+
   std::vector<cv::KeyPoint> vKeys;
-  cv::Point2f UL, UR, BL, BR;
+  cv::Point2i UL, UR, BL, BR;
   std::list<ExtractorNode>::iterator lit;
   bool bNoMore;
 };
@@ -60,7 +80,7 @@ class ORBextractor {
     }
     int sum = 0;
     for (int v : mnFeaturesPerLevel) sum += v;
-    std::printf("Sum of features: %d\n", sum);  // :549
+    std::cout << "Sum of features = " << sum << std::endl;  // the reference's line, :549
   }
   ~ORBextractor() { orbx_destroy(ctx_); }
   ORBextractor(const ORBextractor&) = delete;
@@ -71,7 +91,10 @@ class ORBextractor {
                  cv::OutputArray _descriptors, std::vector<int>& vLappingArea) {
     cv::Mat image = orbx_detail::toMat(_image);
     if (image.empty()) return -1;  // :1536
-    if (image.type() != CV_8UC1) { std::fprintf(stderr, "ORBextractor: image must be CV_8UC1\n"); std::abort(); }  // assert, :1541
+    if (image.type() != CV_8UC1) {  // the reference asserts, :1541
+      std::fprintf(stderr, "ORBextractor::operator(): assertion `image.type() == CV_8UC1' failed (Features/ORBextractor.cpp:1541)\n");
+      std::abort();
+    }
     if (!ensure(image.cols, image.rows)) return -1;
     const int cap = capacity();
     _keypoints.resize(cap);
@@ -83,6 +106,7 @@ class ORBextractor {
     if (rc != ORBX_OK) { std::fprintf(stderr, "orbx_extract: %d %s\n", rc, orbx_last_error(ctx_)); _keypoints.clear(); return -1; }
     _keypoints.resize(n);
     pyramidStale_ = true;
+    if (fillPyramid_) FetchImagePyramid();
     if (n == 0) { orbx_detail::releaseOut(_descriptors); return 0; }  // :1567-1570 (mono index of an empty result)
     orbx_detail::createOut(_descriptors, n, 32, CV_8U);
     cv::Mat d = orbx_detail::outMat(_descriptors);
@@ -103,8 +127,11 @@ class ORBextractor {
   std::vector<float> inline GetInverseScaleSigmaSquares() { return mvInvLevelSigma2; }
   std::vector<int> inline GetNumFeaturesPerLevel() { return mnFeaturesPerLevel; }
 
-  // Public member of the reference (hpp:111).  Filled on request from the device copy.
+  // Public member of the reference (hpp:111): the levels of the last image (unpadded views, as the reference's ROIs).
+  // Filled after every operator() like in the reference; a caller that never reads it can switch the device -> host
+  // copy off (SetFillImagePyramid(false)) and fetch on demand with FetchImagePyramid().
   std::vector<cv::Mat> mvImagePyramid;
+  void SetFillImagePyramid(bool on) { fillPyramid_ = on; }
   const std::vector<cv::Mat>& FetchImagePyramid() {
     if (ctx_ && pyramidStale_) {
       mvImagePyramid.resize(nlevels);
@@ -119,6 +146,11 @@ class ORBextractor {
     return mvImagePyramid;
   }
 
+  // Frame::Frame extracts through orbx_frame_construct on this extractor's context: same bookkeeping as operator()
+  void NotifyExtracted() {
+    pyramidStale_ = true;
+    if (fillPyramid_) FetchImagePyramid();
+  }
   orbx_ctx* context(int width, int height) { return ensure(width, height) ? ctx_ : nullptr; }
   orbx_ctx* context() { return ctx_; }
   int capacity() const {
@@ -146,7 +178,7 @@ class ORBextractor {
   int device_, maxBatch_;
   orbx_ctx* ctx_;
   int w_, h_;
-  bool pyramidStale_ = false;
+  bool pyramidStale_ = false, fillPyramid_ = true;
 };
 
 }  // namespace ORB_SLAM_Tracking

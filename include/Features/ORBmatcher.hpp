@@ -3,6 +3,7 @@
 // north_star's DescriptorDistance (== DBoW2::FORB::distance, Thirdparty/DBoW2/src/FORB.cpp:77-100).
 #pragma once
 #include <cstdio>
+#include <iostream>
 #include <vector>
 
 #include "../SlamTypes/Frame.hpp"
@@ -21,8 +22,11 @@ class ORBmatcher {
     const int rc = orbx_search_for_initialization(F1.mpORBextractor->context(), &f1, &f2, mfNNratio, mbCheckOrientation ? 1 : 0,
                                                   windowSize, vnMatches12.data(), &nmatches, cnt);
     if (rc != ORBX_OK) { std::fprintf(stderr, "orbx_search_for_initialization: %d\n", rc); return 0; }
-    // the three counters the reference prints (ORBmatcher.cpp:144-147)
-    std::printf("bad dist: %d bad ratio: %d bad orientation: %d\n", cnt[0], cnt[1], cnt[2]);
+    // the reference's statistics lines, ORBmatcher.cpp:144-147
+    std::cout << "SearchForInitialization done ----------------------" << std::endl;
+    std::cout << "invalidMatchByDistance: " << cnt[0] << std::endl;
+    std::cout << "invalidMatchByRatio: " << cnt[1] << std::endl;
+    std::cout << "invalidMatchByOrientation: " << cnt[2] << std::endl;
     return nmatches;
   }
 

@@ -30,6 +30,13 @@ struct Point2f {
   Point2f(float x_, float y_) : x(x_), y(y_) {}
 };
 
+struct Point2i {
+  int x, y;
+  Point2i() : x(0), y(0) {}
+  Point2i(int x_, int y_) : x(x_), y(y_) {}
+};
+typedef Point2i Point;
+
 struct KeyPoint {
   Point2f pt;
   float size, angle, response;

@@ -80,7 +80,8 @@ const char* orbx_last_error(const orbx_ctx* ctx); /* never NULL */
 int orbx_set_trig_mode(orbx_ctx* ctx, int mode);
 /* Schedule options of a context (they never change results).  The environment is read ONCE, in orbx_create
  * (ORBX_SINGLE_STREAM, ORBX_RUN_PARTS, ORBX_LANES, ORBX_RESIZE_ROWS, ORBX_MATCH_SERIAL, ORBX_FAST_TILE); this call
- * changes an option of a live context: name = "single_stream" | "run_parts" | "lanes" | "resize_rows" | "match_serial".
+ * changes an option of a live context: name = "single_stream" | "run_parts" | "lanes" | "resize_rows" | "match_serial" |
+ * "match_path" (0 auto, 1 k_match_cta, 2 k_match, 3 brute force) | "frame_graph" (1: single-frame calls use a CUDA graph).
  * No launch path reads the environment.  Returns ORBX_ERR_ARG for an unknown name. */
 int orbx_set_option(orbx_ctx* ctx, const char* name, int value);
 
@@ -100,6 +101,13 @@ int orbx_compute_level_tables(int nfeatures, float scale_factor, int nlevels, fl
  * *mono_index = the reference's return value (may be NULL). */
 int orbx_extract(orbx_ctx* ctx, const uint8_t* img, size_t step, const int lapping[2], orbx_keypoint* kps,
                  uint8_t* desc, int cap, int* n_out, int* mono_index);
+/* Frame::Frame in one call (SlamTypes/Frame.cpp:57-77): extraction + UndistortKeyPoints + grid assignment of one frame
+ * through ONE CUDA graph launch and ONE synchronisation (the single-frame latency path; orbx_extract of one image runs
+ * through the same kind of graph).  Same results as orbx_extract followed by orbx_frame_glue.  kps_un / grid_offsets
+ * (ORBX_GRID_CELLS + 1) / grid_indices (cap) may be NULL.  Needs orbx_set_camera. */
+int orbx_frame_construct(orbx_ctx* ctx, const uint8_t* img, size_t step, const int lapping[2], orbx_keypoint* kps,
+                         uint8_t* desc, int cap, int* n_out, int* mono_index, orbx_keypoint* kps_un,
+                         uint32_t* grid_offsets, uint32_t* grid_indices);
 /* n_img <= max_batch images; outputs are n_img consecutive blocks of `cap` keypoints. */
 int orbx_extract_batch(orbx_ctx* ctx, const uint8_t* const* imgs, size_t step, int n_img, const int lapping[2],
                        orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out, int* mono_index);
@@ -114,6 +122,14 @@ int orbx_get_blurred_level(orbx_ctx* ctx, int slot, int level, uint8_t* dst, siz
 int orbx_get_candidates(orbx_ctx* ctx, int slot, int level, float* xyr, int cap);
 /* keypoints of one level after distribution + orientation (+ descriptors), level coordinates */
 int orbx_get_level_keypoints(orbx_ctx* ctx, int slot, int level, orbx_keypoint* kps, uint8_t* desc, int cap);
+
+/* ---- radius queries on device-resident frames ------------------------------ */
+/* Frame::GetFeaturesInArea (SlamTypes/Frame.cpp:163-206) for n_queries windows on the frames orbx_stream_run left on the
+ * device: query i = queries5[5 i .. 5 i + 4] = (x, y, r, minLevel, maxLevel) on frame slots[i].  out[i * cap ..] receives
+ * the keypoint indices in the reference's visiting order, counts[i] the result size (may exceed cap).  One launch, a
+ * warp per query; nothing is uploaded but the queries. */
+int orbx_stream_features_in_area(orbx_ctx* ctx, int n_queries, const int* slots, const float* queries5, int* out, int cap,
+                                 int* counts);
 
 /* ---- brute-force matching: the distance matrix of one pair sharded by query rows ---------- */
 /* SearchForInitialization(F1, F2) with a window that makes most of F2 a candidate of every query is a

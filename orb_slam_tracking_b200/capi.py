@@ -44,6 +44,7 @@ SIGNATURES = {
     "orbx_get_level_size": (ci, [vp, ci, vp, vp]),
     "orbx_compute_level_tables": (ci, [ci, cf, ci, vp, vp, vp, vp, vp, vp]),
     "orbx_extract": (ci, [vp, vp, sz, vp, vp, vp, ci, vp, vp]),
+    "orbx_frame_construct": (ci, [vp, vp, sz, vp, vp, vp, ci, vp, vp, vp, vp, vp]),
     "orbx_extract_batch": (ci, [vp, vp, sz, ci, vp, vp, vp, ci, vp, vp]),
     "orbx_get_pyramid_level": (ci, [vp, ci, ci, ci, vp, sz]),
     "orbx_get_blurred_level": (ci, [vp, ci, ci, vp, sz]),
@@ -53,6 +54,7 @@ SIGNATURES = {
     "orbx_frame_glue": (ci, [vp, vp, ci, vp, vp, vp]),
     "orbx_features_in_area": (ci, [vp, vp, cf, cf, cf, ci, ci, vp, ci]),
     "orbx_search_for_initialization": (ci, [vp, vp, vp, cf, ci, ci, vp, vp, vp]),
+    "orbx_stream_features_in_area": (ci, [vp, ci, vp, vp, vp, ci, vp]),
     "orbx_match_rows": (ci, [vp, vp, vp, ci, ci, ci, vp, vp]),
     "orbx_match_resolve": (ci, [vp, vp, vp, cf, ci, ci, vp, ci, vp, vp, vp]),
     "orbx_hamming_best2": (ci, [vp, vp, ci, vp, ci, vp, vp, vp, ci, vp]),

@@ -72,6 +72,16 @@ struct orbx_ctx {
   // Initializer scoring scratch (grown on demand): hypotheses, scores, best, list lengths, inlier flags
   orbx::u8* dScore;
   size_t scoreBytes;
+  // single-frame latency path: the whole launch sequence of one frame (H2D of the image from the pinned staging buffer,
+  // extraction, optionally the Frame glue, D2H of every result into the pinned result block) as ONE CUDA graph, built on
+  // first use and rebuilt when what it bakes in changes (lapping area, camera, trig mode, schedule options)
+  struct FrameGraph {
+    cudaGraphExec_t exec;
+    int lap0, lap1, withGlue, epoch;
+  } fg[2];                       // [0] extraction only (orbx_extract), [1] extraction + glue (orbx_frame_construct)
+  int graphEpoch;                // bumped by every setter a graph depends on
+  orbx::u8* hFrameIn;            // pinned [H][W]
+  orbx::u8* hFrameOut;           // pinned result block, see frame_out_layout()
   // timing
   cudaEvent_t evStart, evStop;
   int stageTiming;

@@ -574,6 +574,53 @@ __global__ void __launch_bounds__(32) k_features_in_area(const __grid_constant__
   }
   if (lane == 0) *count = n;
 }
+// The same query for a BATCH of windows on frames that live on the device (what the tracking stage after initialisation
+// asks for, tracking.cpp:44-47: radius searches around projected points with a level range): one warp per query,
+// results in the reference's visiting order.  q = (x, y, r, minLevel, maxLevel) per query, slot = frame of each query.
+__global__ void __launch_bounds__(256) k_features_in_area_batch(const __grid_constant__ Params P, const orbx_keypoint* __restrict__ keysUn,
+                                                                const u32* __restrict__ gridOff, const u32* __restrict__ gridIdx,
+                                                                int stride, const int* __restrict__ slots, const float* __restrict__ q5,
+                                                                int nQ, int* out, int cap, int* counts) {
+  const int w = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (w >= nQ) return;
+  const int slot = slots[w];
+  const float x = q5[5 * w], y = q5[5 * w + 1], r = q5[5 * w + 2];
+  const int minLevel = (int)q5[5 * w + 3], maxLevel = (int)q5[5 * w + 4];
+  const orbx_keypoint* __restrict__ kun = keysUn + (size_t)slot * stride;
+  const u32* __restrict__ gOff = gridOff + (size_t)slot * (kGridCells + 1);
+  const u32* __restrict__ gIdx = gridIdx + (size_t)slot * stride;
+  int* o = out + (size_t)w * cap;
+  int n = 0, minCX, maxCX, minCY, maxCY;
+  if (cell_rect(P, x, y, r, minCX, maxCX, minCY, maxCY)) {
+    const bool check = (minLevel > 0) || (maxLevel >= 0);  // Frame.cpp:187
+    for (int ix = minCX; ix <= maxCX; ++ix) {
+      const int beg = (int)gOff[ix * kGridRows + minCY], end = (int)gOff[ix * kGridRows + maxCY + 1];
+      for (int t0 = beg; t0 < end; t0 += 32) {
+        const int t = t0 + lane;
+        bool ok = false;
+        int i2 = -1;
+        if (t < end) {
+          i2 = (int)gIdx[t];
+          const orbx_keypoint k = kun[i2];
+          ok = !(check && !(k.octave >= minLevel && k.octave <= maxLevel));
+          ok = ok && fabsf(k.x - x) < r && fabsf(k.y - y) < r;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, ok);
+        if (ok) {
+          const int p = n + __popc(m & ((1u << lane) - 1));
+          if (p < cap) o[p] = i2;
+        }
+        n += __popc(m);
+      }
+    }
+  }
+  if (lane == 0) counts[w] = n;
+}
+void launch_features_in_area_batch(const Params& P, const orbx_keypoint* keysUn, const u32* gridOff, const u32* gridIdx, int stride,
+                                   const int* slots, const float* q5, int nQ, int* out, int cap, int* counts, cudaStream_t st) {
+  if (nQ > 0) k_features_in_area_batch<<<(nQ + 7) / 8, 256, 0, st>>>(P, keysUn, gridOff, gridIdx, stride, slots, q5, nQ, out, cap, counts);
+}
+
 void launch_features_in_area(const Params& P, const orbx_keypoint* kun, const u32* gOff, const u32* gIdx, float x,
                              float y, float r, int minLevel, int maxLevel, int* out, int cap, int* count,
                              cudaStream_t st) {

@@ -83,6 +83,7 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   P.optResizeRows = env_int("ORBX_RESIZE_ROWS", 0);
   P.optMatchSerial = env_int("ORBX_MATCH_SERIAL", 0) != 0;
   P.optMatchPath = env_int("ORBX_MATCH_PATH", 0);
+  P.optFrameGraph = env_int("ORBX_FRAME_GRAPH", 1) != 0;
   P.optFastTileBudget = std::max(4096, env_int("ORBX_FAST_TILE", 15360));
   std::memcpy(P.umax, c->T.umax, sizeof(P.umax));
   std::vector<StripDesc> strips;
@@ -207,6 +208,8 @@ extern "C" orbx_ctx* orbx_create(int device, int width, int height, int nfeature
   c->dIngest = nullptr; c->dIngestColor = nullptr; c->hStatus = nullptr; c->hTabPtrs = nullptr; c->launches = 0; c->cameraSet = 0; c->lastBatch = 0; c->dScore = nullptr; c->scoreBytes = 0;
   for (int i = 0; i < 2; ++i) { c->flight[i].active = 0; c->flight[i].n = 0; c->flight[i].chunk = 0; c->evDone[i] = nullptr; }
   c->nextTicket = 0;
+  for (int i = 0; i < 2; ++i) { c->fg[i].exec = nullptr; c->fg[i].epoch = -1; }
+  c->graphEpoch = 0; c->hFrameIn = nullptr; c->hFrameOut = nullptr;
   c->stageTiming = 0; c->evStart = c->evStop = nullptr;
   for (int i = 0; i < 10; ++i) c->evStage[i] = nullptr;
   std::memset(c->stageMs, 0, sizeof(c->stageMs));
@@ -230,6 +233,9 @@ extern "C" void orbx_destroy(orbx_ctx* c) {
   for (int i = 0; i < 10; ++i) if (c->evStage[i]) cudaEventDestroy(c->evStage[i]);
   for (cudaEvent_t e : c->evChunk) cudaEventDestroy(e);
   if (c->hStatus) cudaFreeHost(c->hStatus);
+  for (int i = 0; i < 2; ++i) if (c->fg[i].exec) cudaGraphExecDestroy(c->fg[i].exec);
+  if (c->hFrameIn) cudaFreeHost(c->hFrameIn);
+  if (c->hFrameOut) cudaFreeHost(c->hFrameOut);
   for (int i = 0; i < 2; ++i) if (c->evDone[i]) cudaEventDestroy(c->evDone[i]);
   for (int i = 0; i < orbx_ctx::kLanes; ++i) {
     if (c->sSide[i]) cudaStreamDestroy(c->sSide[i]);
@@ -249,6 +255,7 @@ extern "C" const char* orbx_last_error(const orbx_ctx* c) { return c ? c->err.c_
 extern "C" int orbx_set_trig_mode(orbx_ctx* c, int mode) {
   if (!c || (mode != 0 && mode != 1)) return ORBX_ERR_ARG;
   c->P.trigMode = mode;
+  ++c->graphEpoch;
   return ORBX_OK;
 }
 extern "C" int orbx_set_option(orbx_ctx* c, const char* name, int value) {
@@ -260,7 +267,9 @@ extern "C" int orbx_set_option(orbx_ctx* c, const char* name, int value) {
   else if (n == "resize_rows") c->P.optResizeRows = value;
   else if (n == "match_serial") c->P.optMatchSerial = value != 0;
   else if (n == "match_path") c->P.optMatchPath = value;
+  else if (n == "frame_graph") c->P.optFrameGraph = value != 0;
   else return ORBX_ERR_ARG;
+  ++c->graphEpoch;
   return ORBX_OK;
 }
 extern "C" void* orbx_get_stream(orbx_ctx* c) { return c ? (void*)c->stream : nullptr; }

@@ -119,7 +119,116 @@ int check_status(orbx_ctx* c, int n) {
   return worst;
 }
 
+// ---- single-frame latency path -------------------------------------------------------------------------------------
+// pinned result block of one frame: n | mono | status | pad | kps[cap] | desc[cap][32] | kps_un[cap] | gridOff[cells + 1] | gridIdx[cap]
+struct FrameOut { size_t kps, desc, kun, goff, gidx, total; };
+FrameOut frame_out_layout(int cap) {
+  FrameOut L;
+  size_t o = 16;
+  auto take = [&](size_t b) { const size_t r = o; o += (b + 15) & ~(size_t)15; return r; };
+  L.kps = take((size_t)cap * sizeof(orbx_keypoint));
+  L.desc = take((size_t)cap * 32);
+  L.kun = take((size_t)cap * sizeof(orbx_keypoint));
+  L.goff = take((kGridCells + 1) * sizeof(u32));
+  L.gidx = take((size_t)cap * sizeof(u32));
+  L.total = o;
+  return L;
+}
+
+// Builds (or reuses) the graph of one frame in slot 0.  The stream capture records exactly what the batched path would
+// enqueue, so the results are the same bit for bit.
+int frame_graph(orbx_ctx* c, int withGlue, int lap0, int lap1, cudaGraphExec_t* out) {
+  orbx_ctx::FrameGraph& G = c->fg[withGlue];
+  if (G.exec && G.epoch == c->graphEpoch && G.lap0 == lap0 && G.lap1 == lap1) { *out = G.exec; return ORBX_OK; }
+  const Params& P = c->P;
+  const FrameOut L = frame_out_layout(P.kpStride);
+  if (!c->hFrameIn) CU(c, cudaHostAlloc((void**)&c->hFrameIn, (size_t)P.W * P.H, cudaHostAllocDefault));
+  if (!c->hFrameOut) CU(c, cudaHostAlloc((void**)&c->hFrameOut, L.total, cudaHostAllocDefault));
+  if (G.exec) { cudaGraphExecDestroy(G.exec); G.exec = nullptr; }
+  cudaStream_t st = c->stream;
+  CU(c, cudaStreamSynchronize(st));
+  const int timing = c->stageTiming;
+  c->stageTiming = 0;  // no stage events inside a capture (and the fork to the side stream stays in)
+  CU(c, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+  int rc = ORBX_OK;
+  cudaError_t e = cudaMemcpy2DAsync(P.pyr + P.lv[0].imgOff, P.lv[0].pitch, c->hFrameIn, P.W, P.W, P.H, cudaMemcpyHostToDevice, st);
+  if (e == cudaSuccess) rc = enqueue_extract(c, P, 1, lap0, lap1, st);
+  u8* ho = c->hFrameOut;
+  const size_t cap = (size_t)P.kpStride;
+  if (e == cudaSuccess && rc == ORBX_OK && withGlue) {
+    c->launches += launch_glue(P, 1, st);
+    e = cudaMemcpyAsync(ho + L.kun, P.keysUn, cap * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(ho + L.goff, P.gridOff, (kGridCells + 1) * sizeof(u32), cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(ho + L.gidx, P.gridIdx, cap * sizeof(u32), cudaMemcpyDeviceToHost, st);
+  }
+  if (e == cudaSuccess) e = cudaMemcpyAsync(ho, P.outN, sizeof(int), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(ho + 4, P.outMono, sizeof(int), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(ho + 8, P.status, sizeof(int), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(ho + L.kps, P.outKp, cap * sizeof(orbx_keypoint), cudaMemcpyDeviceToHost, st);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(ho + L.desc, P.outDesc, cap * 32, cudaMemcpyDeviceToHost, st);
+  cudaGraph_t graph = nullptr;
+  const cudaError_t e2 = cudaStreamEndCapture(st, &graph);
+  c->stageTiming = timing;
+  if (e != cudaSuccess || e2 != cudaSuccess || rc != ORBX_OK || !graph) {
+    if (graph) cudaGraphDestroy(graph);
+    cudaGetLastError();
+    c->err = std::string("frame graph capture failed: ") + cudaGetErrorString(e != cudaSuccess ? e : e2);
+    return rc != ORBX_OK ? rc : ORBX_ERR_CUDA;
+  }
+  const cudaError_t e3 = cudaGraphInstantiate(&G.exec, graph, 0);
+  cudaGraphDestroy(graph);
+  if (e3 != cudaSuccess) { G.exec = nullptr; c->err = std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e3); return ORBX_ERR_CUDA; }
+  G.lap0 = lap0; G.lap1 = lap1; G.withGlue = withGlue; G.epoch = c->graphEpoch;
+  *out = G.exec;
+  return ORBX_OK;
+}
+
+// One frame through its graph: image -> pinned staging -> ONE graph launch -> ONE synchronisation -> results copied out
+int run_frame_graph(orbx_ctx* c, int withGlue, const uint8_t* img, size_t step, const int lapping[2], orbx_keypoint* kps, uint8_t* desc,
+                    int cap, int* n_out, int* mono_index, orbx_keypoint* kps_un, uint32_t* grid_offsets, uint32_t* grid_indices) {
+  const Params& P = c->P;
+  const int lap0 = lapping ? lapping[0] : 0, lap1 = lapping ? lapping[1] : 0;
+  int rc = drain_flights(c);
+  if (rc) return rc;
+  cudaGraphExec_t exec = nullptr;
+  if ((rc = frame_graph(c, withGlue, lap0, lap1, &exec))) return rc;
+  for (int y = 0; y < P.H; ++y) std::memcpy(c->hFrameIn + (size_t)y * P.W, img + (size_t)y * step, P.W);
+  const int launchesPerFrame = c->launches;  // counted during the capture of this graph (or of the other one: same sequence)
+  CU(c, cudaGraphLaunch(exec, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  (void)launchesPerFrame;
+  const FrameOut L = frame_out_layout(P.kpStride);
+  const u8* ho = c->hFrameOut;
+  int n, mono, status;
+  std::memcpy(&n, ho, 4); std::memcpy(&mono, ho + 4, 4); std::memcpy(&status, ho + 8, 4);
+  if (status) { c->err = "device-side status " + std::to_string(status); return status; }
+  if (n_out) *n_out = n;
+  if (mono_index) *mono_index = mono;
+  if (n > cap && (kps || desc || kps_un || grid_indices)) return ORBX_ERR_CAPACITY;
+  if (kps && n) std::memcpy(kps, ho + L.kps, (size_t)n * sizeof(orbx_keypoint));
+  if (desc && n) std::memcpy(desc, ho + L.desc, (size_t)n * 32);
+  if (withGlue) {
+    if (kps_un && n) std::memcpy(kps_un, ho + L.kun, (size_t)n * sizeof(orbx_keypoint));
+    if (grid_offsets) std::memcpy(grid_offsets, ho + L.goff, (kGridCells + 1) * sizeof(u32));
+    if (grid_indices && n) std::memcpy(grid_indices, ho + L.gidx, (size_t)n * sizeof(u32));
+  }
+  return ORBX_OK;
+}
+
 }  // namespace
+
+// Frame::Frame's work in one call (SlamTypes/Frame.cpp:57-77): extraction, undistortion and grid assignment of one frame
+// through one CUDA graph and one synchronisation.  Same results as orbx_extract followed by orbx_frame_glue.
+extern "C" int orbx_frame_construct(orbx_ctx* c, const uint8_t* img, size_t step, const int lapping[2], orbx_keypoint* kps,
+                                    uint8_t* desc, int cap, int* n_out, int* mono_index, orbx_keypoint* kps_un,
+                                    uint32_t* grid_offsets, uint32_t* grid_indices) {
+  if (!c) return ORBX_ERR_ARG;
+  if (!img) return ORBX_ERR_EMPTY_IMAGE;
+  if (step < (size_t)c->P.W) return ORBX_ERR_ARG;
+  if (!c->cameraSet) return ORBX_ERR_STATE;
+  CU(c, cudaSetDevice(c->device));
+  return run_frame_graph(c, 1, img, step, lapping, kps, desc, cap, n_out, mono_index, kps_un, grid_offsets, grid_indices);
+}
 
 extern "C" int orbx_extract_batch(orbx_ctx* c, const uint8_t* const* imgs, size_t step, int n_img,
                                   const int lapping[2], orbx_keypoint* kps, uint8_t* desc, int cap, int* n_out,
@@ -130,6 +239,10 @@ extern "C" int orbx_extract_batch(orbx_ctx* c, const uint8_t* const* imgs, size_
     if (!imgs[i]) return ORBX_ERR_EMPTY_IMAGE;
   if (step < (size_t)P.W) return ORBX_ERR_ARG;
   CU(c, cudaSetDevice(c->device));
+  // one frame: the latency path (one graph launch, one synchronisation); orbx_set_option("frame_graph", 0) keeps the
+  // plain launch sequence (the stage timers need it)
+  if (n_img == 1 && P.optFrameGraph && !c->stageTiming)
+    return run_frame_graph(c, 0, imgs[0], step, lapping, kps, desc, cap, n_out, mono_index, nullptr, nullptr, nullptr);
   c->launches = 0;
   for (int i = 0; i < n_img; ++i)
     CU(c, cudaMemcpy2DAsync(P.pyr + (size_t)i * P.slabBytes + P.lv[0].imgOff, P.lv[0].pitch, imgs[i], step, P.W, P.H,

@@ -13,7 +13,11 @@ namespace orbx {
 void launch_features_in_area(const Params& P, const orbx_keypoint* kun, const u32* gOff, const u32* gIdx, float x,
                              float y, float r, int minLevel, int maxLevel, int* out, int cap, int* count,
                              cudaStream_t st);
+void launch_features_in_area_batch(const Params& P, const orbx_keypoint* keysUn, const u32* gridOff, const u32* gridIdx, int stride,
+                                   const int* slots, const float* q5, int nQ, int* out, int cap, int* counts, cudaStream_t st);
 }
+
+static int score_reserve(orbx_ctx* c, size_t bytes);  // scratch block shared by the scoring and the batched query calls
 
 // cv::undistortPoints for the four image corners (ComputeImageBounds, SlamTypes/Frame.cpp:101-134).
 // Runs once per context on the host: it is constructor arithmetic like the level tables, and its
@@ -60,6 +64,7 @@ extern "C" int orbx_set_camera(orbx_ctx* c, const float K4[4], const float dist4
   P.gridHInv = (float)kGridRows / (float)(P.bounds[3] - P.bounds[2]);
   if (bounds_out) std::memcpy(bounds_out, P.bounds, sizeof(P.bounds));
   c->cameraSet = 1;
+  ++c->graphEpoch;
   return ORBX_OK;
 }
 
@@ -122,6 +127,38 @@ extern "C" int orbx_features_in_area(orbx_ctx* c, const orbx_frame* F, float x, 
   const int m = std::min(n, dcap);
   if (m > 0) CU(c, cudaMemcpy(out, c->hfMatches, (size_t)m * sizeof(int), cudaMemcpyDeviceToHost));
   return n;
+}
+
+// Radius queries on the frames the stream path left on the device: no frame is uploaded; n queries in one
+// launch, a warp each.
+extern "C" int orbx_stream_features_in_area(orbx_ctx* c, int n_queries, const int* slots, const float* queries5, int* out, int cap,
+                                            int* counts) {
+  if (!c || n_queries < 0 || cap < 0) return ORBX_ERR_ARG;
+  if (n_queries == 0) return ORBX_OK;
+  if (!slots || !queries5 || !counts || (cap > 0 && !out)) return ORBX_ERR_ARG;
+  if (!c->cameraSet) return ORBX_ERR_STATE;
+  for (int i = 0; i < n_queries; ++i)
+    if (slots[i] < 0 || slots[i] >= c->P.maxBatch) return ORBX_ERR_ARG;
+  CU(c, cudaSetDevice(c->device));
+  int rc = drain_flights(c);
+  if (rc) return rc;
+  const size_t nq = (size_t)n_queries, need = nq * sizeof(int) * 2 + nq * 5 * sizeof(float) + nq * (size_t)std::max(cap, 1) * sizeof(int) + 1024;
+  if ((rc = score_reserve(c, need))) return rc;   // the scratch block of the "next row" calls
+  u8* base = c->dScore;
+  int* dSlots = reinterpret_cast<int*>(base);
+  int* dCounts = dSlots + nq;
+  float* dQ = reinterpret_cast<float*>(dCounts + nq);
+  int* dOut = reinterpret_cast<int*>(dQ + 5 * nq);
+  cudaStream_t st = c->stream;
+  CU(c, cudaMemcpyAsync(dSlots, slots, nq * sizeof(int), cudaMemcpyHostToDevice, st));
+  CU(c, cudaMemcpyAsync(dQ, queries5, nq * 5 * sizeof(float), cudaMemcpyHostToDevice, st));
+  launch_features_in_area_batch(c->P, c->P.keysUn, c->P.gridOff, c->P.gridIdx, c->P.kpStride, dSlots, dQ, n_queries, dOut, cap, dCounts, st);
+  c->launches = 1;
+  CU(c, cudaGetLastError());
+  CU(c, cudaMemcpyAsync(counts, dCounts, nq * sizeof(int), cudaMemcpyDeviceToHost, st));
+  if (cap > 0) CU(c, cudaMemcpyAsync(out, dOut, nq * (size_t)cap * sizeof(int), cudaMemcpyDeviceToHost, st));
+  CU(c, cudaStreamSynchronize(st));
+  return ORBX_OK;
 }
 
 extern "C" int orbx_search_for_initialization(orbx_ctx* c, const orbx_frame* F1, const orbx_frame* F2, float nnratio,
@@ -285,9 +322,7 @@ extern "C" int orbx_descriptor_distance_batch(orbx_ctx* c, const uint8_t* a, con
 }
 
 // ---- Initializer scoring -------------------------------------------------------------
-namespace {
-size_t up256(size_t b) { return (b + 255) & ~(size_t)255; }
-int score_reserve(orbx_ctx* c, size_t bytes) {
+static int score_reserve(orbx_ctx* c, size_t bytes) {
   if (bytes <= c->scoreBytes) return ORBX_OK;
   if (c->dScore) cudaFree(c->dScore);
   c->dScore = nullptr; c->scoreBytes = 0;
@@ -295,6 +330,8 @@ int score_reserve(orbx_ctx* c, size_t bytes) {
   c->scoreBytes = bytes;
   return ORBX_OK;
 }
+namespace {
+size_t up256(size_t b) { return (b + 255) & ~(size_t)255; }
 // invSigmaSquare = 1.0 / (sigma * sigma): float product, double division, narrowed (Initializer.cpp:293,376)
 float inv_sigma_square(float sigma) { const float s2 = sigma * sigma; return (float)(1.0 / (double)s2); }
 

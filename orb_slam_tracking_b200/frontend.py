@@ -141,10 +141,23 @@ class Frame:
     """Frame(im, extractor, K4, D4): extract -> undistort -> grid, as the reference constructor
     (SlamTypes/Frame.cpp:40-82).  The extractor's camera must have been set (statics in the reference)."""
 
-    def __init__(self, extractor, im=None, kps=None, desc=None):
+    def __init__(self, extractor, im=None, kps=None, desc=None, fused=False, vLappingArea=(0, 0)):
         self.ex = extractor
+        if im is not None and fused:
+            # the single-call form (orbx_frame_construct): one CUDA graph, one synchronisation
+            cap = extractor.cap
+            k, d = np.zeros(cap, KP_DTYPE), np.zeros((cap, 32), np.uint8)
+            ku, off, idx = np.zeros(cap, KP_DTYPE), np.zeros(GRID_CELLS + 1, np.uint32), np.zeros(cap, np.uint32)
+            n, mono = C.c_int(0), C.c_int(0)
+            lap = np.asarray(vLappingArea, np.int32)
+            check(lib().orbx_frame_construct(extractor._h, ptr(im), im.strides[0], ptr(lap), ptr(k), ptr(d), cap, C.addressof(n),
+                                             C.addressof(mono), ptr(ku), ptr(off), ptr(idx)), extractor._h)
+            self.N, self.monoIndex = n.value, mono.value
+            self.mvKeys, self.mDescriptors, self.mvKeysUn = k[:self.N].copy(), d[:self.N].copy(), ku[:self.N].copy()
+            self.grid_offsets, self.grid_indices = off, idx[:int(off[-1])].copy()
+            return
         if im is not None:
-            kps, desc, _ = extractor(im)
+            kps, desc, _ = extractor(im, vLappingArea=vLappingArea)
         self.mvKeys = np.ascontiguousarray(kps, KP_DTYPE)
         self.mDescriptors = np.ascontiguousarray(desc, np.uint8)
         self.N = len(self.mvKeys)
@@ -332,6 +345,17 @@ class Stream:
     def wait(self, ticket):
         check(lib().orbx_stream_wait(self.ex._h, ticket), self.ex._h)
         return self._flight.pop(ticket)[1]
+
+    def features_in_area(self, slots, queries, cap=None):
+        """Batched GetFeaturesInArea on the resident frames: queries [n, 5] = (x, y, r, minLevel, maxLevel), slots [n].
+        -> list of index arrays in the reference's visiting order."""
+        q = np.ascontiguousarray(queries, np.float32).reshape(-1, 5)
+        sl = np.ascontiguousarray(slots, np.int32)
+        cap = cap or self.ex.cap
+        out = np.zeros((len(q), cap), np.int32)
+        cnt = np.zeros(len(q), np.int32)
+        check(lib().orbx_stream_features_in_area(self.ex._h, len(q), ptr(sl), ptr(q), ptr(out), cap, ptr(cnt)), self.ex._h)
+        return [out[i, :min(int(cnt[i]), cap)].copy() for i in range(len(q))], cnt
 
     def score_models(self, n_pairs, H21=None, H12=None, F21=None, sigma=1.0):
         """CheckHomography / CheckFundamental for [n_pairs, n_hyp, 9] hypothesis sets on the resident pairs."""

@@ -54,5 +54,15 @@ def test_dropin_demo_sequence(tmp_path, oracle):
     assert int(res[5]) == oracle.descriptor_distance(F[0].desc[0], F[1].desc[0])
     area = [l for l in out.stdout.splitlines() if l.startswith("AREA")][0].split()
     assert int(area[1]) == len(F[1].features_in_area(300.0, 200.0, 50.0, 0, 0))
-    assert "bad dist: %d bad ratio: %d bad orientation: %d" % tuple(cnt) in out.stdout
-    assert "Sum of features: %d" % nf in out.stdout
+    assert int(area[7].split("x")[0]) == 627 and int(area[5]) == 8      # mvImagePyramid is filled like the reference's
+    # the reference's own stdout lines (Features/ORBextractor.cpp:549, Features/ORBmatcher.cpp:144-147)
+    assert "Sum of features = %d" % nf in out.stdout
+    want = ("SearchForInitialization done ----------------------\ninvalidMatchByDistance: %d\ninvalidMatchByRatio: %d\n"
+            "invalidMatchByOrientation: %d\n" % tuple(cnt))
+    assert want in out.stdout
+    st = [l for l in out.stdout.splitlines() if l.startswith("STATICS")][0].split()
+    assert (int(st[3]), int(st[4]), int(st[5]), int(st[6])) == tuple(int(v) for v in b)       # Frame::mnMinX ... as data members
+    assert abs(float(st[1]) - float(K4[0])) < 1e-3 and st[8] == "2" and st[10:] == ["0", "1"]   # nNextId, mnId
+    assert [l for l in out.stdout.splitlines() if l.startswith("COPY")][0].split()[1:] == [str(F[1].N), "1", "1", "1"]
+    assert [l for l in out.stdout.splitlines() if l.startswith("NODE")][0].split()[1:] == ["51", "26", "3", "0", "0", "2", "0"]
+    assert [l for l in out.stdout.splitlines() if l.startswith("LATENCY")]

@@ -273,3 +273,42 @@ def test_stream_process_async_two_in_flight(fe, oracle, synth):
     same(S.wait(t0), want[3], B)
     S.sync()
     E.close()
+
+
+def test_stream_features_in_area_batched(fe, oracle, synth):
+    """radius queries with level ranges on the frames the stream path left on the device, 1000 random
+    windows per frame in one launch, against Frame::GetFeaturesInArea of the oracle (order included)."""
+    W, H, nf, B = 752, 480, 1200, 4
+    K4, D4 = synth.camera_for(W, H)
+    E = fe.ORBextractor(nf, 1.2, 8, 20, 7, W, H, max_batch=B)
+    bounds = E.set_camera(K4, D4)
+    R = oracle.Extractor(nf, 1.2, 8, 20, 7)
+    imgs = synth.frames(B, W, H, first_pair=50)
+    S = fe.Stream(E, 0.9, True, 100)
+    S.upload(imgs)
+    S.run(B)
+    S.sync()
+    O = []
+    for im in imgs:
+        k, d, _ = R(im)
+        O.append(oracle.Frame(k, d, K4, D4, bounds))
+    rng = np.random.default_rng(8)
+    n = 1000
+    q = np.zeros((B * n, 5), np.float32)
+    q[:, 0] = rng.uniform(-150, W + 150, B * n)
+    q[:, 1] = rng.uniform(-150, H + 150, B * n)
+    q[:, 2] = rng.choice([3.0, 10.0, 40.0, 100.0, 350.0, 8192.0], B * n)
+    lo = rng.integers(-1, 5, B * n)
+    q[:, 3] = lo
+    q[:, 4] = np.where(rng.random(B * n) < 0.3, -1, lo + rng.integers(0, 4, B * n))
+    q[:8] = [[0, 0, 100, -1, -1], [5000, 5000, 10, 0, 0], [-5000, 0, 10, 0, 0], [376, 240, 8192, 0, 7],
+             [376, 240, 8192, -1, -1], [376, 240, 1e-3, -1, -1], [376, -4000, 10, 0, 3], [376, 240, 50, 3, 1]]
+    slots = np.repeat(np.arange(B, dtype=np.int32), n)
+    got, cnt = S.features_in_area(slots, q)
+    for i in range(B * n):
+        want = O[slots[i]].features_in_area(float(q[i, 0]), float(q[i, 1]), float(q[i, 2]), int(q[i, 3]), int(q[i, 4]))
+        assert cnt[i] == len(want) and np.array_equal(got[i], want), (i, q[i])
+    # a small cap truncates the lists but keeps the counts
+    got2, cnt2 = S.features_in_area(slots[:50], q[:50], cap=5)
+    assert np.array_equal(cnt2, cnt[:50]) and all(np.array_equal(a, b[:5]) for a, b in zip(got2, got[:50]))
+    E.close()

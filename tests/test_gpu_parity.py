@@ -229,3 +229,45 @@ def test_other_pyramid_shapes(fe, oracle, synth, nf, sf, nl, W, H):
     _assert_kps_equal(kps, rk, "packed keypoints")
     assert np.array_equal(desc, rd) and mono == rmono
     E.close()
+
+
+def test_single_frame_graph_path(fe, oracle, synth):
+    """The latency path: orbx_extract of one image and orbx_frame_construct run through a CUDA graph (one launch, one
+    synchronisation).  Same bits as the plain launch sequence and as the oracle; the graph is rebuilt when the lapping
+    area, the camera or an option changes, and reused otherwise."""
+    W, H, nf = 752, 480, 1200
+    K4, D4 = synth.camera_for(W, H)
+    E = fe.ORBextractor(nf, 1.2, 8, 20, 7, W, H, max_batch=2)
+    bounds = E.set_camera(K4, D4)
+    R = oracle.Extractor(nf, 1.2, 8, 20, 7)
+    imgs = synth.frames(4, W, H, first_pair=90)
+    for it, (im, lap) in enumerate(zip(list(imgs) + [imgs[0]], [(0, 0), (0, 0), (200, 420), (200, 420), (0, 0)])):
+        k, d, mono = R(im, lap)
+        O = oracle.Frame(k, d, K4, D4, bounds)
+        E.set_option("frame_graph", 1)
+        gk, gd, gm = E(im, vLappingArea=lap)                   # graph, extraction only
+        F = fe.Frame(E, im, fused=True, vLappingArea=lap)      # graph, extraction + glue
+        E.set_option("frame_graph", 0)
+        pk, pd, pm = E(im, vLappingArea=lap)                   # plain launches
+        for kk, dd, mm in ((gk, gd, gm), (F.mvKeys, F.mDescriptors, F.monoIndex), (pk, pd, pm)):
+            assert mm == mono and len(kk) == len(k)
+            assert np.array_equal(kk.view(np.uint8), k.view(np.uint8)) and np.array_equal(dd, d), it
+        assert np.array_equal(F.mvKeysUn.view(np.uint8), O.keys_un().view(np.uint8))
+        off, idx = O.grid()
+        assert np.array_equal(F.grid_offsets, off) and np.array_equal(F.grid_indices, idx)
+    # a strided image and a batch call in between do not disturb the graph's staging
+    big = np.zeros((H, W + 40), np.uint8)
+    big[:, :W] = imgs[1]
+    E.set_option("frame_graph", 1)
+    k, d, _ = R(imgs[1])
+    gk, gd, _ = E(big[:, :W])
+    assert np.array_equal(gk.view(np.uint8), k.view(np.uint8)) and np.array_equal(gd, d)
+    res = E.extract_batch([imgs[2], imgs[3]])
+    k3, d3, _ = R(imgs[3])
+    assert np.array_equal(res[1][0].view(np.uint8), k3.view(np.uint8))
+    gk, gd, _ = E(imgs[1])
+    assert np.array_equal(gk.view(np.uint8), k.view(np.uint8)) and np.array_equal(gd, d)
+    # flat image: zero keypoints through the graph
+    F0 = fe.Frame(E, np.full((H, W), 9, np.uint8), fused=True)
+    assert F0.N == 0 and F0.grid_offsets[-1] == 0
+    E.close()
