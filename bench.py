@@ -129,6 +129,68 @@ def cpu_impl():
     return orb_oracle, "port"
 
 
+def cpu_sample_frames(wl, threads):
+    """Frames per pass of the CPU legs (the cpu_baseline object and --impl reference use the SAME sample)."""
+    return max(16 * threads, 64) if wl["W"] * wl["H"] < 2_000_000 else 2 * threads
+
+
+def opencv_primitives(wl, n_frames=8):
+    """The "real OpenCV" data point: the three streaming stages of the reference -- the resize chain with
+    its reflect-101 frames (ORBextractor.cpp:1660-1713), per-cell cv::FAST at iniTh with the minTh retry (:1051-1141) and
+    the 7x7 GaussianBlur of every level (:1598-1606) -- with the cv2 wheel (IPP / AVX-512 OpenCV), per frame, at 1 thread
+    and at OpenCV's default thread count.  The CPU arms above run the reference's sources over the scalar
+    oracle/cv_prims.hpp; this says how much faster a production OpenCV makes those stages."""
+    import math
+    import cv2
+    from orb_slam_tracking_b200 import synth
+    W, H = wl["W"], wl["H"]
+    imgs = synth.tile_frames(n_frames, W, H, unique_pairs=min(4, n_frames // 2))
+    sizes = level_sizes(W, H)
+    fi = cv2.FastFeatureDetector_create(wl["ini"], True, cv2.FAST_FEATURE_DETECTOR_TYPE_9_16)
+    fm = cv2.FastFeatureDetector_create(wl["mn"], True, cv2.FAST_FEATURE_DETECTOR_TYPE_9_16)
+    out = {}
+    default_threads = cv2.getNumThreads()
+    for label, nt in (("threads_1", 1), ("threads_default", default_threads)):
+        cv2.setNumThreads(nt)
+        t = {"pyramid": 0.0, "fast": 0.0, "blur": 0.0}
+        for im in imgs:
+            t0 = time.perf_counter()
+            pyr = [im]
+            for (w, h) in sizes[1:]:
+                pyr.append(cv2.resize(pyr[-1], (w, h), interpolation=cv2.INTER_LINEAR))
+            padded = [cv2.copyMakeBorder(p, 19, 19, 19, 19, cv2.BORDER_REFLECT_101) for p in pyr]
+            t1 = time.perf_counter()
+            for p in pyr:
+                h, w = p.shape
+                mbx, mby = w - 16, h - 16
+                nc, nr = int((mbx - 16) / 35.0), int((mby - 16) / 35.0)
+                wc, hc = math.ceil((mbx - 16) / nc), math.ceil((mby - 16) / nr)
+                for i in range(nr):
+                    y0 = 16 + i * hc
+                    if y0 >= mby - 3:
+                        continue
+                    y1 = min(y0 + hc + 6, mby)
+                    for j in range(nc):
+                        x0 = 16 + j * wc
+                        if x0 >= mbx - 6:
+                            continue
+                        roi = p[y0:y1, x0:min(x0 + wc + 6, mbx)]
+                        if not fi.detect(roi):
+                            fm.detect(roi)
+            t2 = time.perf_counter()
+            for p in padded:
+                cv2.GaussianBlur(p[19:-19, 19:-19].copy(), (7, 7), 2, None, 2, cv2.BORDER_REFLECT_101)
+            t3 = time.perf_counter()
+            t["pyramid"] += t1 - t0; t["fast"] += t2 - t1; t["blur"] += t3 - t2
+        out[label] = {"threads": nt, "ms_per_frame": {k: round(v / n_frames * 1e3, 3) for k, v in t.items()},
+                      "frames_per_s_these_stages_only": n_frames / sum(t.values())}
+    cv2.setNumThreads(default_threads)
+    out["kind"] = "opencv"
+    out["version"] = cv2.__version__
+    out["sample"] = "%d frames of %s; Python call overhead of the per-cell FAST calls included" % (n_frames, wl["desc"])
+    return out
+
+
 def cpu_baseline(wl, n_frames, threads, target_s=12.0, repeats=None):
     """The reference's CPU path on a bounded sample of the same workload (about `target_s` seconds of
     work, or exactly `repeats` passes).  Only the processing is timed (images are generated before)."""
@@ -163,7 +225,7 @@ def run_reference(args, wl):
     if rank != 0:
         return
     threads = host_threads()
-    per_step = max(8 * threads, 32) if wl["W"] * wl["H"] < 2_000_000 else 2 * threads
+    per_step = cpu_sample_frames(wl, threads)
     fps, dt, _, kind = cpu_baseline(wl, per_step, threads, repeats=args.steps)
     sample = "%d frames (%d pairs) of %s per step, %d host threads, %s" % (
         per_step, per_step // 2, wl["desc"], threads,
@@ -299,6 +361,14 @@ def run_ours(args, wl):
     launches = L.orbx_last_launch_count(E._h) * args.steps
     assert launches > 0, "no kernel launches counted"
     clocks = sampler.stop() if rank == 0 else None
+    # the same resident step repeated for at least a second: the K-step headline region is tens of milliseconds, too
+    # short for the clock sampler (100 ms period) and for the sustained clocks to settle
+    k_sus = max(args.steps, int(np.ceil(1200.0 / max(ms / args.steps, 1e-3))))
+    sampler2 = ClockSampler(local)
+    if rank == 0:
+        sampler2.start()
+    ms_sus = timed(step_resident, k_sus)
+    clocks_sus = sampler2.stop() if rank == 0 else None
     for _ in range(2):
         step_e2e()
     ms_e2e_call = timed(step_e2e, args.steps)
@@ -306,6 +376,14 @@ def run_ours(args, wl):
         step_e2e_stream()
     flush_e2e_stream()
     ms_e2e = timed(step_e2e_stream, args.steps, flush_e2e_stream)
+    # what the host link alone needs for one e2e step: the same uploads and downloads with no kernels, every rank at once
+    barrier()
+    link_ms = C.c_float(0)
+    hp_out = L.orbx_host_alloc(nbytes_out)
+    capi.check(L.orbx_hostlink_probe(E._h, hp, nbytes_in, hp_out, nbytes_out, 5, C.byref(link_ms)), E._h)
+    L.orbx_host_free(hp_out)
+    link_ms_step = shard.max_over_ranks(link_ms.value, device="cuda")
+    barrier()
     # per-stage device times (separate pass: the stage events are not in the timed region above)
     L.orbx_set_stage_timing(E._h, 1)
     acc = np.zeros(8)
@@ -356,6 +434,30 @@ def run_ours(args, wl):
             dt = time.perf_counter() - t0
             scoring["cpu"] = {"hypothesis_match_evals_per_s": ev / dt, "cores": 1, "kind": "reference" if use_ref else "port",
                               "sample": "%d pairs x %d hypotheses x 2 models" % (min(nP, 8), nh)}
+    # the same resident step on other inputs (the headline batch is 16 distinct pairs tiled; FAST, quadtree
+    # and matcher costs are data dependent): (i) a batch of B DISTINCT synthetic frames, (ii) the reference's own four
+    # 640x480 images (Thirdparty/DBoW2/demo/images, carried in tests/golden/dbow_640x480_nf1000.npz) tiled to the batch
+    variants = {}
+    if args.variants and args.workload == "tum":
+        def resident_fps(batch):
+            pinned[...] = batch
+            capi.check(L.orbx_stream_upload(E._h, hp, B), E._h)
+            for _ in range(3):
+                step_resident()
+            S.sync()
+            return world * B * args.steps / (timed(step_resident, args.steps) * 1e-3)
+        variants["distinct_frames"] = {"value": resident_fps(synth.frames_parallel(B, W, H, first_pair=1000 + pair_lo)), "unit": UNIT,
+                                       "frames": B, "what": "every frame of the batch distinct (B/2 synthetic pairs)"}
+        try:
+            import cv2
+            z = np.load(ROOT / "tests" / "golden" / "dbow_640x480_nf1000.npz")
+            real = np.stack([cv2.imdecode(z["png%d" % i], cv2.IMREAD_GRAYSCALE) for i in range(4)])
+            variants["real_images_tiled"] = {"value": resident_fps(np.concatenate([real] * (B // 4 + 1))[:B]), "unit": UNIT,
+                                             "what": "the reference's four DBoW2 demo images (640x480 gray) tiled to the batch"}
+        except Exception as e:   # fixture or cv2 missing: report, do not fail the run
+            variants["real_images_tiled"] = {"unavailable": type(e).__name__}
+        pinned[...] = imgs
+        capi.check(L.orbx_stream_upload(E._h, hp, B), E._h)
     # single-frame latency through the reference's own call shape ("report both single-frame latency and
     # batched throughput"): one Frame::Frame per image (orbx_frame_construct: host image in, keypoints / descriptors /
     # undistorted keys / grid out, ONE CUDA graph launch and ONE synchronisation) and one SearchForInitialization per pair
@@ -429,11 +531,16 @@ def run_ours(args, wl):
                        "sharding": "independent frame pairs per rank, no collective", "host_binding_rank0": binding},
             "e2e": {"value": fps_e2e, "unit": UNIT, "h2d_bytes_per_step": int(nbytes_in), "d2h_bytes_per_step": int(nbytes_out),
                     "ms_per_step": ms_e2e / args.steps, "api": "orbx_stream_process_async + orbx_stream_wait, 2 steps in flight",
+                    "host_link": {"copy_only_ms_per_step": link_ms_step, "frac_of_e2e_step": link_ms_step / (ms_e2e / args.steps),
+                                  "h2d_GBps_per_gpu": nbytes_in / (link_ms_step * 1e-3) / 1e9,
+                                  "what": "orbx_hostlink_probe: this step's H2D and D2H bytes, both directions at once, no kernels, all ranks at once"},
                     "chunk_frames": args.chunk if args.chunk > 0 else "auto: 3 equal chunks per step on 3 compute lanes",
                     "blocking_call": {"value": world * B * args.steps / (ms_e2e_call * 1e-3), "ms_per_step": ms_e2e_call / args.steps,
                                       "api": "orbx_stream_process (one step at a time)"}},
             "gpu_launches": int(launches),
             "clocks": clocks,
+            "sustained": {"value": world * B * k_sus / (ms_sus * 1e-3), "unit": UNIT, "steps": k_sus, "seconds": ms_sus * 1e-3,
+                          "ms_per_step": ms_sus / k_sus, "clocks": clocks_sus},
             "stage_ms_per_step": {STAGES[i]: round(float(stage_ms[i]), 4) for i in range(8) if i != 5},
             "pipeline_hbm": {"algorithmic_GBps": ab["frame"] * fps / world / 1e9, "frac_of_peak": ab["frame"] * fps / world / 1e9 / peak,
                              "bytes_per_frame": ab["frame"]},
@@ -442,12 +549,17 @@ def run_ours(args, wl):
                          "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "launches_per_step": n_launch_dom,
                          "ms_per_step": dom_ms, "algorithmic_bytes_per_step": int(ab[dom] * B)},
         }
+        line["variants"] = variants
         line["latency"] = latency
         line["next_rows"] = {"init_scoring": scoring, "brute_force_hamming": brute}
         if world == 1 and not args.no_cpu:
             threads = host_threads()
-            n_cpu = max(16 * threads, 64) if W * H < 2_000_000 else 2 * threads
+            n_cpu = cpu_sample_frames(wl, threads)
             v, dt, reps, kind = cpu_baseline(wl, n_cpu, threads)
+            try:
+                line["cpu_opencv_primitives"] = opencv_primitives(wl)
+            except Exception as e:   # no cv2 on the box: the reference-source arm below is the baseline
+                line["cpu_opencv_primitives"] = {"unavailable": type(e).__name__}
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": kind,
                                     "sample": "%d passes over %d frames (%d pairs) of the same workload, %.1f s, %s" % (
                                         reps, n_cpu, n_cpu // 2, dt, "reference sources compiled in place (oracle/_ref)"
@@ -472,6 +584,7 @@ def main():
     ap.add_argument("--chunk", type=int, default=0,
                     help="frames per pipelined chunk of the e2e path (0 = the library's default: 3 equal chunks per step when streaming, 128 ramped when blocking)")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-variants", dest="variants", action="store_false", help="skip the distinct-frame and real-image batches")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":

@@ -78,6 +78,13 @@ void orbx_destroy(orbx_ctx* ctx);
 const char* orbx_last_error(const orbx_ctx* ctx); /* never NULL */
 /* 0: (float)cos((double)a) [default, pinned by the oracle]; 1: cosf(a).  See DESIGN.md. */
 int orbx_set_trig_mode(orbx_ctx* ctx, int mode);
+/* Keypoint selection policy of the context: 0 = ComputeKeyPointsOctTree (default; what the reference's operator() calls,
+ * Features/ORBextractor.cpp:1552), 1 = ComputeKeyPointsOld (:1207-1496, the alternative the reference keeps behind a
+ * commented-out call, :1555): its own cell grid, the minThFAST retry for cells with at most 3 keypoints, per-cell quotas
+ * and cv::KeyPointsFilter::retainBest (libstdc++'s std::nth_element order).  Everything else of operator() is shared.
+ * Returns ORBX_ERR_ARG for shapes on which that function divides by zero (a level quota too small for one cell column) or
+ * whose cells are wider than 480 tested columns. */
+int orbx_set_keypoint_policy(orbx_ctx* ctx, int policy);
 /* Schedule options of a context (they never change results).  The environment is read ONCE, in orbx_create
  * (ORBX_SINGLE_STREAM, ORBX_RUN_PARTS, ORBX_LANES, ORBX_RESIZE_ROWS, ORBX_MATCH_SERIAL, ORBX_FAST_TILE); this call
  * changes an option of a live context: name = "single_stream" | "run_parts" | "lanes" | "resize_rows" | "match_serial" |
@@ -122,6 +129,12 @@ int orbx_get_blurred_level(orbx_ctx* ctx, int slot, int level, uint8_t* dst, siz
 int orbx_get_candidates(orbx_ctx* ctx, int slot, int level, float* xyr, int cap);
 /* keypoints of one level after distribution + orientation (+ descriptors), level coordinates */
 int orbx_get_level_keypoints(orbx_ctx* ctx, int slot, int level, orbx_keypoint* kps, uint8_t* desc, int cap);
+
+/* Copy-only probe of the host link: reps x (in_bytes pinned host -> device, out_bytes device -> pinned host, both
+ * directions at once, no kernels); *ms_per_rep = device time of one repetition.  bench.py runs it on every rank at the same
+ * time and reports the e2e step against it (e2e.host_link_frac). */
+int orbx_hostlink_probe(orbx_ctx* ctx, const void* host_in, size_t in_bytes, void* host_out, size_t out_bytes, int reps,
+                        float* ms_per_rep);
 
 /* ---- radius queries on device-resident frames ------------------------------ */
 /* Frame::GetFeaturesInArea (SlamTypes/Frame.cpp:163-206) for n_queries windows on the frames orbx_stream_run left on the

@@ -28,6 +28,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <algorithm>
 #include <vector>
 
 namespace orc {
@@ -292,6 +293,23 @@ static inline void undistort_point(float u, float v, const float K[4], const flo
 // ---- cv::cvtColor(BGR2GRAY), CV_8UC3 -> CV_8UC1 ---------------------------------------
 static inline u8 bgr2gray(u8 b, u8 g, u8 r) {
   return (u8)((3735 * b + 19235 * g + 9798 * r + 16384) >> 15);
+}
+
+// cv::KeyPointsFilter::retainBest(keypoints, n_points) -- OpenCV (un-vendored dependency of the reference; semantics of
+// the 4.x line, modules/features2d/src/keypoint.cpp, restated; the Python wheel does not expose it, so unlike the other
+// primitives it cannot be pinned against cv2 here: PARITY UNPINNED for this one function): when more than n_points are
+// held, std::nth_element puts the n_points largest responses first, every later keypoint whose response ties the n-th one
+// is kept as well (std::partition), the rest is dropped.  The element order is whatever the C++ library's nth_element and
+// partition leave -- libstdc++ here, as for std::sort in DistributeOctTree.  KP needs a float member `response`.
+template <typename KP>
+static inline void retain_best(std::vector<KP>& k, int n_points) {
+  if (n_points >= 0 && k.size() > (size_t)n_points) {
+    if (n_points == 0) { k.clear(); return; }
+    std::nth_element(k.begin(), k.begin() + n_points - 1, k.end(), [](const KP& a, const KP& b) { return a.response > b.response; });
+    const float ambiguous = k[n_points - 1].response;
+    typename std::vector<KP>::iterator e = std::partition(k.begin() + n_points, k.end(), [ambiguous](const KP& a) { return a.response >= ambiguous; });
+    k.resize((size_t)(e - k.begin()));
+  }
 }
 
 }  // namespace orc

@@ -316,6 +316,93 @@ static void detect_cells(const Level& L, int iniTh, int minTh, std::vector<Cand>
 }
 
 // =====================================================================================
+// ComputeKeyPointsOld, Features/ORBextractor.cpp:1207-1496: the alternate selection policy the
+// reference keeps behind a commented-out call (:1555).  Larger cells (about five keypoints per cell wanted), the
+// minThFAST retry when a cell yields at most 3 keypoints, a redistribution of the per-cell quotas towards the cells that
+// have more, and cv::KeyPointsFilter::retainBest per cell and per level.  Returns -7 where the reference divides by zero
+// (a level whose quota is too small for one cell column).
+// =====================================================================================
+static int keypoints_old(const Level& L, const Tables& t, int level, float imageRatio, std::vector<KeyPoint>& keypoints) {
+  keypoints.clear();
+  const int nDesired = t.perLevel[level];
+  const int levelCols = (int)std::sqrt((float)nDesired / (5 * imageRatio));  // :1225-1226
+  const int levelRows = (int)(imageRatio * levelCols);                       // :1228
+  if (levelCols < 1 || levelRows < 1) return -7;
+  const int minBX = kEdge, minBY = kEdge, maxBX = L.w - kEdge, maxBY = L.h - kEdge;  // :1233-1236
+  const int W = maxBX - minBX, H = maxBY - minBY;
+  const int cellW = (int)std::ceil((float)W / levelCols), cellH = (int)std::ceil((float)H / levelRows);
+  const int nCells = levelRows * levelCols;
+  const int nfeaturesCell = (int)std::ceil((float)nDesired / nCells);  // :1250-1251
+  std::vector<std::vector<KeyPoint>> cellKeys((size_t)nCells);
+  std::vector<int> nToRetain(nCells, 0), nTotal(nCells, 0), iniXCol(levelCols), iniYRow(levelRows);
+  std::vector<char> bNoMore(nCells, 0);
+  int nNoMore = 0, nToDistribute = 0;
+  std::vector<FastPt> cell;
+  float hY = (float)(cellH + 6);
+  for (int i = 0; i < levelRows; ++i) {
+    const float iniY = (float)(minBY + i * cellH - 3);
+    iniYRow[i] = (int)iniY;
+    if (i == levelRows - 1) {
+      hY = maxBY + 3 - iniY;
+      if (hY <= 0) continue;
+    }
+    float hX = (float)(cellW + 6);
+    for (int j = 0; j < levelCols; ++j) {
+      float iniX;
+      if (i == 0) { iniX = (float)(minBX + j * cellW - 3); iniXCol[j] = (int)iniX; }
+      else iniX = (float)iniXCol[j];
+      if (j == levelCols - 1) {
+        hX = maxBX + 3 - iniX;
+        if (hX <= 0) continue;
+      }
+      const int x0 = (int)iniX, y0 = (int)iniY, x1 = (int)(iniX + hX), y1 = (int)(iniY + hY);
+      const u8* roi = L.roi() + (size_t)y0 * L.step() + x0;
+      fast9_16_nms(roi, x1 - x0, y1 - y0, L.step(), t.iniTh, cell);                       // :1336-1340
+      if (cell.size() <= 3) fast9_16_nms(roi, x1 - x0, y1 - y0, L.step(), t.minTh, cell);  // :1343-1351 (fills `cell` afresh)
+      std::vector<KeyPoint>& out = cellKeys[(size_t)i * levelCols + j];
+      out.resize(cell.size());
+      for (size_t k = 0; k < cell.size(); ++k) {
+        KeyPoint kp;
+        kp.x = (float)cell[k].x; kp.y = (float)cell[k].y; kp.size = 7.f; kp.angle = -1.f; kp.response = (float)cell[k].score;
+        kp.octave = 0; kp.class_id = -1;
+        out[k] = kp;
+      }
+      const int c = i * levelCols + j, nKeys = (int)cell.size();
+      nTotal[c] = nKeys;
+      if (nKeys > nfeaturesCell) { nToRetain[c] = nfeaturesCell; bNoMore[c] = 0; }
+      else { nToRetain[c] = nKeys; nToDistribute += nfeaturesCell - nKeys; bNoMore[c] = 1; ++nNoMore; }
+    }
+  }
+  while (nToDistribute > 0 && nNoMore < nCells) {  // :1390-1425
+    const int nNew = nfeaturesCell + (int)std::ceil((float)nToDistribute / (nCells - nNoMore));
+    nToDistribute = 0;
+    for (int c = 0; c < nCells; ++c) {
+      if (bNoMore[c]) continue;
+      if (nTotal[c] > nNew) { nToRetain[c] = nNew; bNoMore[c] = 0; }
+      else { nToRetain[c] = nTotal[c]; nToDistribute += nNew - nTotal[c]; bNoMore[c] = 1; ++nNoMore; }
+    }
+  }
+  const int scaledPatch = (int)(kPatch * t.scale[level]);
+  for (int i = 0; i < levelRows; ++i)
+    for (int j = 0; j < levelCols; ++j) {
+      std::vector<KeyPoint>& kc = cellKeys[(size_t)i * levelCols + j];
+      const int keep = nToRetain[i * levelCols + j];
+      retain_best(kc, keep);                      // :1452
+      if ((int)kc.size() > keep) kc.resize(keep);  // :1455-1456
+      for (size_t k = 0; k < kc.size(); ++k) {
+        kc[k].x += iniXCol[j]; kc[k].y += iniYRow[i];
+        kc[k].octave = level; kc[k].size = (float)scaledPatch;
+        keypoints.push_back(kc[k]);
+      }
+    }
+  if ((int)keypoints.size() > nDesired) {  // :1480-1484
+    retain_best(keypoints, nDesired);
+    keypoints.resize(nDesired);
+  }
+  return 0;
+}
+
+// =====================================================================================
 // Orientation -- IC_Angle, Features/ORBextractor.cpp:103-159
 // =====================================================================================
 static float ic_angle(const u8* img, size_t step, float px, float py, const std::vector<int>& umax) {
@@ -366,6 +453,7 @@ static void brief256(const u8* img, size_t step, const KeyPoint& kp, int trigMod
 struct Extractor {
   Tables t;
   int trigMode;
+  int policy;  // 0: ComputeKeyPointsOctTree (what operator() calls, :1552); 1: ComputeKeyPointsOld (:1555, commented out)
   std::vector<Level> pyr;
   std::vector<std::vector<Cand>> cands;        // per level, FAST candidates (16,16)-relative
   std::vector<std::vector<KeyPoint>> levelKps;  // per level, after quadtree + orientation
@@ -382,7 +470,11 @@ static int extract(Extractor& E, const u8* img, int W, int H, size_t step, const
   E.levelKps.assign(t.nlevels, std::vector<KeyPoint>());
   E.blurred.assign(t.nlevels, std::vector<u8>());
   E.levelDesc.assign(t.nlevels, std::vector<u8>());
-  for (int l = 0; l < t.nlevels; ++l) {
+  for (int l = 0; l < t.nlevels && E.policy == 1; ++l) {
+    const int rc = keypoints_old(E.pyr[l], t, l, (float)E.pyr[0].w / E.pyr[0].h, E.levelKps[l]);  // :1213-1214
+    if (rc) return rc;
+  }
+  for (int l = 0; l < t.nlevels && E.policy == 0; ++l) {
     const Level& L = E.pyr[l];
     detect_cells(L, t.iniTh, t.minTh, E.cands[l]);
     const int minBX = kEdge - 3, minBY = minBX;
@@ -636,11 +728,13 @@ void* orc_extractor_create(int nfeatures, float scaleFactor, int nlevels, int in
   Extractor* e = new Extractor();
   e->t = make_tables(nfeatures, scaleFactor, nlevels, iniTh, minTh);
   e->trigMode = 0;
+  e->policy = 0;
   if (e->t.status) { delete e; return 0; }
   return e;
 }
 void orc_extractor_destroy(void* h) { delete (Extractor*)h; }
 void orc_extractor_set_trig_mode(void* h, int m) { ((Extractor*)h)->trigMode = m; }
+void orc_extractor_set_policy(void* h, int p) { ((Extractor*)h)->policy = p; }
 int orc_extractor_tables(void* h, float* scale, float* invScale, float* sigma2, float* invSigma2,
                          int* perLevel, int* umax16) {
   const Tables& t = ((Extractor*)h)->t;
@@ -768,6 +862,7 @@ long long orc_run_stream(const u8* imgs, int nframes, int W, int H, int nfeature
     Extractor E;
     E.t = make_tables(nfeatures, scaleFactor, nlevels, iniTh, minTh);
     E.trigMode = 0;
+    E.policy = 0;
     const int lap[2] = {0, 0};
     for (;;) {
       int p = next.fetch_add(1);

@@ -41,6 +41,7 @@ def lib():
         L.orc_extractor_create.argtypes = [C.c_int, C.c_float, C.c_int, C.c_int, C.c_int]
         L.orc_extractor_destroy.argtypes = [vp]
         L.orc_extractor_set_trig_mode.argtypes = [vp, C.c_int]
+        L.orc_extractor_set_policy.argtypes = [vp, C.c_int]
         L.orc_extractor_tables.argtypes = [vp, vp, vp, vp, vp, vp, vp]
         L.orc_extract.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp]
         L.orc_level_size.argtypes = [vp, C.c_int, vp, vp]
@@ -157,12 +158,14 @@ def image_bounds(W, H, K4, D4):
 class Extractor:
     """Mirror of ORB_SLAM_Tracking::ORBextractor (reference Features/ORBextractor.hpp:55-158)."""
 
-    def __init__(self, nfeatures, scale_factor, nlevels, ini_th, min_th, trig_mode=0):
+    def __init__(self, nfeatures, scale_factor, nlevels, ini_th, min_th, trig_mode=0, policy=0):
+        """policy 0: ComputeKeyPointsOctTree (the reference's operator()); 1: ComputeKeyPointsOld (its commented-out alternative)."""
         self.nfeatures, self.nlevels = nfeatures, nlevels
         self._h = lib().orc_extractor_create(nfeatures, scale_factor, nlevels, ini_th, min_th)
         if not self._h:
             raise ValueError("scaleFactor == 1.0 but nlevels is not 1")
         lib().orc_extractor_set_trig_mode(self._h, trig_mode)
+        lib().orc_extractor_set_policy(self._h, policy)
         f = lambda: np.zeros(nlevels, np.float32)
         self.scale, self.inv_scale, self.sigma2, self.inv_sigma2 = f(), f(), f(), f()
         self.per_level = np.zeros(nlevels, np.int32)

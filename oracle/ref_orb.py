@@ -20,7 +20,7 @@ _LIB = None
 
 def build():
     """Needs /root/reference; a no-op (and `available()` stays False) without it."""
-    srcs = [_DIR / "ref_driver.cpp", _DIR / "ref_init_driver.cpp", _DIR / "build_ref.sh", _DIR / "cv_prims.hpp", _DIR / "refshim" / "opencv2" / "opencv.hpp"]
+    srcs = [_DIR / "ref_driver.cpp", _DIR / "ref_init_driver.cpp", _DIR / "ref_old_driver.cpp", _DIR / "build_ref.sh", _DIR / "cv_prims.hpp", _DIR / "refshim" / "opencv2" / "opencv.hpp"]
     if SO.exists() and all(s.stat().st_mtime <= SO.stat().st_mtime for s in srcs):
         return SO
     subprocess.run(["bash", str(_DIR / "build_ref.sh")], check=True, stdout=subprocess.DEVNULL)
@@ -55,6 +55,11 @@ def lib():
         L.ref_forb_distance.argtypes = [vp, vp]
         L.ref_run_stream.restype = C.c_longlong
         L.ref_run_stream.argtypes = [vp, ci, ci, ci, ci, cf, ci, ci, ci, vp, vp, ci, cf, ci, vp]
+        if hasattr(L, "ref_old_extract"):
+            L.ref_old_extractor_create.restype = vp
+            L.ref_old_extractor_create.argtypes = [ci, cf, ci, ci, ci]
+            L.ref_old_extractor_destroy.argtypes = [vp]
+            L.ref_old_extract.argtypes = [vp, vp, ci, ci, ci, ci, ci, vp, vp, ci, vp]
         if hasattr(L, "ref_check_homography"):
             L.ref_check_homography.argtypes = [vp, ci, vp, ci, vp, vp, vp, ci, cf, vp, vp]
             L.ref_check_fundamental.argtypes = [vp, ci, vp, ci, vp, vp, ci, cf, vp, vp]
@@ -103,6 +108,32 @@ class Extractor:
         out = np.zeros((h.value, w.value), np.uint8)
         lib().ref_get_level(self._h, level, int(padded), _p(out), C.byref(w), C.byref(h))
         return out
+
+
+class OldPolicyExtractor:
+    """The reference's ORBextractor with operator() calling ComputeKeyPointsOld (Features/ORBextractor.cpp:1207-1496) instead
+    of ComputeKeyPointsOctTree: the reference's own code, one call swapped at build time (oracle/build_ref.sh)."""
+
+    def __init__(self, nfeatures, scale_factor, nlevels, ini_th, min_th):
+        self.nfeatures = nfeatures
+        self._h = lib().ref_old_extractor_create(nfeatures, scale_factor, nlevels, ini_th, min_th)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().ref_old_extractor_destroy(self._h)
+            self._h = None
+
+    def __call__(self, img, lapping=(0, 0)):
+        img = np.ascontiguousarray(img, np.uint8)
+        h, w = img.shape
+        cap = max(4 * self.nfeatures, 64)
+        kps = np.zeros(cap, KP_DTYPE)
+        desc = np.zeros((cap, 32), np.uint8)
+        mono = C.c_int(0)
+        n = lib().ref_old_extract(self._h, _p(img), w, h, img.strides[0], lapping[0], lapping[1], _p(kps), _p(desc), cap, C.byref(mono))
+        assert n >= -1, "capacity"
+        n = max(n, 0)
+        return kps[:n].copy(), desc[:n].copy(), mono.value
 
 
 class Frame:

@@ -307,12 +307,7 @@ static inline void undistortPoints(InputArray src_, OutputArray dst_, InputArray
 
 struct KeyPointsFilter {
   // only called from the reference's dead ComputeKeyPointsOld path (Features/ORBextractor.cpp:1452,1482)
-  static void retainBest(std::vector<KeyPoint>& k, int n) {
-    if (n >= 0 && (int)k.size() > n) {
-      std::stable_sort(k.begin(), k.end(), [](const KeyPoint& a, const KeyPoint& b) { return a.response > b.response; });
-      k.resize((size_t)n);
-    }
-  }
+  static void retainBest(std::vector<KeyPoint>& k, int n) { orc::retain_best(k, n); }
 };
 
 }  // namespace cv

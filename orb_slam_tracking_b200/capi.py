@@ -40,6 +40,7 @@ SIGNATURES = {
     "orbx_last_error": (C.c_char_p, [vp]),
     "orbx_set_trig_mode": (ci, [vp, ci]),
     "orbx_set_option": (ci, [vp, C.c_char_p, ci]),
+    "orbx_set_keypoint_policy": (ci, [vp, ci]),
     "orbx_get_level_tables": (ci, [vp, vp, vp, vp, vp, vp, vp]),
     "orbx_get_level_size": (ci, [vp, ci, vp, vp]),
     "orbx_compute_level_tables": (ci, [ci, cf, ci, vp, vp, vp, vp, vp, vp]),
@@ -76,6 +77,7 @@ SIGNATURES = {
     "orbx_set_stage_timing": (ci, [vp, ci]),
     "orbx_get_stage_times": (ci, [vp, vp]),
     "orbx_last_launch_count": (ci, [vp]),
+    "orbx_hostlink_probe": (ci, [vp, vp, sz, vp, sz, ci, vp]),
     "orbx_host_alloc": (vp, [sz]),
     "orbx_host_free": (None, [vp]),
     "orbx_get_stream": (vp, [vp]),

@@ -38,6 +38,9 @@ struct LevelInfo {
   u32 imgOff;         // byte offset of the level in a slot's slab
   int nCols, nRows, wCell, hCell;  // FAST cell grid, :1066-1075
   int fastBoxW, fastBoxH;  // TMA box of k_fast at this level: bytes per staged row (an odd multiple of 16), rows
+  // ComputeKeyPointsOld's own cell grid (Features/ORBextractor.cpp:1222-1251), filled when that policy is selected
+  int oCols, oRows, oCellW, oCellH, oNfCell;  // levelCols, levelRows, cellW, cellH, nfeaturesCell
+  int oBoxW, oBoxH;        // TMA box of k_fast for that grid
   int quota;          // mnFeaturesPerLevel[l]
   int candCap;        // capacity of the candidate arrays of this level
   u32 candOff;        // first candidate of this level in a slot's candidate arrays
@@ -63,7 +66,9 @@ struct StripDesc {    // one work item of k_fast: a run of consecutive FAST cell
   short wCell;
   short sx, sy;           // j0 * wCell, i * hCell: shift applied to ROI-relative coordinates (:1134-1135)
   short nIniM1;           // lv[level].nIni - 1
-  int tileBytes;          // fastBoxW * fastBoxH of the level: what the tile copy delivers
+  int tileBytes;          // box bytes of the level: what the tile copy delivers; bits 24..27: retryMax (a cell with at most that many
+                          // keypoints at iniThFAST runs again at minThFAST: 0 in ComputeKeyPointsOctTree, 3 in ComputeKeyPointsOld);
+                          // bits 28..31: bits per coordinate of the emission-order key (7 or 9)
   u32 cellMul;            // (xb * cellMul) >> 16 == xb / wCell for every interior column xb of a strip
   int index0;             // i * nCols + j0: row-major index of the strip's first cell
   u32 candOff;            // lv[level].candOff, candCap, rootTabOff
@@ -104,6 +109,10 @@ struct Params {
   u32* candNode;
   u32* candCount;      // [slot][kMaxLevels]
   const StripDesc* strips;
+  int kpPolicy;            // 0: ComputeKeyPointsOctTree (default), 1: ComputeKeyPointsOld (orbx_set_keypoint_policy)
+  u64* oldSorted;          // [slot][candTotal]  ComputeKeyPointsOld: candidates in the reference's order (response << 48 | y << 16 | x ...)
+  int* oldCell;            // [slot][oldCellTotal * 4]  per cell: count, start, nToRetain, flags
+  int oldCellTotal;        // cells of all levels (per slot)
   const BlurTile* blurTiles;
   const u8* rootTab;
   // quadtree node tables [slot][nodeTotal]
@@ -169,6 +178,7 @@ int launch_pyramid(const Params& P, const int* const* dTabs, int nSlots, cudaStr
 int launch_blur(const Params& P, int nSlots, cudaStream_t st);
 int launch_fast(const Params& P, const TmaMaps& M, int nSlots, cudaStream_t st);
 int launch_quadtree(const Params& P, int nSlots, cudaStream_t st);
+int launch_retain_old(const Params& P, int nSlots, cudaStream_t st);
 int launch_describe(const Params& P, int nSlots, int lap0, int lap1, cudaStream_t st);
 int launch_glue(const Params& P, int nSlots, cudaStream_t st);
 // scratch of the brute-force matcher (match_bf.cu), per pair; topk == nullptr: not available

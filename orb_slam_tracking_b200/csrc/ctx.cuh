@@ -29,7 +29,12 @@ int compute_tables(int nfeatures, float scaleFactor, int nlevels, HostTables& t)
 struct orbx_ctx {
   orbx::Params P;
   orbx::HostTables T;
-  orbx::TmaMaps tma;               // per-level tensor maps over P.pyr (k_fast tile staging)
+  orbx::TmaMaps tma;               // per-level tensor maps over P.pyr (k_fast tile staging) of the ACTIVE keypoint policy
+  struct FastSet {                 // what k_fast needs per keypoint policy ([0] ComputeKeyPointsOctTree, [1] ComputeKeyPointsOld)
+    const orbx::StripDesc* strips;
+    int nStrips, tileMax, segW, segP, grid, ready;
+    orbx::TmaMaps tma;
+  } fastSet[2];
   int device;
   cudaStream_t stream;
   static constexpr int kLanes = 4;

@@ -127,6 +127,8 @@ struct StripCtx {
   // emission
   int slot, level, sx, sy, index0, nIniM1, candCap;
   u32 candOff, rootTabOff;
+  int retryMax;           // a cell with at most this many keypoints at iniThFAST is tested again at minThFAST (and its iniThFAST keypoints dropped)
+  int orderBits;          // bits per coordinate of the emission-order key
 };
 
 // bytes of word g (bit 7 each) that lie inside [bLo, bHi)
@@ -159,32 +161,37 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
   const int SW = S.SW, SB = S.SB;
   const u32 K = (u32)(t < 128 ? 127 - t : 255 - t) * 0x01010101u;
 
-  // ---- phase A: a warp per interior row, a lane per aligned word pair (the strip's interior is at most 32 pairs wide) ----
+  // ---- phase A: a warp per interior row, a lane per aligned word pair.  The strips of the default grid are at most 32 pairs
+  // wide (one pass); the wide cells of ComputeKeyPointsOld take one pass per block of 32 pairs. ----
   int nW = 0;
   {
-    const int g = ((S.bLo >> 2) & ~1) + 2 * lane;  // first word of this lane's pair
-    u32 m0 = interior_mask(g, S.bLo, S.bHi), m1 = interior_mask(g + 1, S.bLo, S.bHi);
-    if (RETRY) { m0 &= cell_mask(S, g, cells); m1 &= cell_mask(S, g + 1, cells); }
-    const bool act = (m0 | m1) != 0;
-    for (int r = warp; r < S.nR; r += kFastWarps) {
-      u32 a0 = 0, a1 = 0;
-      if (act) {
-        const u32* p = S.imgW + (r + 3) * SW + g;
-        const uint2 c = *reinterpret_cast<const uint2*>(p);
-        const uint2 n = *reinterpret_cast<const uint2*>(p - 3 * SW);
-        const uint2 s = *reinterpret_cast<const uint2*>(p + 3 * SW);
-        const u32 l = p[-1], q = p[2];
-        a0 = m0 & any_gt<MODE>(__vabsdiffu4(c.x, n.x), __vabsdiffu4(c.x, s.x), K);
-        a1 = m1 & any_gt<MODE>(__vabsdiffu4(c.y, n.y), __vabsdiffu4(c.y, s.y), K);
-        a0 &= any_gt<MODE>(__vabsdiffu4(c.x, word_at<3>(l, c.x, c.y)), __vabsdiffu4(c.x, word_at<-3>(l, c.x, c.y)), K);
-        a1 &= any_gt<MODE>(__vabsdiffu4(c.y, word_at<3>(c.x, c.y, q)), __vabsdiffu4(c.y, word_at<-3>(c.x, c.y, q)), K);
+    const int gBase = (S.bLo >> 2) & ~1;
+    const int nQ = ((((S.bHi - 1) >> 2) - gBase) >> 1) + 1;
+    for (int qb = 0; qb < nQ; qb += 32) {
+      const int g = gBase + 2 * (qb + lane);  // first word of this lane's pair
+      u32 m0 = interior_mask(g, S.bLo, S.bHi), m1 = interior_mask(g + 1, S.bLo, S.bHi);
+      if (RETRY) { m0 &= cell_mask(S, g, cells); m1 &= cell_mask(S, g + 1, cells); }
+      const bool act = (m0 | m1) != 0;
+      for (int r = warp; r < S.nR; r += kFastWarps) {
+        u32 a0 = 0, a1 = 0;
+        if (act) {
+          const u32* p = S.imgW + (r + 3) * SW + g;
+          const uint2 c = *reinterpret_cast<const uint2*>(p);
+          const uint2 n = *reinterpret_cast<const uint2*>(p - 3 * SW);
+          const uint2 s = *reinterpret_cast<const uint2*>(p + 3 * SW);
+          const u32 l = p[-1], q = p[2];
+          a0 = m0 & any_gt<MODE>(__vabsdiffu4(c.x, n.x), __vabsdiffu4(c.x, s.x), K);
+          a1 = m1 & any_gt<MODE>(__vabsdiffu4(c.y, n.y), __vabsdiffu4(c.y, s.y), K);
+          a0 &= any_gt<MODE>(__vabsdiffu4(c.x, word_at<3>(l, c.x, c.y)), __vabsdiffu4(c.x, word_at<-3>(l, c.x, c.y)), K);
+          a1 &= any_gt<MODE>(__vabsdiffu4(c.y, word_at<3>(c.x, c.y, q)), __vabsdiffu4(c.y, word_at<-3>(c.x, c.y, q)), K);
+        }
+        const u32 b0 = __ballot_sync(0xffffffffu, a0 != 0), b1 = __ballot_sync(0xffffffffu, a1 != 0);
+        const u32 e = ((u32)(r + 3) << 8) | (u32)g;
+        if (a0) S.segW[nW + __popc(b0 & lt)] = a0 | e;
+        nW += __popc(b0);
+        if (a1) S.segW[nW + __popc(b1 & lt)] = a1 | (e + 1);
+        nW += __popc(b1);
       }
-      const u32 b0 = __ballot_sync(0xffffffffu, a0 != 0), b1 = __ballot_sync(0xffffffffu, a1 != 0);
-      const u32 e = ((u32)(r + 3) << 8) | (u32)g;
-      if (a0) S.segW[nW + __popc(b0 & lt)] = a0 | e;
-      nW += __popc(b0);
-      if (a1) S.segW[nW + __popc(b1 & lt)] = a1 | (e + 1);
-      nW += __popc(b1);
     }
   }
   __syncwarp();
@@ -254,7 +261,10 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
       const int mR = xb + 1 != cs + S.wCell ? max(max((int)q[-SB + 1], (int)q[1]), (int)q[SB + 1]) : 0;
       const int mN = max(max((int)q[-SB], (int)q[SB]), max(mL, mR));
       peak = m >= 2 && m > mN;
-      if (peak && !RETRY) S.cellIni[j] = 1;
+      if (peak && !RETRY) {
+        if (S.retryMax == 0) S.cellIni[j] = 1;     // ComputeKeyPointsOctTree only asks "any keypoint?" (:1116)
+        else atomicAdd(&S.cellIni[j], 1);          // ComputeKeyPointsOld counts them (:1343)
+      }
     }
     const u32 bp = __ballot_sync(0xffffffffu, peak);
     if (peak) segK[nK + __popc(bp & lt)] = (unsigned short)e;
@@ -262,6 +272,29 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
   }
   __syncwarp();
   // ---- phase P4: the keypoints of this run go to the level's candidate list ----
+  // ComputeKeyPointsOld drops the iniThFAST keypoints of a cell that has at most retryMax of them: its emission waits for
+  // the cell counts of all warps (after the barrier) and compacts the warp's peak list first.
+  const bool deferred = S.retryMax > 0 && !RETRY;
+  auto emit = [&]() {
+  if (deferred) {
+    int kept = 0;
+    for (int i0 = 0; i0 < nK; i0 += 32) {
+      const int i = i0 + lane;
+      bool on = false;
+      unsigned short e = 0;
+      if (i < nK) {
+        e = segK[i];
+        const int xb = (int)(e & 511) - S.bLo;
+        on = S.cellIni[(int)(((u32)xb * S.cellMul) >> 16)] > S.retryMax;
+      }
+      const u32 bo = __ballot_sync(0xffffffffu, on);
+      __syncwarp();
+      if (on) segK[kept + __popc(bo & lt)] = e;   // kept + rank <= i: in-place compaction, a chunk at a time
+      kept += __popc(bo);
+      __syncwarp();
+    }
+    nK = kept;
+  }
   if (nK > 0) {
     const size_t co = (size_t)S.slot * P.candTotal + S.candOff;
     const u8* rootTab = P.rootTab + S.rootTabOff;
@@ -278,14 +311,17 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
         const int j = (int)(((u32)xb * S.cellMul) >> 16);
         const int rx = xb - j * S.wCell + 3;  // ROI-relative column in the pixel's cell; the reference shifts by the cell origin (:1134-1135)
         const int x = xb + 3 + S.sx, y = ry + S.sy;  // relative to (16,16)
-        const u32 order = ((u32)(S.index0 + j) << 14) | ((u32)ry << 7) | (u32)rx;
+        const u32 order = ((u32)(S.index0 + j) << (2 * S.orderBits)) | ((u32)ry << S.orderBits) | (u32)rx;
         P.candKey[co + k] = ((u64)(u32)(m - 1) << 32) | (u64)(~order);
         P.candXY[co + k] = (u32)x | ((u32)y << 16);
         P.candNode[co + k] = (u32)(S.nIniM1 - __ldg(rootTab + x));  // root i lives at node nIni-1-i
       }
     }
   }
+  };
+  if (!deferred) emit();
   __syncthreads();  // every neighbour read of the m-map is done
+  if (deferred) emit();
   for (int i = lane; i < nP; i += 32) {  // the m-map entries of this run are cleared
     const int e = S.segP[i];
     S.mm[(e >> 9) * SB + (e & 511)] = 0;
@@ -330,7 +366,7 @@ __global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k_fast(const __g
   // thread 0: one TMA tile copy of a strip of a slot into ring buffer `buf`
   auto issue = [&](int sl, const StripDesc& d, int buf) {
     const u32 bar = smem_addr(&sBar[buf]);
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(d.tileBytes) : "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(d.tileBytes & 0xffffff) : "memory");
     asm volatile(
         "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
         ::"r"(smem_addr(smem + buf * P.fastTileMax)), "l"(reinterpret_cast<u64>(&M.lvl[d.level])), "r"((int)d.tmaX), "r"((int)d.y0),
@@ -356,6 +392,7 @@ __global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k_fast(const __g
     S.wCell = d.wCell; S.cellMul = d.cellMul;
     S.slot = slot; S.level = d.level; S.sx = d.sx; S.sy = d.sy; S.index0 = d.index0;
     S.nIniM1 = d.nIniM1; S.candCap = d.candCap; S.candOff = d.candOff; S.rootTabOff = d.rootTabOff;
+    S.retryMax = (d.tileBytes >> 24) & 15; S.orderBits = (int)((u32)d.tileBytes >> 28);
     {
       const u32 bar = smem_addr(&sBar[buf]);
       const u32 parity = (u32)(kFastStages == 1 ? k : k >> 1) & 1u;
@@ -367,10 +404,10 @@ __global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k_fast(const __g
       }
     }
     fast_run_mode(P, S, tIni, false, 0xffffffffu);
-    if (tMin < tIni) {  // cells without a keypoint at iniThFAST run again at minThFAST (:1119)
+    if (tMin < tIni || S.retryMax > 0) {  // cells without a keypoint at iniThFAST run again at minThFAST (:1119; ComputeKeyPointsOld: at most 3, :1343)
       __syncthreads();  // the cell flags of phase P3 and the cleared m-map
       const int ln = tid & 31;
-      const u32 retry = __ballot_sync(0xffffffffu, ln < d.nCells && sCellIni[ln] == 0);
+      const u32 retry = __ballot_sync(0xffffffffu, ln < d.nCells && sCellIni[ln] <= S.retryMax);
       if (retry) fast_run_mode(P, S, tMin, true, retry);
     }
     __syncthreads();
@@ -388,9 +425,13 @@ int launch_fast(const Params& P, const TmaMaps& M, int nSlots, cudaStream_t st) 
 // Called once per context (after cudaSetDevice): opts k_fast into its dynamic shared memory and sizes the persistent grid.
 int configure_fast(Params& P) {
   const size_t smem = fast_smem_bytes(P);
-  if (cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return ORBX_ERR_CUDA;
-  int dev = 0, sms = 0, perSm = 0;
+  int dev = 0, sms = 0, perSm = 0, optin = 0;
   if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return ORBX_ERR_CUDA;
+  // the attribute is per function and device, not per context: opt in to the device maximum once, contexts differ in what they ask for
+  if (cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev) != cudaSuccess) return ORBX_ERR_CUDA;
+  optin -= 2048;  // the kernel's static shared memory counts against the same limit
+  if ((size_t)optin < smem) return ORBX_ERR_CUDA;
+  if (cudaFuncSetAttribute(k_fast, cudaFuncAttributeMaxDynamicSharedMemorySize, optin) != cudaSuccess) return ORBX_ERR_CUDA;
   if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, k_fast, kFastThreads, smem) != cudaSuccess || perSm < 1) return ORBX_ERR_CUDA;
   P.fastGrid = sms * perSm;
   return ORBX_OK;

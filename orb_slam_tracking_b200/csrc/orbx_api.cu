@@ -15,6 +15,8 @@ void build_resize_tab(int sw, int sh, int dw, int dh, std::vector<int>& tab);
 int build_geometry(Params& P, const HostTables& T, int fastTileBudget, std::vector<StripDesc>& strips, std::vector<BlurTile>& tiles,
                    std::vector<u8>& rootTab, std::vector<int>& rootEdges);
 int configure_fast(Params& P);
+int build_strips_old(Params& P, const HostTables& T, int fastTileBudget, std::vector<StripDesc>& strips, int& tileMaxOut, int& segWOut,
+                     int& segPOut, int& cellTotal);
 }
 using namespace orbx;
 
@@ -37,7 +39,7 @@ static int dupload(orbx_ctx* c, T** p, const std::vector<T>& v) {
 
 // One u8 tensor map per pyramid level, {x, y, slot}; the driver entry point is taken from the loaded
 // libcuda through the runtime (liborbx.so links cudart statically and does not link libcuda).
-static int build_tensor_maps(orbx_ctx* c) {
+static int build_tensor_maps(orbx_ctx* c, int policy = 0) {
   typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -52,7 +54,7 @@ static int build_tensor_maps(orbx_ctx* c) {
     // that no tested pixel's ring reaches, rows beyond h are zero-filled
     cuuint64_t dims[3] = {(cuuint64_t)(L.pitch / 4), (cuuint64_t)L.h, (cuuint64_t)P.maxBatch};
     cuuint64_t strides[2] = {(cuuint64_t)L.pitch, (cuuint64_t)P.slabBytes};
-    cuuint32_t box[3] = {(cuuint32_t)(L.fastBoxW / 4), (cuuint32_t)L.fastBoxH, 1};
+    cuuint32_t box[3] = {(cuuint32_t)((policy ? L.oBoxW : L.fastBoxW) / 4), (cuuint32_t)(policy ? L.oBoxH : L.fastBoxH), 1};
     cuuint32_t estr[3] = {1, 1, 1};
     CUresult r = ((EncodeFn)fn)(&c->tma.lvl[l], CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, P.pyr + L.imgOff, dims, strides, box, estr,
                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -191,6 +193,9 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   if ((rc = dalloc(c, &c->dIngest, B * (size_t)width * height))) return rc;
   if ((rc = build_tensor_maps(c))) return rc;
   if ((rc = configure_fast(P))) { c->err = "k_fast: shared memory / occupancy configuration failed"; return rc; }
+  c->fastSet[0].strips = P.strips; c->fastSet[0].nStrips = P.nStrips; c->fastSet[0].tileMax = P.fastTileMax;
+  c->fastSet[0].segW = P.fastSegW; c->fastSet[0].segP = P.fastSegP; c->fastSet[0].grid = P.fastGrid; c->fastSet[0].tma = c->tma;
+  c->fastSet[0].ready = 1; c->fastSet[1].ready = 0;
   CU(c, cudaMemset(P.status, 0, B * sizeof(int)));
   CU(c, cudaMemset(P.outN, 0, B * sizeof(int)));
   CU(c, cudaMemset(P.pyr, 0, B * P.slabBytes));
@@ -258,6 +263,42 @@ extern "C" int orbx_set_trig_mode(orbx_ctx* c, int mode) {
   ++c->graphEpoch;
   return ORBX_OK;
 }
+// ComputeKeyPointsOctTree (0, what the reference's operator() calls) or ComputeKeyPointsOld (1, Features/ORBextractor.cpp:1207-1496)
+extern "C" int orbx_set_keypoint_policy(orbx_ctx* c, int policy) {
+  if (!c || (policy != 0 && policy != 1)) return ORBX_ERR_ARG;
+  CU(c, cudaSetDevice(c->device));
+  int rc = drain_flights(c);
+  if (rc) return rc;
+  CU(c, cudaStreamSynchronize(c->stream));
+  Params& P = c->P;
+  orbx_ctx::FastSet& S = c->fastSet[policy];
+  if (!S.ready) {  // first use of ComputeKeyPointsOld: its cell grid, strips, tensor maps and scratch
+    std::vector<StripDesc> strips;
+    int cellTotal = 0;
+    if ((rc = build_strips_old(P, c->T, P.optFastTileBudget, strips, S.tileMax, S.segW, S.segP, cellTotal))) return rc;
+    if (strips.empty()) return ORBX_ERR_ARG;
+    StripDesc* d = nullptr;
+    if ((rc = dupload(c, &d, strips))) return rc;
+    S.strips = d; S.nStrips = (int)strips.size();
+    if ((rc = dalloc(c, &P.oldSorted, (size_t)P.maxBatch * P.candTotal))) return rc;
+    P.oldCellTotal = cellTotal;
+    const TmaMaps keep = c->tma;
+    if ((rc = build_tensor_maps(c, 1))) { c->tma = keep; return rc; }
+    S.tma = c->tma;
+    c->tma = keep;
+    Params Q = P;
+    Q.strips = S.strips; Q.nStrips = S.nStrips; Q.fastTileMax = S.tileMax; Q.fastSegW = S.segW; Q.fastSegP = S.segP;
+    if ((rc = configure_fast(Q))) { c->err = "k_fast: shared memory / occupancy configuration failed"; return rc; }
+    S.grid = Q.fastGrid;
+    S.ready = 1;
+  }
+  P.strips = S.strips; P.nStrips = S.nStrips; P.fastTileMax = S.tileMax; P.fastSegW = S.segW; P.fastSegP = S.segP; P.fastGrid = S.grid;
+  c->tma = S.tma;
+  P.kpPolicy = policy;
+  ++c->graphEpoch;
+  return ORBX_OK;
+}
+
 extern "C" int orbx_set_option(orbx_ctx* c, const char* name, int value) {
   if (!c || !name) return ORBX_ERR_ARG;
   const std::string n(name);

@@ -40,6 +40,7 @@ Params shifted(const orbx_ctx* c, int s0) {
   Q.pyr += s * Q.slabBytes; Q.blur += s * Q.slabBytes;
   Q.candKey += s * Q.candTotal; Q.candXY += s * Q.candTotal; Q.candNode += s * Q.candTotal;
   Q.candCount += s * kMaxLevels;
+  if (Q.oldSorted) Q.oldSorted += s * Q.candTotal;
   Q.nodeBox += s * Q.nodeTotal; Q.nodeCount += s * Q.nodeTotal; Q.nodeSlot += s * Q.nodeTotal; Q.nodeBest += s * Q.nodeTotal;
   Q.nodeAux += 4 * s * Q.nodeTotal; Q.nodeList += s * Q.nodeTotal; Q.nodeScan += s * Q.nodeTotal; Q.nodeSort += s * Q.nodeTotal;
   const size_t k = s * (size_t)Q.kpStride;
@@ -74,7 +75,7 @@ int enqueue_extract(orbx_ctx* c, const Params& P, int n, int lap0, int lap1, cud
     c->launches += launch_blur(P, n, c->sSide[side]);
     CU(c, cudaEventRecord(c->evJoin[side], c->sSide[side]));
   }
-  c->launches += launch_quadtree(P, n, st);
+  c->launches += P.kpPolicy == 1 ? launch_retain_old(P, n, st) : launch_quadtree(P, n, st);
   mark(c, 3);
   if (fork) CU(c, cudaStreamWaitEvent(st, c->evJoin[side], 0));
   else c->launches += launch_blur(P, n, st);
@@ -661,6 +662,42 @@ extern "C" int orbx_set_stage_timing(orbx_ctx* c, int enable) {
 extern "C" int orbx_get_stage_times(orbx_ctx* c, float* ms8) {
   if (!c || !ms8) return ORBX_ERR_ARG;
   std::memcpy(ms8, c->stageMs, sizeof(c->stageMs));
+  return ORBX_OK;
+}
+
+// Copy-only probe of the host link (no kernels): `reps` times the uploads and downloads of one e2e step -- in_bytes from
+// pinned host memory to the device on the H2D stream, out_bytes back on the D2H stream, both directions in flight at
+// once -- timed on the device.  With every rank of a multi-GPU job calling it at the same time it measures the link the
+// ranks share; bench.py reports the e2e step time against it (e2e.host_link_frac).
+extern "C" int orbx_hostlink_probe(orbx_ctx* c, const void* host_in, size_t in_bytes, void* host_out, size_t out_bytes, int reps,
+                                   float* ms_per_rep) {
+  if (!c || !host_in || !host_out || reps < 1 || !ms_per_rep) return ORBX_ERR_ARG;
+  const size_t cap = (size_t)c->P.maxBatch * c->P.W * c->P.H;
+  if (in_bytes > cap || out_bytes > (size_t)c->P.maxBatch * c->P.slabBytes) return ORBX_ERR_ARG;
+  CU(c, cudaSetDevice(c->device));
+  int rc = drain_flights(c);
+  if (rc) return rc;
+  CU(c, cudaStreamSynchronize(c->stream));
+  cudaEvent_t e0, e1, eUp, eDn;
+  CU(c, cudaEventCreate(&e0)); CU(c, cudaEventCreate(&e1));
+  CU(c, cudaEventCreateWithFlags(&eUp, cudaEventDisableTiming)); CU(c, cudaEventCreateWithFlags(&eDn, cudaEventDisableTiming));
+  CU(c, cudaEventRecord(e0, c->stream));
+  CU(c, cudaStreamWaitEvent(c->sH2D, e0, 0));
+  CU(c, cudaStreamWaitEvent(c->sD2H, e0, 0));
+  for (int i = 0; i < reps; ++i) {
+    CU(c, cudaMemcpyAsync(c->dIngest, host_in, in_bytes, cudaMemcpyHostToDevice, c->sH2D));
+    CU(c, cudaMemcpyAsync(host_out, c->P.blur, out_bytes, cudaMemcpyDeviceToHost, c->sD2H));  // any device bytes: only the link is measured
+  }
+  CU(c, cudaEventRecord(eUp, c->sH2D));
+  CU(c, cudaEventRecord(eDn, c->sD2H));
+  CU(c, cudaStreamWaitEvent(c->stream, eUp, 0));
+  CU(c, cudaStreamWaitEvent(c->stream, eDn, 0));
+  CU(c, cudaEventRecord(e1, c->stream));
+  CU(c, cudaEventSynchronize(e1));
+  float ms = 0.f;
+  CU(c, cudaEventElapsedTime(&ms, e0, e1));
+  *ms_per_rep = ms / reps;
+  cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(eUp); cudaEventDestroy(eDn);
   return ORBX_OK;
 }
 

@@ -168,6 +168,65 @@ ORBX_HD void stdsort_emul_t(T* f, long n, Less lt) {
   }
 }
 
+// Reorders f[0..n) exactly as std::nth_element(f, f + nth, f + n, lt) does (GCC 13 bits/stl_algo.h __introselect:
+// median-of-3 partitioning around the nth position until at most 3 elements remain, heap-select after 2*floor(log2 n)
+// rounds, insertion sort of the last range).  cv::KeyPointsFilter::retainBest, which ComputeKeyPointsOld calls per cell
+// and per level (Features/ORBextractor.cpp:1452,1482), keeps the FIRST n elements of that arrangement, so which of the
+// keypoints with tied responses survive, and in which order, is decided here.
+template <class T, class Less>
+ORBX_HD void stdnth_emul_t(T* f, long n, long nth, Less lt) {
+  using namespace ss;
+  if (n <= 0 || nth >= n) return;
+  int lg = 0;
+  for (long t = n; t > 1; t >>= 1) ++lg;
+  long first = 0, last = n;
+  int depth = 2 * lg;
+  while (last - first > 3) {
+    if (depth == 0) {
+      // __heap_select(first, nth + 1, last), then iter_swap(first, nth)
+      T* b = f + first;
+      const long mid = nth + 1 - first, len = last - first;
+      if (mid >= 2) {
+        long parent = (mid - 2) / 2;
+        for (;;) {
+          T v = b[parent];
+          adjust_heap(b, parent, mid, v, lt);
+          if (parent == 0) break;
+          parent--;
+        }
+      }
+      for (long i = mid; i < len; ++i)
+        if (lt(b[i], b[0])) {  // __pop_heap(first, middle, i)
+          T v = b[i];
+          b[i] = b[0];
+          adjust_heap(b, 0, mid, v, lt);
+        }
+      swp(f[first], f[nth]);
+      return;
+    }
+    --depth;
+    const long a = first + 1, b = first + (last - first) / 2, c = last - 1;  // __move_median_to_first(first, first+1, mid, last-1)
+    if (lt(f[a], f[b])) {
+      if (lt(f[b], f[c])) swp(f[first], f[b]);
+      else if (lt(f[a], f[c])) swp(f[first], f[c]);
+      else swp(f[first], f[a]);
+    } else if (lt(f[a], f[c])) swp(f[first], f[a]);
+    else if (lt(f[b], f[c])) swp(f[first], f[c]);
+    else swp(f[first], f[b]);
+    long lo = first + 1, hi = last;  // __unguarded_partition(first+1, last, first)
+    for (;;) {
+      while (lt(f[lo], f[first])) ++lo;
+      --hi;
+      while (lt(f[first], f[hi])) --hi;
+      if (!(lo < hi)) break;
+      swp(f[lo], f[hi]);
+      ++lo;
+    }
+    if (lo <= nth) first = lo; else last = lo;
+  }
+  insertion_sort(f, first, last, lt);
+}
+
 // Sorts f[0..n) exactly as std::sort(f, f + n, [](a, b){ return a.key < b.key; }) does.
 ORBX_HD void stdsort_emul(SortElem* f, long n) { stdsort_emul_t(f, n, ss::KeyLess()); }
 

@@ -176,7 +176,7 @@ int build_geometry(Params& P, const HostTables& T, int fastTileBudget, std::vect
         s.wCell = (short)L.wCell;
         s.sx = (short)(j0 * L.wCell); s.sy = (short)(i * L.hCell);
         s.nIniM1 = 0;  // level fields that are not known yet are filled in below
-        s.tileBytes = L.fastBoxW * L.fastBoxH;
+        s.tileBytes = (L.fastBoxW * L.fastBoxH) | (0 << 24) | (7 << 28);
         s.cellMul = cellMul;
         s.index0 = i * L.nCols + j0;
         s.candOff = 0; s.candCap = 0; s.rootTabOff = 0;
@@ -192,7 +192,7 @@ int build_geometry(Params& P, const HostTables& T, int fastTileBudget, std::vect
       }
     }
     if ((u32)(L.nCols * L.nRows) >= (1u << 18)) return ORBX_ERR_ARG;  // order key has 18 cell bits
-    L.candCap = cap > 0 ? cap : 1;
+    L.candCap = cap + cap / 8 + 64;  // the bound of this grid, with room for the coarser grid of ComputeKeyPointsOld
     L.candOff = candOff;
     candOff += align_up((u32)L.candCap, 32);
     // quadtree roots, :706-739, and the key -> root map, :743-748
@@ -230,6 +230,94 @@ int build_geometry(Params& P, const HostTables& T, int fastTileBudget, std::vect
   P.fastSegW = (listW + 7) & ~7;
   P.fastSegP = (listP + 7) & ~7;
   P.nBlurTiles = (int)tiles.size();
+  return ORBX_OK;
+}
+
+// Strip table of k_fast for ComputeKeyPointsOld's cell grid (Features/ORBextractor.cpp:1222-1330): levelCols x levelRows
+// cells of cellW x cellH tested pixels starting at (19, 19); the last column / row runs to the border; a cell is skipped
+// when nothing is left for it (hX <= 0, :1317-1320).  Same strip rules as above (whole cells, at most 244 tested columns).
+// Fills the o* fields of P.lv[]; returns ORBX_ERR_ARG where the reference itself divides by zero (levelCols == 0) or a
+// cell does not fit one strip.
+int build_strips_old(Params& P, const HostTables& T, int fastTileBudget, std::vector<StripDesc>& strips, int& tileMaxOut, int& segWOut,
+                     int& segPOut, int& cellTotal) {
+  strips.clear();
+  int tileMax = 0, listW = 0, listP = 0;
+  cellTotal = 0;
+  const float imageRatio = (float)P.lv[0].w / (float)P.lv[0].h;  // :1213-1214
+  for (int l = 0; l < P.nlevels; ++l) {
+    LevelInfo& L = P.lv[l];
+    const int nDesired = T.perLevel[l];
+    L.oCols = (int)std::sqrt((float)nDesired / (5 * imageRatio));
+    L.oRows = (int)(imageRatio * L.oCols);
+    if (L.oCols < 1 || L.oRows < 1 || L.oCols * L.oRows > 4096) return ORBX_ERR_ARG;
+    const int minB = kEdge, maxBX = L.w - kEdge, maxBY = L.h - kEdge;
+    const int W = maxBX - minB, H = maxBY - minB;
+    L.oCellW = (int)std::ceil((float)W / L.oCols);
+    L.oCellH = (int)std::ceil((float)H / L.oRows);
+    L.oNfCell = (int)std::ceil((float)nDesired / (L.oCols * L.oRows));
+    if (L.oCellW > 480 || L.oCellH + 6 > 127) return ORBX_ERR_ARG;  // a cell is one strip at least: 9-bit byte columns, 7-bit rows
+    cellTotal += L.oCols * L.oRows;
+    // columns with something to test: ROI [16 + j cellW, 16 + j cellW + hX), hX = cellW + 6 or (last column) w - 16 - iniX
+    int nValid = 0, lastX1 = 0;
+    for (int j = 0; j < L.oCols; ++j) {
+      const int iniX = minB + j * L.oCellW - 3;
+      const int hX = j == L.oCols - 1 ? maxBX + 3 - iniX : L.oCellW + 6;
+      if (hX <= 0) continue;  // only the last column can be skipped
+      if (hX - 6 < 1) continue;  // cv::FAST yields nothing for ROIs under 7 px (the cell stays in the books with 0 keypoints)
+      nValid = j + 1;
+      lastX1 = iniX + hX;
+    }
+    const u32 cellMul = 65535u / (u32)L.oCellW + 1;
+    int nSplit = 1, perStrip = nValid;
+    auto box_w = [&](int nc) {
+      u32 w = align_up((u32)(nc * L.oCellW + 6 + 20), 16);
+      if (((w / 16) & 1) == 0) w += 16;
+      return (int)w;
+    };
+    const int boxH = L.oCellH + 6;
+    for (; nValid > 0; ++nSplit) {
+      perStrip = (nValid + nSplit - 1) / nSplit;
+      if (perStrip <= 1 || (perStrip <= 24 && perStrip * L.oCellW <= 244 && box_w(perStrip) * boxH <= fastTileBudget)) break;
+    }
+    if (nValid > 0 && perStrip * L.oCellW > 480) return ORBX_ERR_ARG;
+    L.oBoxW = box_w(std::max(perStrip, 1));
+    L.oBoxH = boxH;
+    if (L.oBoxW > 508) return ORBX_ERR_ARG;
+    tileMax = std::max(tileMax, L.oBoxW * L.oBoxH);
+    for (int i = 0; i < L.oRows && nValid > 0; ++i) {
+      const int iniY = minB + i * L.oCellH - 3;
+      const int hY = i == L.oRows - 1 ? maxBY + 3 - iniY : L.oCellH + 6;
+      if (hY <= 0) continue;
+      const int ih = hY - 6;
+      if (ih < 1) continue;
+      for (int j0 = 0; j0 < nValid; j0 += perStrip) {
+        const int j1 = std::min(nValid, j0 + perStrip);
+        StripDesc s;
+        const int x0 = minB - 3 + j0 * L.oCellW;
+        const int x1 = j1 == nValid ? lastX1 : minB - 3 + j1 * L.oCellW + 6;
+        const int xs = (x0 - 1) & ~15, off = x0 - xs;
+        s.level = (short)l; s.nCells = (short)(j1 - j0);
+        s.tmaX = (short)(xs >> 2); s.y0 = (short)iniY;
+        s.SB = (short)L.oBoxW;
+        s.bLo = (short)(off + 3); s.bHi = (short)(off + (x1 - x0) - 3);
+        s.nR = (short)ih;
+        s.wCell = (short)L.oCellW;
+        s.sx = (short)(j0 * L.oCellW); s.sy = (short)(i * L.oCellH);
+        s.nIniM1 = (short)(L.nIni - 1);
+        s.tileBytes = (L.oBoxW * L.oBoxH) | (3 << 24) | (9 << 28);
+        s.cellMul = cellMul;
+        s.index0 = i * L.oCols + j0;
+        s.candOff = L.candOff; s.candCap = L.candCap; s.rootTabOff = L.rootTabOff;
+        strips.push_back(s);
+        const int iwS = x1 - x0 - 6, rowsPerWarp = (ih + kFastWarps - 1) / kFastWarps;
+        listW = std::max(listW, rowsPerWarp * (iwS / 4 + 4));
+        listP = std::max(listP, rowsPerWarp * iwS);
+      }
+    }
+  }
+  tileMaxOut = (int)align_up((u32)tileMax, 128);
+  segWOut = (listW + 7) & ~7;
+  segPOut = (listP + 7) & ~7;
   return ORBX_OK;
 }
 

@@ -53,6 +53,10 @@ class ORBextractor:
     def set_trig_mode(self, mode):
         check(lib().orbx_set_trig_mode(self._h, mode), self._h)
 
+    def set_keypoint_policy(self, policy):
+        """0: ComputeKeyPointsOctTree (default), 1: ComputeKeyPointsOld (Features/ORBextractor.cpp:1207-1496)."""
+        check(lib().orbx_set_keypoint_policy(self._h, int(policy)), self._h)
+
     def set_option(self, name, value):
         """Schedule options (orbx_set_option): they never change results."""
         check(lib().orbx_set_option(self._h, name.encode(), int(value)), self._h)

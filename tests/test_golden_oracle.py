@@ -5,7 +5,7 @@ images.  Bit-exact: keypoint records, descriptors, undistorted keys, bounds, gri
 import numpy as np
 import pytest
 
-from golden_util import CASES, Case, same_records
+from golden_util import CASES, LIGHT, Case, LightCase, same_records
 
 
 def test_golden_present():
@@ -54,3 +54,21 @@ def test_demo_pair_headline_counts():
     assert len(c.frame(0)[0]) == 2000 and len(c.frame(1)[0]) == 2000
     assert c.matches(0, 100)[0] == 129
     assert list(c.bounds) == [-78, 857, -61, 543]
+
+
+@pytest.mark.parametrize("name", LIGHT)
+def test_oracle_matches_reference_outputs_large_shapes(oracle, name):
+    """KITTI-shape and 3840x2160 / 8000 keypoints, windows 100 and 8192 (all level-0 pairs)."""
+    c = LightCase(name)
+    E = oracle.Extractor(c.nf, 1.2, 8, 20, 7)
+    bounds = oracle.image_bounds(c.W, c.H, c.K4, c.D4)
+    F = []
+    for i, im in enumerate(c.imgs):
+        k, d, _ = E(im)
+        f = oracle.Frame(k, d, c.K4, c.D4, bounds)
+        c.check_frame(i, k, d, f.keys_un())
+        F.append(f)
+    for w in c.windows:
+        n, m12, _ = oracle.search_for_initialization(F[0], F[1], 0.9, True, w)
+        gn, gm = c.matches(w)
+        assert n == gn and np.array_equal(m12, gm), w

@@ -5,7 +5,7 @@ level tables, keypoint records, descriptors, lapping split, undistorted keys, im
 import numpy as np
 import pytest
 
-from golden_util import CASES, Case, same_records
+from golden_util import CASES, LIGHT, Case, LightCase, same_records
 
 pytestmark = pytest.mark.gpu
 
@@ -88,3 +88,32 @@ def test_color_ingest_matches_cvtcolor():
                 n = int(out["n"][i])
                 assert n == len(k) and same_records(out["kps"][i, :n], k) and np.array_equal(out["desc"][i, :n], d)
         E.close()
+
+
+@pytest.mark.parametrize("name", LIGHT)
+def test_cuda_matches_reference_outputs_large_shapes(name):
+    """BASELINE.json configs[3] / configs[4] against the reference's own outputs: 1241x376 / 2000 and 3840x2160 / 8000
+    keypoints, SearchForInitialization with windows 100 and 8192 (brute force), every matcher path."""
+    from orb_slam_tracking_b200 import frontend as fe
+    c = LightCase(name)
+    E = fe.ORBextractor(c.nf, 1.2, 8, 20, 7, c.W, c.H, max_batch=2)
+    E.set_camera(c.K4, c.D4)
+    F = []
+    for i, im in enumerate(c.imgs):
+        f = fe.Frame(E, im, fused=True)
+        c.check_frame(i, f.mvKeys, f.mDescriptors, f.mvKeysUn)
+        F.append(f)
+    for w in c.windows:
+        gn, gm = c.matches(w)
+        for path in (0, 3, 1):
+            E.set_option("match_path", path)
+            n, m12, _ = fe.ORBmatcher(0.9, True).SearchForInitialization(F[0], F[1], w)
+            assert n == gn and np.array_equal(m12, gm), (w, path)
+    E.set_option("match_path", 0)
+    S = fe.Stream(E, 0.9, True, 8192)
+    S.upload(c.imgs)
+    S.run(2)
+    out = S.download(2)
+    gn, gm = c.matches(8192)
+    assert int(out["nmatches"][0]) == gn and np.array_equal(out["matches12"][0, :len(gm)], gm)
+    E.close()

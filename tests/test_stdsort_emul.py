@@ -12,3 +12,11 @@ def test_stdsort_emul_matches_libstdcxx(tmp_path):
     subprocess.check_call(["g++", "-O2", "-std=c++17", str(ROOT / "tests/csrc/stdsort_check.cpp"), "-o", str(exe)])
     out = subprocess.run([str(exe), "6000"], capture_output=True, text=True)
     assert out.returncode == 0 and out.stdout.strip() == "0", out.stdout + out.stderr
+
+
+def test_stdnth_emul_matches_libstdcxx(tmp_path):
+    """stdnth_emul_t() == std::nth_element with retainBest's comparator (ComputeKeyPointsOld, SURVEY.md 8f N3)."""
+    exe = tmp_path / "stdnth_check"
+    subprocess.check_call(["g++", "-O2", "-std=c++17", str(ROOT / "tests/csrc/stdnth_check.cpp"), "-o", str(exe)])
+    out = subprocess.run([str(exe), "6000"], capture_output=True, text=True)
+    assert out.returncode == 0 and out.stdout.strip() == "0", out.stdout + out.stderr
