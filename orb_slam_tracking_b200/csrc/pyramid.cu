@@ -196,7 +196,9 @@ int launch_pyramid(const Params& P, const int* const* dTabs, int nSlots, cudaStr
   int n = 0;
   for (int l = 1; l < P.nlevels; ++l) {
     dim3 block(32, kResizeWarps);
-    const int rows = P.optResizeRows > 0 ? P.optResizeRows : kResizeRows;
+    // a warp walks its rows one after the other (a dependent chain of loads): with whole batches the SMs are full anyway and
+    // 16 rows per warp amortise the lane constants best; a single frame wants the chain short (its latency is the kernel's)
+    const int rows = P.optResizeRows > 0 ? P.optResizeRows : nSlots >= 64 ? kResizeRows : nSlots >= 8 ? 8 : 4;
     dim3 grid((P.lv[l].w + 127) / 128, (P.lv[l].h + rows * kResizeWarps - 1) / (rows * kResizeWarps), nSlots);
     // taps of 4 adjacent output columns span 3 * scale + 2 source bytes
     if (P.lv[l - 1].w > 2 * P.lv[l].w + 1) k_resize<true><<<grid, block, 0, st>>>(P, l, dTabs[l], rows);

@@ -12,7 +12,8 @@ rows = list(csv.reader(io.StringIO(out)))
 h = [i for i, r in enumerate(rows) if r and r[0] == "Address"][0]
 hdr = rows[h]
 ie, ss, te = hdr.index("Instructions Executed"), hdr.index("# Samples"), hdr.index("Thread Instructions Executed")
-sass = [(r[1], float(r[ie] or 0), float(r[ss] or 0), float(r[te] or 0)) for r in rows[h + 1:] if len(r) > ie]
+end = next((i for i in range(h + 1, len(rows)) if rows[i] and rows[i][0] in ("Kernel Name", "Address")), len(rows))  # first instance only
+sass = [(r[1], float(r[ie] or 0), float(r[ss] or 0), float(r[te] or 0)) for r in rows[h + 1:end] if len(r) > ie]
 d = tempfile.mkdtemp()
 subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(obj)], cwd=d, capture_output=True)
 dis = subprocess.run(["nvdisasm", "-g", "-c", glob.glob(d + "/*.cubin")[0]], capture_output=True, text=True).stdout

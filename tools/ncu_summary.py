@@ -48,8 +48,20 @@ if rep.exists():
         g = per.setdefault(k, {})
         g[r[ig]] = max(g.get(r[ig], 0.0), b)
     traffic = {k: (sum(g.values()) if "k_resize" in k else max(g.values())) for k, g in per.items()}
+    # instruction-issue side of the same launches: warp instructions, issue-slot and pipe utilisation (what bounds the integer kernels)
+    ii, iis = hdr.index("smsp__inst_executed.sum"), hdr.index("smsp__issue_active.avg.pct_of_peak_sustained_active")
+    pipes = {n: hdr.index(c) for n, c in (("alu", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"), ("fma", "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active"),
+                                          ("xu", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active"), ("lsu", "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active")) if c in hdr}
+    issue = {}
+    for r in rr[2:]:
+        k = r[idx[0][0]].split("(")[0]
+        if k in issue and "k_resize" not in k: continue
+        e = issue.setdefault(k, {"warp_instr": 0.0, "issue_active_pct": 0.0, "pipes_pct": {}, "launches": 0})
+        e["warp_instr"] += float(r[ii]); e["launches"] += 1
+        e["issue_active_pct"] = max(e["issue_active_pct"], float(r[iis]))
+        for n, i in pipes.items(): e["pipes_pct"][n] = max(e["pipes_pct"].get(n, 0.0), float(r[i]))
     (P / f"{tag}_traffic.json").write_text(json.dumps({"source": f"ncu --set full, {tag}_full.ncu-rep, dram__bytes_read.sum + dram__bytes_write.sum per launch "
-                                                       "(k_resize: sum over its 7 launches of a step)", "bytes_per_launch": traffic}, indent=1))
+                                                       "(k_resize: sum over its 7 launches of a step)", "bytes_per_launch": traffic, "issue": issue}, indent=1))
     seen = {}
     for r in rr[2:]:
         k = r[idx[0][0]].split("(")[0]
