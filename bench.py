@@ -293,7 +293,8 @@ def run_ours(args, wl):
     assert pair_hi - pair_lo == B // 2
     imgs = synth.tile_frames(B, W, H, unique_pairs=min(16, B // 2), first_pair=pair_lo)
     nbytes_in = imgs.nbytes
-    hp = L.orbx_host_alloc(nbytes_in)
+    wc = bool(os.environ.get("ORBX_BENCH_WC"))   # experiment: write-combined upload buffer (bench-side switch, not a library option)
+    hp = L.orbx_host_alloc_ex(nbytes_in, 1) if wc else L.orbx_host_alloc(nbytes_in)
     assert hp, "pinned allocation failed"
     pinned = np.ctypeslib.as_array(C.cast(hp, C.POINTER(C.c_ubyte)), shape=(nbytes_in,)).reshape(imgs.shape)
     pinned[...] = imgs
@@ -534,7 +535,8 @@ def run_ours(args, wl):
             "config": {"workload": wl["desc"], "frames_per_step_per_gpu": B, "pairs_per_step_per_gpu": B // 2,
                        "nlevels": 8, "scale": 1.2, "fast_th": [wl["ini"], wl["mn"]], "nnratio": NNRATIO, "window": WINDOW,
                        "l2": "batch working set (%.0f MB of pyramids) exceeds the 126 MB L2; no flush" % (2 * B * 1.25 * W * H / 307200),
-                       "sharding": "independent frame pairs per rank, no collective", "host_binding_rank0": binding},
+                       "sharding": "independent frame pairs per rank, no collective", "host_binding_rank0": binding,
+                       "upload_buffer": "pinned, write-combined" if wc else "pinned"},
             "e2e": {"value": fps_e2e, "unit": UNIT, "h2d_bytes_per_step": int(nbytes_in), "d2h_bytes_per_step": int(nbytes_out),
                     "ms_per_step": ms_e2e / args.steps, "api": "orbx_stream_process_async + orbx_stream_wait, 2 steps in flight",
                     "host_link": {"copy_only_ms_per_step": link_ms_step, "frac_of_e2e_step": link_ms_step / (ms_e2e / args.steps),

@@ -133,6 +133,7 @@ int orbx_get_level_keypoints(orbx_ctx* ctx, int slot, int level, orbx_keypoint* 
 /* Copy-only probe of the host link: reps x (in_bytes pinned host -> device, out_bytes device -> pinned host, both
  * directions at once, no kernels); *ms_per_rep = device time of one repetition.  bench.py runs it on every rank at the same
  * time and reports the e2e step against it (e2e.host_link_frac). */
+void* orbx_host_alloc_ex(size_t bytes, int write_combined); /* page-locked; write-combined for upload-only buffers */
 int orbx_hostlink_probe(orbx_ctx* ctx, const void* host_in, size_t in_bytes, void* host_out, size_t out_bytes, int reps,
                         float* ms_per_rep);
 
@@ -226,7 +227,10 @@ int orbx_stream_upload_color(orbx_ctx* ctx, const uint8_t* imgs, int n_img, int 
 /* enqueue the whole pipeline on the context's stream for the first n_img slots; asynchronous */
 int orbx_stream_run(orbx_ctx* ctx, int n_img, float nnratio, int check_orientation, int window_size);
 /* wait, then copy results to the host.  Any pointer may be NULL.  kps/kps_un/desc: blocks of
- * `cap` per frame; matches12: blocks of `cap` per pair; nmatches/counters per pair. */
+ * `cap` per frame; matches12: blocks of `cap` per pair; nmatches/counters per pair.
+ * Rows are copied whole, so `cap` must hold a frame's keypoint capacity (max(nfeatures, sum of the level quotas)):
+ * a smaller `cap` with any of the four array pointers set returns ORBX_ERR_CAPACITY instead of truncating
+ * (also for orbx_stream_process / orbx_stream_process_async). */
 int orbx_stream_download(orbx_ctx* ctx, int n_img, orbx_keypoint* kps, orbx_keypoint* kps_un, uint8_t* desc,
                          int cap, int* n_out, int* matches12, int* nmatches, int* counters3);
 /* compact result of the e2e path: per pair nmatches + matches12 only */

@@ -79,6 +79,7 @@ SIGNATURES = {
     "orbx_last_launch_count": (ci, [vp]),
     "orbx_hostlink_probe": (ci, [vp, vp, sz, vp, sz, ci, vp]),
     "orbx_host_alloc": (vp, [sz]),
+    "orbx_host_alloc_ex": (vp, [sz, ci]),
     "orbx_host_free": (None, [vp]),
     "orbx_get_stream": (vp, [vp]),
 }

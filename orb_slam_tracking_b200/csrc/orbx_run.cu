@@ -454,9 +454,11 @@ extern "C" int orbx_stream_download(orbx_ctx* c, int n_img, orbx_keypoint* kps, 
   cudaStream_t st = c->stream;
   int rc = check_status(c, n_img);
   if (rc) return rc;
+  // rows are copied whole: a row shorter than a frame's keypoint capacity would truncate silently (and matches12 could then
+  // hold indices beyond it), so such a buffer is refused up front
+  if ((kps || kps_un || desc || matches12) && cap < P.kpStride) return ORBX_ERR_CAPACITY;
   const int m = std::min(cap, P.kpStride);
   const size_t w = (size_t)m;
-  if ((kps || kps_un || desc || matches12) && cap < 1) return ORBX_ERR_ARG;
   if (kps)
     CU(c, cudaMemcpy2DAsync(kps, (size_t)cap * sizeof(orbx_keypoint), P.outKp, (size_t)P.kpStride * sizeof(orbx_keypoint),
                             w * sizeof(orbx_keypoint), n_img, cudaMemcpyDeviceToHost, st));
@@ -607,7 +609,7 @@ extern "C" int orbx_stream_process(orbx_ctx* c, const uint8_t* imgs, int n_img, 
                                    int cap, int* n_out, int* matches12, int* nmatches, int* counters3) {
   if (!c || !imgs || n_img < 1 || n_img > c->P.maxBatch) return ORBX_ERR_ARG;
   if (!c->cameraSet) return ORBX_ERR_STATE;
-  if ((kps || kps_un || desc || matches12) && cap < 1) return ORBX_ERR_ARG;
+  if ((kps || kps_un || desc || matches12) && cap < c->P.kpStride) return ORBX_ERR_CAPACITY;  // see orbx_stream_download
   CU(c, cudaSetDevice(c->device));
   int rc = drain_flights(c);
   if (rc) return rc;
@@ -624,7 +626,7 @@ extern "C" int orbx_stream_process_async(orbx_ctx* c, const uint8_t* imgs, int n
                                          int cap, int* n_out, int* matches12, int* nmatches, int* counters3) {
   if (!c || !imgs || n_img < 1 || n_img > c->P.maxBatch) return ORBX_ERR_ARG;
   if (!c->cameraSet) return ORBX_ERR_STATE;
-  if ((kps || kps_un || desc || matches12) && cap < 1) return ORBX_ERR_ARG;
+  if ((kps || kps_un || desc || matches12) && cap < c->P.kpStride) return ORBX_ERR_CAPACITY;
   CU(c, cudaSetDevice(c->device));
   const int ticket = c->nextTicket;
   if (c->flight[ticket].active) return ORBX_ERR_STATE;  // wait for this ticket first
@@ -644,11 +646,13 @@ extern "C" int orbx_stream_wait(orbx_ctx* c, int ticket) {
 // ---- timing ---------------------------------------------------------------------------------------
 extern "C" int orbx_timer_start(orbx_ctx* c) {
   if (!c) return ORBX_ERR_ARG;
+  CU(c, cudaSetDevice(c->device));
   CU(c, cudaEventRecord(c->evStart, c->stream));
   return ORBX_OK;
 }
 extern "C" int orbx_timer_stop(orbx_ctx* c, float* ms) {
   if (!c || !ms) return ORBX_ERR_ARG;
+  CU(c, cudaSetDevice(c->device));
   CU(c, cudaEventRecord(c->evStop, c->stream));
   CU(c, cudaEventSynchronize(c->evStop));
   CU(c, cudaEventElapsedTime(ms, c->evStart, c->evStop));
@@ -705,6 +709,12 @@ extern "C" int orbx_hostlink_probe(orbx_ctx* c, const void* host_in, size_t in_b
 extern "C" void* orbx_host_alloc(size_t bytes) {
   void* p = nullptr;
   return cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) == cudaSuccess ? p : nullptr;
+}
+// write_combined != 0: cudaHostAllocWriteCombined (the CPU only writes the buffer, e.g. frames on their way to the device:
+// the DMA reads need no cache snoop); such a buffer is slow to READ from the CPU
+extern "C" void* orbx_host_alloc_ex(size_t bytes, int write_combined) {
+  void* p = nullptr;
+  return cudaHostAlloc(&p, bytes ? bytes : 1, write_combined ? cudaHostAllocWriteCombined : cudaHostAllocDefault) == cudaSuccess ? p : nullptr;
 }
 extern "C" void orbx_host_free(void* p) {
   if (p) cudaFreeHost(p);

@@ -271,3 +271,24 @@ def test_single_frame_graph_path(fe, oracle, synth):
     F0 = fe.Frame(E, np.full((H, W), 9, np.uint8), fused=True)
     assert F0.N == 0 and F0.grid_offsets[-1] == 0
     E.close()
+
+
+def test_clustered_corners_quadtree_capacity(fe, oracle):
+    """the quadtree's node table is sized from the quota, not from a bound on the nodes ever created.  Tightly
+    clustered candidates split many times while the list grows slowly: a checkerboard patch in one corner of an otherwise
+    flat image (and the same at several scales) must still come out like the reference's, not as ORBX_ERR_CAPACITY."""
+    W, H = 640, 480
+    rng = np.random.default_rng(17)
+    for nf, patch in ((1000, 96), (2000, 160), (500, 48), (1000, 300)):
+        im = np.full((H, W), 120, np.uint8)
+        yy, xx = np.mgrid[0:patch, 0:patch]
+        board = (((xx // 4) + (yy // 4)) & 1).astype(np.uint8) * 110 + 60
+        board = np.clip(board.astype(np.int16) + rng.integers(-6, 7, board.shape), 0, 255).astype(np.uint8)
+        im[30:30 + patch, 40:40 + patch] = board
+        im[H - 60:H - 40, W - 70:W - 40] = 30          # one far-away blob keeps a second root populated
+        E = fe.ORBextractor(nf, 1.2, 8, 20, 7, W, H)
+        R = oracle.Extractor(nf, 1.2, 8, 20, 7)
+        k, d, _ = E(im)
+        rk, rd, _ = R(im)
+        assert len(k) == len(rk) and np.array_equal(k.view(np.uint8), rk.view(np.uint8)) and np.array_equal(d, rd), (nf, patch, len(k), len(rk))
+        E.close()
