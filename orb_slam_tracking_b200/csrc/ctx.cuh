@@ -46,7 +46,8 @@ struct orbx_ctx {
   orbx::u8* dIngest;               // dense [maxBatch][H][W] staging of uploaded frames
   orbx::u8* dIngestColor;          // dense [maxBatch][H][W][3], allocated on the first colour upload
   int* hStatus;                    // pinned [2][maxBatch]: one block per step in flight
-  struct Flight { int active, n, chunk; } flight[2];  // steps of orbx_stream_process_async not yet waited for
+  struct Flight { int active, n, chunk, status; } flight[2];  // steps of orbx_stream_process_async not yet waited for; status: the
+                                                              // step's worst device-side status once it has been drained (0 = ok / not known yet)
   cudaEvent_t evDone[2];
   int nextTicket;
   std::vector<void*> allocs;       // every cudaMalloc, freed in orbx_destroy

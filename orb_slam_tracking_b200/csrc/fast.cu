@@ -227,20 +227,36 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
     nP = n2 + __popc(b3);
   }
   __syncwarp();
-  // ---- phase P2: exact segment-test value of the surviving pixels (ring offsets in cv::FAST order) ----
+  // ---- phase P2: exact segment-test value of the surviving pixels (ring offsets in cv::FAST order).  The pixel list is
+  // compacted IN PLACE to the corners (m > t; a chunk's survivors land at or before the chunk): only they own an m-map entry,
+  // so only they take part in the maximum search and in the clearing ----
   const u8* sImg = reinterpret_cast<const u8*>(S.imgW);
-  for (int i = lane; i < nP; i += 32) {
-    const int e = S.segP[i], ry = e >> 9, b = e & 511;
-    const u8* p = sImg + ry * SB + b;
-    const u32 vb = ((256u - (u32)p[0]) << 16) | ((u32)p[0] + 256u);
-    u32 x[16];
-    x[0] = ring_pack(vb, p[3 * SB]); x[1] = ring_pack(vb, p[3 * SB + 1]); x[2] = ring_pack(vb, p[2 * SB + 2]); x[3] = ring_pack(vb, p[SB + 3]);
-    x[4] = ring_pack(vb, p[3]); x[5] = ring_pack(vb, p[-SB + 3]); x[6] = ring_pack(vb, p[-2 * SB + 2]); x[7] = ring_pack(vb, p[-3 * SB + 1]);
-    x[8] = ring_pack(vb, p[-3 * SB]); x[9] = ring_pack(vb, p[-3 * SB - 1]); x[10] = ring_pack(vb, p[-2 * SB - 2]); x[11] = ring_pack(vb, p[-SB - 3]);
-    x[12] = ring_pack(vb, p[-3]); x[13] = ring_pack(vb, p[SB - 3]); x[14] = ring_pack(vb, p[2 * SB - 2]); x[15] = ring_pack(vb, p[3 * SB - 1]);
-    const int m = arc_value(x);
-    if (m > t) S.mm[ry * SB + b] = (u8)m;
+  int nC = 0;
+  for (int i0 = 0; i0 < nP; i0 += 32) {
+    const int i = i0 + lane;
+    bool corner = false;
+    unsigned short e16 = 0;
+    if (i < nP) {
+      e16 = S.segP[i];
+      const int e = e16, ry = e >> 9, b = e & 511;
+      const u8* p = sImg + ry * SB + b;
+      const u32 vb = ((256u - (u32)p[0]) << 16) | ((u32)p[0] + 256u);
+      u32 x[16];
+      x[0] = ring_pack(vb, p[3 * SB]); x[1] = ring_pack(vb, p[3 * SB + 1]); x[2] = ring_pack(vb, p[2 * SB + 2]); x[3] = ring_pack(vb, p[SB + 3]);
+      x[4] = ring_pack(vb, p[3]); x[5] = ring_pack(vb, p[-SB + 3]); x[6] = ring_pack(vb, p[-2 * SB + 2]); x[7] = ring_pack(vb, p[-3 * SB + 1]);
+      x[8] = ring_pack(vb, p[-3 * SB]); x[9] = ring_pack(vb, p[-3 * SB - 1]); x[10] = ring_pack(vb, p[-2 * SB - 2]); x[11] = ring_pack(vb, p[-SB - 3]);
+      x[12] = ring_pack(vb, p[-3]); x[13] = ring_pack(vb, p[SB - 3]); x[14] = ring_pack(vb, p[2 * SB - 2]); x[15] = ring_pack(vb, p[3 * SB - 1]);
+      const int m = arc_value(x);
+      corner = m > t;
+      if (corner) S.mm[ry * SB + b] = (u8)m;
+    }
+    const u32 bc = __ballot_sync(0xffffffffu, corner);
+    __syncwarp();
+    if (corner) S.segP[nC + __popc(bc & lt)] = e16;
+    nC += __popc(bc);
+    __syncwarp();
   }
+  nP = nC;
   __syncthreads();
   // ---- phase P3: strict 3x3 maxima inside the pixel's own cell (branch-free: 60 % of the listed pixels are corners) ----
   int nK = 0;

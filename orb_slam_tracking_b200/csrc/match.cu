@@ -197,7 +197,7 @@ constexpr int kChunkQ = 128;            // queries per chunk (segment table size
 constexpr u32 kInvalid = 0xffffffffu;   // entry of a cell-rectangle key outside the window
 
 struct MatchSmem {  // byte offsets into dynamic shared memory
-  int off0, cx, cy, ci, md, m21, q, bin, ent, total;
+  int off0, cx, cy, ci, md, m21, q, bin, touch, ent, total;
   int entCap;
 };
 __host__ __device__ inline MatchSmem match_smem_layout(int stride) {
@@ -212,6 +212,7 @@ __host__ __device__ inline MatchSmem match_smem_layout(int stride) {
   L.m21 = take(stride * 2);
   L.q = take(stride * 2);
   L.bin = take(stride);
+  L.touch = take(stride * 4);
   L.entCap = stride > 8192 ? stride : 8192;
   L.ent = take(L.entCap * 4);
   L.total = o;
@@ -236,6 +237,7 @@ __global__ void __launch_bounds__(MT) k_match_cta(const __grid_constant__ Params
   unsigned short* const sM21 = reinterpret_cast<unsigned short*>(dsm + LY.m21);
   unsigned short* const sQ = reinterpret_cast<unsigned short*>(dsm + LY.q);
   u8* const sBin = dsm + LY.bin;
+  u32* const sTouch = reinterpret_cast<u32*>(dsm + LY.touch);  // per key of F2: the first query (lane) of the running batch that takes it
   u32* const sEnt = reinterpret_cast<u32*>(dsm + LY.ent);
 
   const int pair = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -250,7 +252,7 @@ __global__ void __launch_bounds__(MT) k_match_cta(const __grid_constant__ Params
   int* m12 = A.matches12 + (size_t)pair * A.stride;
 
   for (int i = tid; i < n1; i += MT) m12[i] = -1;
-  for (int i = tid; i < n2; i += MT) { sMD[i] = 0xffffu; sM21[i] = 0xffffu; }
+  for (int i = tid; i < n2; i += MT) { sMD[i] = 0xffffu; sM21[i] = 0xffffu; sTouch[i] = 0xffffffffu; }
   if (tid < HISTO_LENGTH) sHist[tid] = 0;
 
   // ---- S1: level-0 CSR of F2 (thread t owns cells [12 t, 12 t + 12)) ----
@@ -411,12 +413,19 @@ __global__ void __launch_bounds__(MT) k_match_cta(const __grid_constant__ Params
       __syncwarp();
     }
     __syncthreads();
-    // (d) the reference loop over the chunk's queries, in order (:36-117), by warp 0
+    // (d) the reference loop over the chunk's queries, in order (:36-117), by warp 0 -- 32 queries at a time.
+    // A query's outcome depends on the earlier ones only through vMatchedDistance (:67): an earlier match to key c changes it
+    // only if c is one of the query's two best unskipped candidates.  So every lane first decides ITS query against the
+    // state at the start of the batch (its own candidates, in order); a lane whose best or second-best key is taken by an
+    // earlier lane of the batch is in conflict.  All lanes before the first conflict commit together (their keys are
+    // distinct); the conflicting query is then decided again against the current state by the whole warp (the reference's
+    // loop body, below), and the rest of the batch is checked again.  The result is the ordered loop's, query for query.
     if (warp == 0) {
-      for (int qi = 0; qi < nq; ++qi) {
+      // the reference's loop body for one query, lanes over its candidates; returns the matched key of F2 or -1
+      auto resolve_one = [&](int qi) -> int {
         const int segB = sSeg[qi], segN = sSeg[qi + 1] - segB;
-        if (segN == 0) continue;  // vIndices2.empty(), :46
-        u32 key = kNone;          // (best distance << 20) | visiting position
+        if (segN == 0) return -1;  // vIndices2.empty(), :46
+        u32 key = kNone;           // (best distance << 20) | visiting position
         int bidx = -1, bd2 = INT_MAX, found = 0;
         for (int t = lane; t < segN; t += 32) {
           const u32 en = sEnt[segB + t];
@@ -430,15 +439,15 @@ __global__ void __launch_bounds__(MT) k_match_cta(const __grid_constant__ Params
             key = k; bidx = i2;
           } else if (dist < bd2) bd2 = dist;
         }
-        if (!__any_sync(0xffffffffu, found)) continue;  // no key of the rectangle is inside the window
+        if (!__any_sync(0xffffffffu, found)) return -1;  // no key of the rectangle is inside the window
         const u32 best = __reduce_min_sync(0xffffffffu, key);
         const int winner = __ffs((int)__ballot_sync(0xffffffffu, key == best)) - 1;
         const int bestDist = best == kNone ? INT_MAX : (int)(best >> 20);
         const int mine2 = (lane == winner) ? bd2 : (key == kNone ? INT_MAX : (int)(key >> 20));
         const int bestDist2 = (int)__reduce_min_sync(0xffffffffu, (u32)mine2);
         const int bestIdx = __shfl_sync(0xffffffffu, bidx, winner);
-        if (bestDist > TH_LOW) { ++badDist; continue; }                                        // :82
-        if ((float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) { ++badRatio; continue; }  // :87
+        if (bestDist > TH_LOW) { ++badDist; return -1; }                                        // :82
+        if ((float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) { ++badRatio; return -1; }  // :87
         const int prev = sM21[bestIdx] == 0xffffu ? -1 : (int)sM21[bestIdx];
         if (prev >= 0) --nmatches;  // :95-98
         ++nmatches;
@@ -458,6 +467,81 @@ __global__ void __launch_bounds__(MT) k_match_cta(const __grid_constant__ Params
             sHist[bin] += 1;
           }
         }
+        __syncwarp();
+        return bestIdx;
+      };
+      for (int qb = 0; qb < nq; qb += 32) {
+        const int qi = qb + lane;
+        int segB = 0, segN = 0;
+        if (qi < nq) { segB = sSeg[qi]; segN = sSeg[qi + 1] - segB; }
+        // every lane: its own query against the state at the start of the batch
+        int best = INT_MAX, best2 = INT_MAX, bidx = -1, bidx2 = -1;
+        bool found = false;
+        const int maxN = (int)__reduce_max_sync(0xffffffffu, (u32)segN);
+        for (int t = 0; t < maxN; ++t) {
+          if (t < segN) {
+            const u32 en = sEnt[segB + t];
+            if (en != kInvalid) {
+              found = true;
+              const int dist = (int)(en >> 16), i2 = (int)(en & 0xffffu);
+              if (!((int)sMD[i2] <= dist)) {  // :67
+                if (dist < best) { best2 = best; bidx2 = bidx; best = dist; bidx = i2; }  // :70-76, strict <: the first minimum stays
+                else if (dist < best2) { best2 = dist; bidx2 = i2; }
+              }
+            }
+          }
+        }
+        const bool bad = best > TH_LOW;                                                    // :82 (also "every candidate skipped")
+        const bool ratio = !bad && (float)best > __fmul_rn(nnratio, (float)best2);        // :87
+        u32 pend = __ballot_sync(0xffffffffu, found);
+        int myTouch = -1;
+        while (pend) {
+          const bool mine = (pend >> lane) & 1u;
+          const bool isMatch = mine && !bad && !ratio;
+          if (isMatch) atomicMin(&sTouch[bidx], (u32)lane);
+          __syncwarp();
+          // a query that fails on distance cannot be rescued by a skipped candidate (its best can only get worse)
+          const bool conf = mine && !bad && (sTouch[bidx] < (u32)lane || (bidx2 >= 0 && sTouch[bidx2] < (u32)lane));
+          const u32 cm = __ballot_sync(0xffffffffu, conf);
+          const int f = cm ? __ffs((int)cm) - 1 : 32;
+          const u32 commit = f >= 32 ? pend : pend & ((1u << f) - 1u);
+          const bool doCommit = (commit >> lane) & 1u;
+          __syncwarp();
+          if (isMatch && !doCommit && sTouch[bidx] == (u32)lane) sTouch[bidx] = 0xffffffffu;  // tentative claims are withdrawn
+          int prev = -1;
+          if (doCommit && isMatch) {
+            prev = sM21[bidx] == 0xffffu ? -1 : (int)sM21[bidx];
+            const int i1 = sQ[qs + qi];
+            if (prev >= 0) m12[prev] = -1;  // :95-98
+            m12[i1] = bidx;
+            sM21[bidx] = (unsigned short)i1;
+            sMD[bidx] = (unsigned short)best;
+            myTouch = bidx;
+            if (checkOri) {
+              float rot = k1[i1].angle - k2[bidx].angle;
+              if (rot < 0.0f) rot = rot + 360.0f;
+              int bin = (int)roundf(__fmul_rn(rot, factor));
+              if (bin == HISTO_LENGTH) bin = 0;
+              sBin[qs + qi] = (u8)bin;
+              atomicAdd(&sHist[bin], 1);
+            }
+          }
+          badDist += __popc(__ballot_sync(0xffffffffu, doCommit && bad));
+          badRatio += __popc(__ballot_sync(0xffffffffu, doCommit && ratio));
+          nmatches += __popc(__ballot_sync(0xffffffffu, doCommit && isMatch)) - __popc(__ballot_sync(0xffffffffu, prev >= 0));
+          pend &= ~commit;
+          __syncwarp();
+          if (f < 32) {
+            const int got = resolve_one(qb + f);
+            if (got >= 0) {
+              if (lane == 0) atomicMin(&sTouch[got], (u32)f);
+              if (lane == f) myTouch = got;
+            }
+            pend &= ~(1u << f);
+            __syncwarp();
+          }
+        }
+        if (myTouch >= 0) sTouch[myTouch] = 0xffffffffu;
         __syncwarp();
       }
     }

@@ -211,7 +211,7 @@ extern "C" orbx_ctx* orbx_create(int device, int width, int height, int nfeature
   c->stream = nullptr; c->sH2D = c->sD2H = nullptr;
   for (int i = 0; i < orbx_ctx::kLanes; ++i) { c->sLane[i] = c->sSide[i] = nullptr; c->evFork[i] = c->evJoin[i] = c->evLane[i] = nullptr; }
   c->dIngest = nullptr; c->dIngestColor = nullptr; c->hStatus = nullptr; c->hTabPtrs = nullptr; c->launches = 0; c->cameraSet = 0; c->lastBatch = 0; c->dScore = nullptr; c->scoreBytes = 0;
-  for (int i = 0; i < 2; ++i) { c->flight[i].active = 0; c->flight[i].n = 0; c->flight[i].chunk = 0; c->evDone[i] = nullptr; }
+  for (int i = 0; i < 2; ++i) { c->flight[i].active = 0; c->flight[i].n = 0; c->flight[i].chunk = 0; c->flight[i].status = 0; c->evDone[i] = nullptr; }
   c->nextTicket = 0;
   for (int i = 0; i < 2; ++i) { c->fg[i].exec = nullptr; c->fg[i].epoch = -1; }
   c->graphEpoch = 0; c->hFrameIn = nullptr; c->hFrameOut = nullptr;

@@ -9,17 +9,18 @@
 using namespace orbx;
 
 // Waits for every step of orbx_stream_process_async still in flight (entry points that touch the slot arrays call it
-// first).  Returns the worst device-side status of those steps.
+// first).  A device-side error of a drained step is NOT this call's result: it is kept with the step's ticket, and
+// orbx_stream_wait(ticket) reports it -- the caller that drains is usually issuing an unrelated request.
 int drain_flights(orbx_ctx* c) {
-  int worst = 0;
   for (int t = 0; t < 2; ++t) {
     if (!c->flight[t].active) continue;
     CU(c, cudaEventSynchronize(c->evDone[t]));
     c->flight[t].active = 0;
+    int worst = 0;
     for (int i = 0; i < c->flight[t].n; ++i) worst = std::min(worst, c->hStatus[(size_t)t * c->P.maxBatch + i]);
+    c->flight[t].status = worst;
   }
-  if (worst) c->err = "device-side status " + std::to_string(worst);
-  return worst;
+  return ORBX_OK;
 }
 
 namespace {
@@ -370,6 +371,7 @@ extern "C" int orbx_stream_upload(orbx_ctx* c, const uint8_t* imgs, int n_img) {
   if (!c || !imgs || n_img < 1 || n_img > c->P.maxBatch) return ORBX_ERR_ARG;
   const Params& P = c->P;
   CU(c, cudaSetDevice(c->device));
+  { const int rc = drain_flights(c); if (rc) return rc; }  // ends a chain of asynchronous steps (see process_enqueue)
   // one DMA for the whole batch into the dense staging buffer, then level 0 of every slot on the device
   CU(c, cudaMemcpyAsync(c->dIngest, imgs, (size_t)n_img * P.W * P.H, cudaMemcpyHostToDevice, c->stream));
   launch_ingest(P, c->dIngest, n_img, c->stream);
@@ -382,6 +384,7 @@ extern "C" int orbx_stream_upload_color(orbx_ctx* c, const uint8_t* imgs, int n_
   if (!c || !imgs || n_img < 1 || n_img > c->P.maxBatch) return ORBX_ERR_ARG;
   const Params& P = c->P;
   CU(c, cudaSetDevice(c->device));
+  { const int rc = drain_flights(c); if (rc) return rc; }
   if (!c->dIngestColor) {
     void* q = nullptr;
     CU(c, cudaMalloc(&q, (size_t)P.maxBatch * P.W * P.H * 3));
@@ -401,6 +404,7 @@ extern "C" int orbx_stream_run(orbx_ctx* c, int n_img, float nnratio, int check_
   CU(c, cudaSetDevice(c->device));
   c->launches = 0;
   int rc;
+  if ((rc = drain_flights(c))) return rc;
   const int parts = std::min(orbx_ctx::kLanes, std::max(1, P.optRunParts > 0 ? P.optRunParts : 2));
   if (n_img >= 64 * parts && parts > 1 && !c->stageTiming && !P.optSingleStream) {
     // the batch in `parts` pieces (each a whole number of pairs), one per compute lane: the latency-bound kernels of
@@ -531,7 +535,9 @@ int process_enqueue(orbx_ctx* c, const uint8_t* imgs, int n_img, float nnratio, 
   const int lane0 = streaming ? 1 : 0;
   const int lanes = std::min(orbx_ctx::kLanes - lane0, std::max(1, lanesEnv > 0 ? lanesEnv : 3));
   int rc = ORBX_OK;
-  if (!chained) {  // whatever the caller enqueued on the context's stream (orbx_stream_run ...) comes first
+  if (!chained) {  // whatever the caller enqueued on the context's stream (orbx_stream_run ...) comes first.  A chained step needs no
+                   // fence: every other entry point that enqueues on the context's stream drains the steps in flight first, so
+                   // nothing can sit between two chained steps
     CU(c, cudaEventRecord(c->evLane[0], c->stream));
     for (int i = 0; i < lanes; ++i)
       if (lane0 + i) CU(c, cudaStreamWaitEvent(c->sLane[lane0 + i], c->evLane[0], 0));
@@ -584,14 +590,19 @@ int process_enqueue(orbx_ctx* c, const uint8_t* imgs, int n_img, float nnratio, 
   // The context's stream (lane 0) joins it, so work enqueued on it later -- and orbx_timer_stop -- comes after the step.
   CU(c, cudaEventRecord(c->evDone[ticket], c->sD2H));
   CU(c, cudaStreamWaitEvent(c->stream, c->evDone[ticket], 0));
-  c->flight[ticket].active = 1; c->flight[ticket].n = n_img; c->flight[ticket].chunk = chunk;
+  c->flight[ticket].active = 1; c->flight[ticket].n = n_img; c->flight[ticket].chunk = chunk; c->flight[ticket].status = 0;
   if (rc) { drain_flights(c); return rc; }
   c->lastBatch = n_img;
   return ORBX_OK;
 }
 
 int wait_ticket(orbx_ctx* c, int ticket) {
-  if (!c->flight[ticket].active) return ORBX_OK;
+  if (!c->flight[ticket].active) {  // already drained by another call: its status was kept for this one
+    const int st = c->flight[ticket].status;
+    c->flight[ticket].status = 0;
+    if (st) c->err = "device-side status " + std::to_string(st);
+    return st;
+  }
   CU(c, cudaEventSynchronize(c->evDone[ticket]));
   c->flight[ticket].active = 0;
   CU(c, cudaGetLastError());

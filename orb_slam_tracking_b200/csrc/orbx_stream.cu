@@ -75,6 +75,7 @@ extern "C" int orbx_frame_glue(orbx_ctx* c, const orbx_keypoint* kps, int n, orb
   const Params& P = c->P;
   if (n > P.kpStride) return ORBX_ERR_CAPACITY;
   CU(c, cudaSetDevice(c->device));
+  { const int rc = drain_flights(c); if (rc) return rc; }
   cudaStream_t st = c->stream;
   // slot 0 of the frame store is the staging area of this call
   if (n) CU(c, cudaMemcpyAsync(P.outKp, kps, (size_t)n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, st));
@@ -115,8 +116,9 @@ extern "C" int orbx_features_in_area(orbx_ctx* c, const orbx_frame* F, float x, 
   if (!c || !F || cap < 0 || (cap > 0 && !out)) return ORBX_ERR_ARG;
   if (!c->cameraSet) return ORBX_ERR_STATE;
   CU(c, cudaSetDevice(c->device));
-  int rc = stage_frame(c, F, 0);
+  int rc = drain_flights(c);
   if (rc) return rc;
+  if ((rc = stage_frame(c, F, 0))) return rc;
   const int dcap = std::min(cap, c->hfCap);
   launch_features_in_area(c->P, c->hfKeys, c->hfGridOff, c->hfGridIdx, x, y, r, min_level, max_level, c->hfMatches,
                           dcap, c->hfNMatches, c->stream);
@@ -167,8 +169,9 @@ extern "C" int orbx_search_for_initialization(orbx_ctx* c, const orbx_frame* F1,
   if (!c || !F1 || !F2) return ORBX_ERR_ARG;
   if (!c->cameraSet) return ORBX_ERR_STATE;
   CU(c, cudaSetDevice(c->device));
-  int rc = stage_frame(c, F1, 0);
+  int rc = drain_flights(c);
   if (rc) return rc;
+  if ((rc = stage_frame(c, F1, 0))) return rc;
   if ((rc = stage_frame(c, F2, 1))) return rc;
   MatchArgs A;
   A.keysUn = c->hfKeys; A.desc = c->hfDesc; A.gridOff = c->hfGridOff; A.gridIdx = c->hfGridIdx; A.n = c->hfN;
