@@ -189,7 +189,8 @@ __global__ void __launch_bounds__(32) k_bf_resolve(const __grid_constant__ Param
   const int nC = B.counts[pair * 4 + 0], nQ = B.counts[pair * 4 + 1];
   unsigned short* const sMD = reinterpret_cast<unsigned short*>(dsm);   // vMatchedDistance (0xffff = INT_MAX; distances are <= 256)
   unsigned short* const sM21 = sMD + A.stride;                           // vnMatches21 (0xffff = -1)
-  u8* const sBin = reinterpret_cast<u8*>(sM21 + A.stride);               // rotation bin of query position q (0xff = none)
+  u32* const sTouch = reinterpret_cast<u32*>(sM21 + A.stride);           // per key of F2: the first query (lane) of the running batch that takes it
+  u8* const sBin = reinterpret_cast<u8*>(sTouch + A.stride);             // rotation bin of query position q (0xff = none)
   const orbx_keypoint* __restrict__ k1 = A.keysUn + (size_t)s1 * A.stride;
   const orbx_keypoint* __restrict__ k2 = A.keysUn + (size_t)s2 * A.stride;
   const u8* __restrict__ d1 = A.desc + (size_t)s1 * A.stride * 32;
@@ -200,7 +201,7 @@ __global__ void __launch_bounds__(32) k_bf_resolve(const __grid_constant__ Param
   const u32* __restrict__ topk = B.topk + (size_t)pair * A.stride * (kBfK + 1);
   int* m12 = A.matches12 + (size_t)pair * A.stride;
   for (int i = lane; i < n1; i += 32) m12[i] = -1;
-  for (int i = lane; i < n2; i += 32) { sMD[i] = 0xffffu; sM21[i] = 0xffffu; }
+  for (int i = lane; i < n2; i += 32) { sMD[i] = 0xffffu; sM21[i] = 0xffffu; sTouch[i] = 0xffffffffu; }
   for (int i = lane; i < nQ; i += 32) sBin[i] = 0xff;
   if (lane < HISTO_LENGTH) sHist[lane] = 0;
   __syncwarp();
@@ -208,39 +209,13 @@ __global__ void __launch_bounds__(32) k_bf_resolve(const __grid_constant__ Param
   const float factor = (float)HISTO_LENGTH / 360.0f;
   int nmatches = 0, badDist = 0, badRatio = 0;
 
-  for (int qb = 0; qb < nQ; qb += 32) {
-    {  // stage the batch
-      const int q = qb + lane;
-      u32 w[8] = {kNoKey, kNoKey, kNoKey, kNoKey, kNoKey, kNoKey, kNoKey, 0u};
-      int i1 = 0;
-      if (q < nQ) {
-        const uint4 lo = __ldg(reinterpret_cast<const uint4*>(topk + (size_t)q * 8)), hi = __ldg(reinterpret_cast<const uint4*>(topk + (size_t)q * 8) + 1);
-        w[0] = lo.x; w[1] = lo.y; w[2] = lo.z; w[3] = lo.w; w[4] = hi.x; w[5] = hi.y; w[6] = hi.z; w[7] = hi.w;
-        i1 = __ldg(qIdx + q);
-      }
-      const int nList = (int)(w[7] >> 24);
-#pragma unroll
-      for (int j = 0; j < kBfK; ++j) {
-        u32 e = kNoKey;
-        float ang = 0.f;
-        if (j < nList) {
-          const int i2 = (int)(__ldg(cand + (w[j] & 0xfffffu)) & 0xffffu);
-          e = ((w[j] >> 20) << 16) | (u32)i2;
-          ang = k2[i2].angle;
-        }
-        sEnt[lane][j] = e;
-        sAng[lane][j] = ang;
-      }
-      sEnt[lane][7] = w[7];
-      sAng[lane][7] = q < nQ ? k1[i1].angle : 0.f;
-      sI1[lane] = i1;
-    }
-    __syncwarp();
-    const int nb = min(32, nQ - qb);
-    for (int qi = 0; qi < nb; ++qi) {
+  int qb = 0;
+  // the reference's loop body for query qi of the staged batch against the current state, lanes over its list (and, when
+  // the list runs out, over all candidates); returns the matched key of F2 or -1
+  auto resolve_one = [&](int qi) -> int {
       const u32 info = sEnt[qi][7];
       const int nCand = (int)(info & 0xfffffu), nList = (int)(info >> 24);
-      if (nCand == 0) continue;  // vIndices2.empty(), :46
+      if (nCand == 0) return -1;  // vIndices2.empty(), :46
       // lane j < nList: is list entry j skipped by :67 ?
       u32 e = kNoKey;
       bool ok = false;
@@ -291,8 +266,8 @@ __global__ void __launch_bounds__(32) k_bf_resolve(const __grid_constant__ Param
         bestIdx = __shfl_sync(0xffffffffu, bidx, winner);
         if (bestIdx >= 0) ang2 = k2[bestIdx].angle;
       }
-      if (bestDist > TH_LOW) { ++badDist; continue; }                                        // :82
-      if ((float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) { ++badRatio; continue; }  // :87
+      if (bestDist > TH_LOW) { ++badDist; return -1; }                                        // :82
+      if ((float)bestDist > __fmul_rn(nnratio, (float)bestDist2)) { ++badRatio; return -1; }  // :87
       const int prev = sM21[bestIdx] == 0xffffu ? -1 : (int)sM21[bestIdx];
       if (prev >= 0) --nmatches;  // :95-98
       ++nmatches;
@@ -312,6 +287,107 @@ __global__ void __launch_bounds__(32) k_bf_resolve(const __grid_constant__ Param
         }
       }
       __syncwarp();
+      return bestIdx;
+  };
+
+  for (qb = 0; qb < nQ; qb += 32) {
+    {  // stage the batch
+      const int q = qb + lane;
+      u32 w[8] = {kNoKey, kNoKey, kNoKey, kNoKey, kNoKey, kNoKey, kNoKey, 0u};
+      int i1 = 0;
+      if (q < nQ) {
+        const uint4 lo = __ldg(reinterpret_cast<const uint4*>(topk + (size_t)q * 8)), hi = __ldg(reinterpret_cast<const uint4*>(topk + (size_t)q * 8) + 1);
+        w[0] = lo.x; w[1] = lo.y; w[2] = lo.z; w[3] = lo.w; w[4] = hi.x; w[5] = hi.y; w[6] = hi.z; w[7] = hi.w;
+        i1 = __ldg(qIdx + q);
+      }
+      const int nList = (int)(w[7] >> 24);
+#pragma unroll
+      for (int j = 0; j < kBfK; ++j) {
+        u32 e = kNoKey;
+        float ang = 0.f;
+        if (j < nList) {
+          const int i2 = (int)(__ldg(cand + (w[j] & 0xfffffu)) & 0xffffu);
+          e = ((w[j] >> 20) << 16) | (u32)i2;
+          ang = k2[i2].angle;
+        }
+        sEnt[lane][j] = e;
+        sAng[lane][j] = ang;
+      }
+      sEnt[lane][7] = w[7];
+      sAng[lane][7] = q < nQ ? k1[i1].angle : 0.f;
+      sI1[lane] = i1;
+    }
+    __syncwarp();
+    // Every lane decides ITS query of the batch from its list against the state at the start of the batch; a lane whose best
+    // or second-best key is taken by an earlier lane of the batch, or whose list runs out, is decided again by the whole warp
+    // (resolve_one) once every lane before it has committed.  See k_match_cta, phase (d): same argument, same result as the
+    // reference's ordered loop.
+    {
+      const u32 info = sEnt[lane][7];
+      const int nCand = (int)(info & 0xfffffu), nList = (int)(info >> 24);
+      int best = INT_MAX, best2 = INT_MAX, bidx = -1, bidx2 = -1, j0 = 0;
+#pragma unroll
+      for (int j = 0; j < kBfK; ++j) {
+        if (j < nList) {
+          const u32 e = sEnt[lane][j];
+          const int dist = (int)(e >> 16), i2 = (int)(e & 0xffffu);
+          if (!((int)sMD[i2] <= dist)) {  // :67; the list is sorted (distance, visiting position)
+            if (bidx < 0) { best = dist; bidx = i2; j0 = j; }
+            else if (bidx2 < 0) { best2 = dist; bidx2 = i2; }
+          }
+        }
+      }
+      const bool hard = bidx2 < 0 && nList < nCand;  // the list ran out before the candidates did
+      const bool bad = best > TH_LOW;
+      const bool ratio = !bad && (float)best > __fmul_rn(nnratio, (float)best2);
+      u32 pend = __ballot_sync(0xffffffffu, qb + lane < nQ && nCand > 0);
+      int myTouch = -1;
+      while (pend) {
+        const bool mine = (pend >> lane) & 1u;
+        const bool isMatch = mine && !hard && !bad && !ratio;
+        if (isMatch) atomicMin(&sTouch[bidx], (u32)lane);
+        __syncwarp();
+        const bool conf = mine && (hard || (!bad && (sTouch[bidx] < (u32)lane || (bidx2 >= 0 && sTouch[bidx2] < (u32)lane))));
+        const u32 cm = __ballot_sync(0xffffffffu, conf);
+        const int f = cm ? __ffs((int)cm) - 1 : 32;
+        const u32 commit = f >= 32 ? pend : pend & ((1u << f) - 1u);
+        const bool doCommit = (commit >> lane) & 1u;
+        __syncwarp();
+        if (isMatch && !doCommit && sTouch[bidx] == (u32)lane) sTouch[bidx] = 0xffffffffu;  // tentative claims are withdrawn
+        int prev = -1;
+        if (doCommit && isMatch) {
+          prev = sM21[bidx] == 0xffffu ? -1 : (int)sM21[bidx];
+          const int i1 = sI1[lane];
+          if (prev >= 0) m12[prev] = -1;  // :95-98
+          m12[i1] = bidx;
+          sM21[bidx] = (unsigned short)i1;
+          sMD[bidx] = (unsigned short)best;
+          myTouch = bidx;
+          if (checkOri) {
+            float rot = sAng[lane][7] - sAng[lane][j0];
+            if (rot < 0.0f) rot = rot + 360.0f;
+            int bin = (int)roundf(__fmul_rn(rot, factor));
+            if (bin == HISTO_LENGTH) bin = 0;
+            sBin[qb + lane] = (u8)bin;
+            atomicAdd(&sHist[bin], 1);
+          }
+        }
+        badDist += __popc(__ballot_sync(0xffffffffu, doCommit && bad));
+        badRatio += __popc(__ballot_sync(0xffffffffu, doCommit && ratio));
+        nmatches += __popc(__ballot_sync(0xffffffffu, doCommit && isMatch)) - __popc(__ballot_sync(0xffffffffu, prev >= 0));
+        pend &= ~commit;
+        __syncwarp();
+        if (f < 32) {
+          const int got = resolve_one(f);
+          if (got >= 0) {
+            if (lane == 0) atomicMin(&sTouch[got], (u32)f);
+            if (lane == f) myTouch = got;
+          }
+          pend &= ~(1u << f);
+          __syncwarp();
+        }
+      }
+      if (myTouch >= 0) sTouch[myTouch] = 0xffffffffu;
     }
     __syncwarp();
   }
@@ -336,7 +412,7 @@ __global__ void __launch_bounds__(32) k_bf_resolve(const __grid_constant__ Param
   }
 }
 
-size_t bf_resolve_smem(int stride) { return (size_t)stride * 5 + 16; }
+size_t bf_resolve_smem(int stride) { return (size_t)stride * 9 + 16; }
 
 int launch_match_bf(const Params& P, const MatchArgs& A, const BfScratch& B, int nPairs, int pairStep, float nnratio, int checkOri,
                     int window, cudaStream_t st) {
