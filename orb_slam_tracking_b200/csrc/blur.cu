@@ -8,10 +8,11 @@
 // (+ halo out of L2), writes P_l.  One WARP per strip of 120 columns x 64 rows, no shared memory:
 // lane = one aligned 32-bit word (4 columns) of the 128 staged columns x0-4 .. x0+123; lanes 1..30 produce
 // output, lanes 0 and 31 only carry the halo.  Walking down the rows, a lane loads its word (rows are
-// fetched 7 at a time so that the loads of a block are in flight together), takes the neighbouring words
+// fetched kRB = 10 at a time so that the loads of a block are in flight together), takes the neighbouring words
 // from the adjacent lanes by shuffle, runs the row pass with funnel shifts and dp4a, and keeps the last 7
 // row-pass results of its 4 columns in registers for the column pass (rows paired in 16-bit halves:
-// 3 dp2a + 1 multiply-add per pixel).  BORDER_REFLECT_101 in x costs nothing in the loop: a word that touches or
+// 3 dp2a + 1 multiply-add per pixel; the window of five row pairs is a ring whose position is a compile-time constant
+// because the row block is a multiple of five rows: no register moves).  BORDER_REFLECT_101 in x costs nothing in the loop: a word that touches or
 // lies beyond the level's border is a lane-constant byte permutation of two aligned words inside the level.
 #include "common.cuh"
 
@@ -19,6 +20,8 @@ namespace orbx {
 
 constexpr int kTW = 120, kTH = 64;
 constexpr int kBlurWarps = 4;
+constexpr int kRB = 10;  // rows per block of loads: a multiple of the 5-deep pair ring, and (kTH + 6) % kRB == 0
+static_assert((kTH + 6) % kRB == 0 && kRB % 5 == 0, "row block");
 
 __global__ void __launch_bounds__(kBlurWarps * 32) k_blur(const __grid_constant__ Params P) {
   const int lane = threadIdx.x & 31;
@@ -58,21 +61,33 @@ __global__ void __launch_bounds__(kBlurWarps * 32) k_blur(const __grid_constant_
   for (int k = 0; k < 5; ++k) { pr[k][0] = pr[k][1] = pr[k][2] = pr[k][3] = 0; }
   hl[0] = hl[1] = hl[2] = hl[3] = 0;
   const u8* __restrict__ colp = src + A;
-  for (int rb = 0; rb < kTH + 6; rb += 7) {
+  for (int rb = 0; rb < kTH + 6; rb += kRB) {
     if (t.y0 + rb - 6 >= L.h) break;  // nothing left to emit in this strip
-    u32 v0[7], v1[7];
+    u32 v0[kRB], v1[kRB];
+    const int yb = t.y0 + rb - 3;
+    if (yb >= 0 && yb + kRB <= L.h) {  // all rows of the block inside the level: one pointer walks down
+      const u8* rp = colp + yb * L.pitch;
 #pragma unroll
-    for (int k = 0; k < 7; ++k) {
-      int y = t.y0 + rb + k - 3;
-      y = y < 0 ? -y : y;
-      y = y >= L.h ? 2 * (L.h - 1) - y : y;
-      y = max(y, 0);  // rows beyond the halo of the last strip are never used
-      const u32* rp = reinterpret_cast<const u32*>(colp + y * L.pitch);
-      v0[k] = __ldg(rp);
-      v1[k] = two ? __ldg(rp + 1) : 0u;
+      for (int k = 0; k < kRB; ++k, rp += L.pitch) {
+        v0[k] = __ldg(reinterpret_cast<const u32*>(rp));
+        v1[k] = two ? __ldg(reinterpret_cast<const u32*>(rp) + 1) : 0u;
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < kRB; ++k) {
+        int y = yb + k;
+        y = y < 0 ? -y : y;
+        y = y >= L.h ? 2 * (L.h - 1) - y : y;
+        y = max(y, 0);  // rows beyond the halo of the last strip are never used
+        const u32* rp = reinterpret_cast<const u32*>(colp + y * L.pitch);
+        v0[k] = __ldg(rp);
+        v1[k] = two ? __ldg(rp + 1) : 0u;
+      }
     }
+    const int nEmit = emit ? L.h - (t.y0 + rb - 6) : 0;  // rows k < nEmit of the block are inside the level
+    u8* dp = dst + (t.y0 + rb - 6) * L.pitch + xw;
 #pragma unroll
-    for (int k = 0; k < 7; ++k) {
+    for (int k = 0; k < kRB; ++k) {
       const u32 w1 = __byte_perm(v0[k], v1[k], S);
       const u32 w0 = __shfl_up_sync(0xffffffffu, w1, 1);
       const u32 w2 = __shfl_down_sync(0xffffffffu, w1, 1);
@@ -82,24 +97,22 @@ __global__ void __launch_bounds__(kBlurWarps * 32) k_blur(const __grid_constant_
       const u32 n2 = __dp4a(__funnelshift_r(w0, w1, 24), kA, __dp4a(__funnelshift_r(w1, w2, 24), kB, 0u));
       const u32 n3 = __dp4a(w1, kA, __dp4a(w2, kB, 0u));
       const u32 nn[4] = {n0, n1, n2, n3};
-      const int yo = t.y0 + rb + k - 6;
       u32 px[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        // rows 0..6 of the window = pr[0] (0,1), pr[2] (2,3), pr[4] (4,5) and the new row
+        // rows 0..6 of the window = ring entries 0 (rows 0,1), 2 (2,3), 4 (4,5) and the new row; entry i is pr[(i + k) % 5]
         u32 v;
-        asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(v) : "r"(pr[0][j]), "r"(kT01), "r"(18u * nn[j] + 32768u));
-        asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(v) : "r"(pr[2][j]), "r"(kT23), "r"(v));
-        asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(v) : "r"(pr[4][j]), "r"(kT45), "r"(v));
+        asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(v) : "r"(pr[k % 5][j]), "r"(kT01), "r"(18u * nn[j] + 32768u));
+        asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(v) : "r"(pr[(k + 2) % 5][j]), "r"(kT23), "r"(v));
+        asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(v) : "r"(pr[(k + 4) % 5][j]), "r"(kT45), "r"(v));
         px[j] = v;  // < 2^24: the output pixel is byte 2
-        const u32 pn = __byte_perm(hl[j], nn[j], 0x5410);  // (previous row, new row)
-        pr[0][j] = pr[1][j]; pr[1][j] = pr[2][j]; pr[2][j] = pr[3][j]; pr[3][j] = pr[4][j]; pr[4][j] = pn;
+        pr[k % 5][j] = __byte_perm(hl[j], nn[j], 0x5410);  // (previous row, new row) replaces the oldest pair
         hl[j] = nn[j];
       }
-      if (emit && rb + k >= 6 && yo < L.h) {
-        *reinterpret_cast<u32*>(dst + yo * L.pitch + xw) =
-            __byte_perm(__byte_perm(px[0], px[1], 0x0062), __byte_perm(px[2], px[3], 0x0062), 0x5410);
+      if (k < nEmit && (k >= 6 || rb > 0)) {
+        *reinterpret_cast<u32*>(dp) = __byte_perm(__byte_perm(px[0], px[1], 0x0062), __byte_perm(px[2], px[3], 0x0062), 0x5410);
       }
+      dp += L.pitch;
     }
   }
 }
