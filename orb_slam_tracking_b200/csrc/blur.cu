@@ -18,9 +18,15 @@
 
 namespace orbx {
 
-constexpr int kTW = 120, kTH = 64;
-constexpr int kBlurWarps = 4;
-constexpr int kRB = 10;  // rows per block of loads: a multiple of the 5-deep pair ring, and (kTH + 6) % kRB == 0
+constexpr int kTW = kBlurTW, kTH = kBlurTH;
+#ifndef ORBX_BLUR_WARPS
+#define ORBX_BLUR_WARPS 4
+#endif
+#ifndef ORBX_BLUR_RB
+#define ORBX_BLUR_RB 10
+#endif
+constexpr int kBlurWarps = ORBX_BLUR_WARPS;
+constexpr int kRB = ORBX_BLUR_RB;  // rows per block of loads: a multiple of the 5-deep pair ring, and (kTH + 6) % kRB == 0
 static_assert((kTH + 6) % kRB == 0 && kRB % 5 == 0, "row block");
 
 __global__ void __launch_bounds__(kBlurWarps * 32) k_blur(const __grid_constant__ Params P) {

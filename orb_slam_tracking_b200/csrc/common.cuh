@@ -30,6 +30,10 @@ constexpr int kHalfPatch = 15;  // HALF_PATCH_SIZE, :74
 constexpr int kPatch = 31;      // PATCH_SIZE, :72
 constexpr int kMinBorder = 16;  // EDGE_THRESHOLD - 3, :1056
 constexpr int kGridCols = ORBX_GRID_COLS, kGridRows = ORBX_GRID_ROWS, kGridCells = ORBX_GRID_CELLS;
+#ifndef ORBX_BLUR_TH
+#define ORBX_BLUR_TH 124
+#endif
+constexpr int kBlurTW = 120, kBlurTH = ORBX_BLUR_TH;  // k_blur: output columns x rows per warp strip
 constexpr int kFastWarps = 8;   // warps of a k_fast CTA (its per-warp list segments are sized on the host)
 constexpr int kMaxCellDim = 80;  // cell ROI (wCell + 6) is < 76 for every image size
 

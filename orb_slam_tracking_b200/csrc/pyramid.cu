@@ -21,7 +21,7 @@ namespace orbx {
 
 constexpr int kResizeRows = 16, kResizeWarps = 4;
 
-// tab: xofs[dw] | xcoef[dw] (a0 | a1 << 16) | yofs[dh] | ycoef[dh] (b0 | b1 << 16)
+// tab: xofs[dw] | xcoef[dw] (a0 | a1 << 16) | per output row { r0 | r1 << 16, b0 | b1 << 16 }
 template <bool WIDE>
 __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_constant__ Params P, int l, const int* __restrict__ tab, int rows) {
   const LevelInfo& D = P.lv[l];
@@ -34,8 +34,7 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
   u8* dst = level_ptr(P.pyr, P, slot, l);
   const int* xofs = tab;
   const int* xcoef = tab + D.w;
-  const int* yofs = tab + 2 * D.w;
-  const int* ycoef = yofs + D.h;
+  const int2* __restrict__ ytab = reinterpret_cast<const int2*>(tab + 2 * D.w);  // the table base is 256-byte aligned
   // lane constants
   int a0[4], a1[4], e0[4], e1[4];
   u32 acoef[4], sel[4];
@@ -75,13 +74,11 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
     }
   };
 
-  u32 hPrev[4] = {0, 0, 0, 0};
-  int rPrev = -1;
   const int dyEnd = min(dy0 + rows, D.h);
   {
     // the strip's source rows are consumed one after the other (a dependent chain of loads per lane): pull its
     // 128-byte lines into L2 up front, one line per lane and round
-    const int rFirst = min(max(__ldg(yofs + dy0), 0), S.h - 1), rLast = min(max(__ldg(yofs + dyEnd - 1) + 1, 0), S.h - 1);
+    const int rFirst = __ldg(&ytab[dy0].x) & 0xffff, rLast = (int)((u32)__ldg(&ytab[dyEnd - 1].x) >> 16);
     const int xb = __shfl_sync(0xffffffffu, sx0, 0) & ~127;
     const int nLines = (min(__shfl_sync(0xffffffffu, sx0 + e1[3], 31), S.pitch - 1) - xb) / 128 + 1;
     const int total = (rLast - rFirst + 1) * nLines;
@@ -90,34 +87,35 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
       asm volatile("prefetch.global.L2 [%0];" ::"l"(src + (size_t)(rFirst + r) * S.pitch + xb + 128 * ln));
     }
   }
-  for (int dy = dy0; dy < dyEnd; ++dy) {
-    const int sy = __ldg(yofs + dy), bc = __ldg(ycoef + dy);
+  // Output row dy from the horizontally interpolated source rows r0, r1.  At scale 1.2 row r1 of dy is row r0 of dy + 1 five
+  // times out of six, so the rows alternate between two register sets (hHave holds row rHave on entry, hNew row r1 on exit;
+  // the caller swaps the roles: no register moves).
+  int rHave = -1;
+  u8* dp = dst + (size_t)dy0 * D.pitch + dx0;  // pitch is a multiple of 128, so the 4-pixel group is always inside the row allocation
+  const bool emit = dx0 < D.w;
+  auto out_row = [&](int dy, u32 (&hHave)[4], u32 (&hNew)[4]) {
+    const int2 yt = __ldg(ytab + dy);
+    const int r0 = yt.x & 0xffff, r1 = (int)((u32)yt.x >> 16);
     // (b * h) >> 16 == umulhi(b << 16, h): coefficients are in [0, 2048], h < 2^15
-    const u32 B0 = (u32)(bc & 0xffff) << 16, B1 = (u32)bc & 0xffff0000u;
-    const int r0 = min(max(sy, 0), S.h - 1), r1 = min(max(sy + 1, 0), S.h - 1);
-    u32 h0[4], h1[4];
-    if (r0 == rPrev) {
+    const u32 B0 = (u32)yt.y << 16, B1 = (u32)yt.y & 0xffff0000u;
+    if (r0 != rHave) hrow(r0, hHave);
+    if (r1 != r0) hrow(r1, hNew);
+    else {
 #pragma unroll
-      for (int k = 0; k < 4; ++k) h0[k] = hPrev[k];
-    } else {
-      hrow(r0, h0);
+      for (int k = 0; k < 4; ++k) hNew[k] = hHave[k];
     }
-    if (r1 == r0) {
+    u32 v[4];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) h1[k] = h0[k];
-    } else {
-      hrow(r1, h1);
-    }
-    u32 packed = 0;
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const u32 v = (__umulhi(B0, h0[k]) + __umulhi(B1, h1[k]) + 2u) >> 2;
-      packed |= (v & 0xffu) << (8 * k);
-      hPrev[k] = h1[k];
-    }
-    rPrev = r1;
-    // pitch is a multiple of 128, so the 4-pixel group is always inside the row allocation
-    if (dx0 < D.w) *reinterpret_cast<u32*>(dst + dy * D.pitch + dx0) = packed;
+    for (int k = 0; k < 4; ++k) v[k] = (__umulhi(B0, hHave[k]) + __umulhi(B1, hNew[k]) + 2u) >> 2;  // <= 255
+    if (emit) *reinterpret_cast<u32*>(dp) = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
+    dp += D.pitch;
+    rHave = r1;
+  };
+  u32 hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0};
+  for (int dy = dy0; dy < dyEnd; dy += 2) {
+    out_row(dy, hA, hB);
+    if (dy + 1 >= dyEnd) break;
+    out_row(dy + 1, hB, hA);
   }
 }
 

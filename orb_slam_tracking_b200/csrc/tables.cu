@@ -58,7 +58,8 @@ int compute_tables(int nfeatures, float scaleFactorF, int nlevels, HostTables& t
   return ORBX_OK;
 }
 
-// cv::resize INTER_LINEAR 8U coefficient tables.  Layout: xofs | xcoef | yofs | ycoef.
+// cv::resize INTER_LINEAR 8U coefficient tables.  Layout: xofs[dw] | xcoef[dw] | { r0 | r1 << 16, ycoef }[dh]:
+// the two source rows of an output row already clipped to [0, sh - 1] like OpenCV's row loop does at use.
 void build_resize_tab(int sw, int sh, int dw, int dh, std::vector<int>& tab) {
   tab.assign(2 * (size_t)dw + 2 * (size_t)dh, 0);
   const double sxs = 1. / ((double)dw / sw), sys = 1. / ((double)dh / sh);
@@ -77,8 +78,9 @@ void build_resize_tab(int sw, int sh, int dw, int dh, std::vector<int>& tab) {
     const int s = cv_floor_f(f);
     f -= s;
     const int b0 = cv_round_f((1.f - f) * 2048.f), b1 = cv_round_f(f * 2048.f);
-    tab[2 * dw + d] = s;  // clipped to [0, sh-1] at use, like OpenCV's row loop
-    tab[2 * dw + dh + d] = (b0 & 0xffff) | (b1 << 16);
+    const int r0 = std::min(std::max(s, 0), sh - 1), r1 = std::min(std::max(s + 1, 0), sh - 1);
+    tab[2 * dw + 2 * d] = r0 | (r1 << 16);
+    tab[2 * dw + 2 * d + 1] = (b0 & 0xffff) | (b1 << 16);
   }
 }
 
@@ -215,8 +217,8 @@ int build_geometry(Params& P, const HostTables& T, int fastTileBudget, std::vect
       if (sd.level == l) { sd.nIniM1 = (short)(L.nIni - 1); sd.candOff = L.candOff; sd.candCap = L.candCap; sd.rootTabOff = L.rootTabOff; }
     nodeOff += align_up((u32)L.nodeCap, 32);
     // blur strips of 120 x 64 (one warp each)
-    for (int y = 0; y < L.h; y += 64)
-      for (int x = 0; x < L.w; x += 120) {
+    for (int y = 0; y < L.h; y += kBlurTH)
+      for (int x = 0; x < L.w; x += kBlurTW) {
         BlurTile t;
         t.level = (short)l; t.pad = 0; t.x0 = (short)x; t.y0 = (short)y;
         tiles.push_back(t);

@@ -32,7 +32,7 @@ assert len(lines) == len(sass), (len(lines), len(sass))
 text = open(src).read().splitlines()
 marks = [(i + 1, re.search(r"// ---- phase (\S+)", l).group(1)) for i, l in enumerate(text) if "// ---- phase " in l]
 base = os.path.basename(src)
-first = marks[0][0]
+first = marks[0][0] if marks else 1 << 30
 def phase_of(ln):
     p = None
     for a, n in marks:
