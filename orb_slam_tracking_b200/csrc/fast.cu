@@ -38,7 +38,10 @@ constexpr int kFastThreads = 32 * kFastWarps;
 #define ORBX_FAST_STAGES 2
 #endif
 constexpr int kFastStages = ORBX_FAST_STAGES;  // tile buffers of the ring
-constexpr int kFastCtasPerSm = kFastStages == 1 ? 4 : 3;   // register cap: 65536 / (3 * 256) = 85
+#ifndef ORBX_FAST_CTAS
+#define ORBX_FAST_CTAS (ORBX_FAST_STAGES == 1 ? 4 : 3)
+#endif
+constexpr int kFastCtasPerSm = ORBX_FAST_CTAS;   // register cap: 65536 / (3 * 256) = 85
 
 // m(p) for one pixel.  Both polarities ride in one register per ring position: e_k = v - p_k + 256 in the
 // low half-word and 512 - e_k = p_k - v + 256 in the high one, so the min-of-9 / max-of-16 ladder below

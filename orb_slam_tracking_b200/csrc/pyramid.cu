@@ -91,23 +91,20 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
   // times out of six, so the rows alternate between two register sets (hHave holds row rHave on entry, hNew row r1 on exit;
   // the caller swaps the roles: no register moves).
   int rHave = -1;
-  u8* dp = dst + (size_t)dy0 * D.pitch + dx0;  // pitch is a multiple of 128, so the 4-pixel group is always inside the row allocation
-  const bool emit = dx0 < D.w;
+  // pitch = width rounded up to 128 and a warp covers 128 columns: every lane's 4-pixel group is inside the row allocation,
+  // lanes beyond the level's width write row padding that nothing reads
+  u8* dp = dst + (size_t)dy0 * D.pitch + dx0;
   auto out_row = [&](int dy, u32 (&hHave)[4], u32 (&hNew)[4]) {
     const int2 yt = __ldg(ytab + dy);
     const int r0 = yt.x & 0xffff, r1 = (int)((u32)yt.x >> 16);
     // (b * h) >> 16 == umulhi(b << 16, h): coefficients are in [0, 2048], h < 2^15
     const u32 B0 = (u32)yt.y << 16, B1 = (u32)yt.y & 0xffff0000u;
     if (r0 != rHave) hrow(r0, hHave);
-    if (r1 != r0) hrow(r1, hNew);
-    else {
-#pragma unroll
-      for (int k = 0; k < 4; ++k) hNew[k] = hHave[k];
-    }
+    hrow(r1, hNew);  // r1 == r0 only where the row loop clips (never when shrinking): the row is simply interpolated again
     u32 v[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) v[k] = (__umulhi(B0, hHave[k]) + __umulhi(B1, hNew[k]) + 2u) >> 2;  // <= 255
-    if (emit) *reinterpret_cast<u32*>(dp) = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
+    *reinterpret_cast<u32*>(dp) = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
     dp += D.pitch;
     rHave = r1;
   };
