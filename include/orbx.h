@@ -166,6 +166,20 @@ int orbx_match_resolve(orbx_ctx* ctx, const orbx_frame* F1, const orbx_frame* F2
  * pointers may be NULL.  kernel_ms (may be NULL): device time of one pass, averaged over `repeats` passes. */
 int orbx_hamming_best2(orbx_ctx* ctx, const uint8_t* a, int n_a, const uint8_t* b, int n_b, int* best_idx, int* best_dist,
                        int* second_dist, int repeats, float* kernel_ms);
+/* The same result for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid allocation).  No counterpart in the reference.
+ * d_a, d_b and the three outputs (each may be NULL) are DEVICE pointers on the context's device; `stream` is a
+ * cudaStream_t (NULL = the context's stream); synchronize != 0 waits for the stream before returning, otherwise the two
+ * kernels are only enqueued.  The call allocates nothing: the per-query table (8 words per query) lives in a fixed
+ * device array inside the library, ORBX_NOALLOC_MAX_QUERIES rows = 512 KiB, held by every GPU that loads the library
+ * until the process exits.  n_a beyond that limit returns ORBX_ERR_CAPACITY (text in orbx_last_error); split the
+ * queries or use orbx_hamming_best2.  Every call on a GPU shares the array (it keeps the previous call's rows; each
+ * call overwrites the rows it reads, nothing needs clearing): calls that overlap on the GPU race on it -- keep them on
+ * one stream or order them with events.  The first call per device looks up the array's device address
+ * (cudaGetSymbolAddress); make that call outside stream capture. */
+#define ORBX_NOALLOC_MAX_QUERIES 16384
+int orbx_hamming_best2_noalloc(orbx_ctx* ctx, const uint8_t* d_a, int n_a, const uint8_t* d_b, int n_b, int* d_best_idx,
+                               int* d_best_dist, int* d_second_dist, void* stream, int synchronize);
 
 /* ---- Frame glue ---------------------------------------------------------------------------- */
 /* K4 = fx, fy, cx, cy; dist4 = k1, k2, p1, p2 (float32, as the reference's CV_32F matrices).

@@ -15,7 +15,7 @@ CSRC = PKG / "csrc"
 OBJ = PKG / "build"
 LIB = PKG / "liborbx.so"
 SOURCES = ["pyramid.cu", "blur.cu", "fast.cu", "quadtree.cu", "retain_old.cu", "describe.cu", "glue.cu", "match.cu", "match_bf.cu", "score.cu", "tables.cu",
-           "orbx_api.cu", "orbx_run.cu", "orbx_stream.cu"]
+           "orbx_api.cu", "orbx_run.cu", "orbx_stream.cu", "no_alloc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = (os.environ.get("ORBX_NVCC_EXTRA", "").split()) + ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-fmad=false",
          "-prec-div=true", "-prec-sqrt=true", "-ftz=false", "-Xcompiler", "-fPIC,-O2,-Wall", "-Xptxas", "-v"]

@@ -59,6 +59,7 @@ SIGNATURES = {
     "orbx_match_rows": (ci, [vp, vp, vp, ci, ci, ci, vp, vp]),
     "orbx_match_resolve": (ci, [vp, vp, vp, cf, ci, ci, vp, ci, vp, vp, vp]),
     "orbx_hamming_best2": (ci, [vp, vp, ci, vp, ci, vp, vp, vp, ci, vp]),
+    "orbx_hamming_best2_noalloc": (ci, [vp, vp, ci, vp, ci, vp, vp, vp, vp, ci]),
     "orbx_descriptor_distance": (ci, [vp, vp]),
     "orbx_descriptor_distance_batch": (ci, [vp, vp, vp, ci, vp]),
     "orbx_check_homography": (ci, [vp, vp, ci, vp, ci, vp, vp, vp, ci, cf, vp, vp, vp, vp]),
