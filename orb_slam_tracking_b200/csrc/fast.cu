@@ -34,6 +34,9 @@
 namespace orbx {
 
 constexpr int kFastThreads = 32 * kFastWarps;
+#ifndef ORBX_FAST_BC
+#define ORBX_FAST_BC 2  // pair tests of phase BC: 2 = all six, 1 = the two on rows +-3 only, 0 = none (every pixel that passes phase A gets the exact value)
+#endif
 #ifndef ORBX_FAST_STAGES
 #define ORBX_FAST_STAGES 2
 #endif
@@ -208,13 +211,17 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
       alive = e & 0x80808080u;
       const int g = e & 0x7f;
       const u32* r0 = S.imgW + ((e >> 8) & 0x7f) * SW;
+#if ORBX_FAST_BC >= 1
       const Row3 rm3 = load3(r0 - 3 * SW, g), r00 = load3(r0, g), rp3 = load3(r0 + 3 * SW, g);
       const u32 cc = r00.c;
       alive &= any_gt<MODE>(__vabsdiffu4(cc, word_at<1>(rp3.l, rp3.c, rp3.r)), __vabsdiffu4(cc, word_at<-1>(rm3.l, rm3.c, rm3.r)), K);
       alive &= any_gt<MODE>(__vabsdiffu4(cc, word_at<1>(rm3.l, rm3.c, rm3.r)), __vabsdiffu4(cc, word_at<-1>(rp3.l, rp3.c, rp3.r)), K);
-      if (alive) {
+#endif
+      if (ORBX_FAST_BC >= 2 && alive) {
+#if ORBX_FAST_BC >= 2
         const Row3 rm2 = load3(r0 - 2 * SW, g), rm1 = load3(r0 - SW, g), rp1 = load3(r0 + SW, g), rp2 = load3(r0 + 2 * SW, g);
         alive = pairs_rows_1_2<MODE>(alive, cc, rm2, rm1, rp1, rp2, K);
+#endif
       }
     }
     __syncwarp();
