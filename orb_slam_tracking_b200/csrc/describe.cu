@@ -49,7 +49,7 @@ constexpr int kPatchRows = 37, kPatchWords = 10;  // blurred patch [-18, 18]^2 s
 //      coalesced word loads, then lane = descriptor byte gathers its 16 samples from shared memory.
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 6) k_describe(const __grid_constant__ Params P) {
   __shared__ float4 sPat[256];  // pattern pair (x0, y0, x1, y1) as floats, [i * 32 + byte]: conflict-free for lane = byte
-  __shared__ u32 sDD[32];       // per patch row: 0x80808080 | umax[|v|] * 0x01010101 (byte-wise column limit of IC_Angle)
+  __shared__ u32 sMask[4][31 * 9];  // IC_Angle's disc as byte masks: [x & 3][row][word], 0xff where |u| <= umax[|v|]
   __shared__ u32 sPatch[kWarpsPerCta][kPatchRows * kPatchWords];
   __shared__ float sAngle[kKpPerCta], sCos[kKpPerCta], sSin[kKpPerCta];
   __shared__ u32 sXY[kKpPerCta];
@@ -59,7 +59,15 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 6) k_describe(const __grid_
     const int b = tid & 31, i = tid >> 5;  // 256 threads: pair (b, i) -> pattern row 8b + i
     const signed char* p = c_pattern + 4 * (8 * b + i);
     sPat[i * 32 + b] = make_float4((float)p[0], (float)p[1], (float)p[2], (float)p[3]);
-    if (tid < 31) sDD[tid] = 0x80808080u | ((u32)P.umax[tid < kHalfPatch ? kHalfPatch - tid : tid - kHalfPatch] * 0x01010101u);
+    // word w of a row starts at column offset u = 4 w - 15 - ((x + 1) & 3) from the keypoint (x - 15 = xa + ((x + 1) & 3))
+    for (int i = tid; i < 4 * 31 * 9; i += kWarpsPerCta * 32) {
+      const int a = i / (31 * 9), rw = i - a * (31 * 9), r = rw / 9, w = rw - 9 * r;
+      const int d = P.umax[r < kHalfPatch ? kHalfPatch - r : r - kHalfPatch], u0 = 4 * w - kHalfPatch - ((a + 1) & 3);
+      u32 m = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) m |= (abs(u0 + j) <= d ? 0xffu : 0u) << (8 * j);
+      sMask[a][rw] = m;
+    }
   }
   const int slot = blockIdx.y;
   const int gBase = blockIdx.x * kKpPerCta;
@@ -93,23 +101,23 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 6) k_describe(const __grid_
     // and only the row's half-width d = umax[|v|] changes: byte j counts iff |u_j| <= d
     const int lr = lane / 9, w = lane - 9 * lr;
     const int u0 = xa + 4 * w - x;
-    // |u_j| per byte (< 128); byte j of a row counts iff umax >= |u_j|: bit 7 of (0x80 | umax) - |u_j| survives
-    const u32 apk = (u32)abs(u0) | ((u32)abs(u0 + 1) << 8) | ((u32)abs(u0 + 2) << 16) | ((u32)abs(u0 + 3) << 24);
     const int upk = (u0 & 255) | (((u0 + 1) & 255) << 8) | (((u0 + 2) & 255) << 16) | (((u0 + 3) & 255) << 24);  // s8 x 4
     if (lane < 27) {
+      // m01 = sum over rows of (r - 15) * rowsum with r = rb + lr: T = sum of the bytes, U = sum of rb * bytes (rb is a
+      // compile-time byte), m01 = U + (lr - 15) * T
+      const u32* const mk = &sMask[x & 3][9 * lr + w];
+      const u8* const ip = img + (size_t)lr * L.pitch + 4 * w;
+      u32 T = 0, U = 0;
 #pragma unroll
       for (int rb = 0; rb < 33; rb += 3) {
-        const int r = rb + lr;
-        if (r < 31) {
-          const int v = r - kHalfPatch;
-          u32 word = __ldg(reinterpret_cast<const u32*>(img + (size_t)r * L.pitch) + w);
-          word &= (((sDD[r] - apk) & 0x80808080u) >> 7) * 255u;
-          int su;
-          asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(su) : "r"(word), "r"(upk), "r"(0));
-          m10 += su;
-          m01 += v * (int)__dp4a(word, 0x01010101u, 0u);
+        if (rb + lr < 31) {
+          const u32 word = __ldg(reinterpret_cast<const u32*>(ip + (size_t)rb * L.pitch)) & mk[9 * rb];
+          asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(m10) : "r"(word), "r"(upk), "r"(m10));
+          T = __dp4a(word, 0x01010101u, T);
+          U = __dp4a(word, (u32)rb * 0x01010101u, U);
         }
       }
+      m01 = (int)U + (lr - kHalfPatch) * (int)T;
     }
 #pragma unroll
     for (int o = 16; o; o >>= 1) {

@@ -431,10 +431,13 @@ __global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k_fast(const __g
     }
     fast_run_mode(P, S, tIni, false, 0xffffffffu);
     if (tMin < tIni || S.retryMax > 0) {  // cells without a keypoint at iniThFAST run again at minThFAST (:1119; ComputeKeyPointsOld: at most 3, :1343)
-      __syncthreads();  // the cell flags of phase P3 and the cleared m-map
+      // the cell flags are final since the run's last barrier (every warp is past phase P3); the answer is the same in every warp
       const int ln = tid & 31;
       const u32 retry = __ballot_sync(0xffffffffu, ln < d.nCells && sCellIni[ln] <= S.retryMax);
-      if (retry) fast_run_mode(P, S, tMin, true, retry);
+      if (retry) {
+        __syncthreads();  // the m-map is cleared
+        fast_run_mode(P, S, tMin, true, retry);
+      }
     }
     __syncthreads();
     if (kFastStages == 1 && tid == 0 && item + (int)gridDim.x < nItems) issue(nslot, load_desc(nstrip), 0);
