@@ -92,6 +92,14 @@ struct BlurTile {
 struct TmaMaps {
   CUtensorMap lvl[kMaxLevels];
 };
+// k_describe's keypoint patches: the same tensors over P.pyr (IC_Angle, 31 rows) and P.blur (steered BRIEF, 37 rows) with
+// boxes of kPatchWords words per row.  A box must start on a 16-byte boundary in global memory (anything else raises Warp
+// Illegal Instruction), so a patch starts at the 16-byte column at or below x - 18 and is 64 bytes wide.
+constexpr int kPatchRows = 37, kDiscRows = 31, kPatchWords = 16;
+struct PatchMaps {
+  CUtensorMap pyr[kMaxLevels], blur[kMaxLevels];
+};
+__device__ __forceinline__ u32 smem_addr(const void* p) { return (u32)__cvta_generic_to_shared(p); }
 
 struct Params {
   int W, H, nlevels, nfeatures, iniTh, minTh, maxBatch;
@@ -183,7 +191,7 @@ int launch_blur(const Params& P, int nSlots, cudaStream_t st);
 int launch_fast(const Params& P, const TmaMaps& M, int nSlots, cudaStream_t st);
 int launch_quadtree(const Params& P, int nSlots, cudaStream_t st);
 int launch_retain_old(const Params& P, int nSlots, cudaStream_t st);
-int launch_describe(const Params& P, int nSlots, int lap0, int lap1, cudaStream_t st);
+int launch_describe(const Params& P, const PatchMaps& M, int nSlots, int lap0, int lap1, cudaStream_t st);
 int launch_glue(const Params& P, int nSlots, cudaStream_t st);
 // scratch of the brute-force matcher (match_bf.cu), per pair; topk == nullptr: not available
 struct BfScratch {

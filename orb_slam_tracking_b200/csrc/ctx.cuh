@@ -29,6 +29,7 @@ int compute_tables(int nfeatures, float scaleFactor, int nlevels, HostTables& t)
 struct orbx_ctx {
   orbx::Params P;
   orbx::HostTables T;
+  orbx::PatchMaps patchMaps;       // per-level tensor maps over P.pyr and P.blur with k_describe's patch boxes
   orbx::TmaMaps tma;               // per-level tensor maps over P.pyr (k_fast tile staging) of the ACTIVE keypoint policy
   struct FastSet {                 // what k_fast needs per keypoint policy ([0] ComputeKeyPointsOctTree, [1] ComputeKeyPointsOld)
     const orbx::StripDesc* strips;

@@ -38,19 +38,31 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 
 constexpr int kWarpsPerCta = 8;
 constexpr int kKpPerCta = 32;           // keypoint slots per CTA: 4 per warp, one per thread of warp 0 for the trigonometry
-constexpr int kPatchRows = 37, kPatchWords = 10;  // blurred patch [-18, 18]^2 staged as 37 rows of 10 aligned words
+constexpr int kRowBytes = 4 * kPatchWords;                   // 64: a staged patch row
+constexpr int kDiscBytes = kDiscRows * kRowBytes;            // 1984: TMA box of the unblurred level (rows y - 15 .. y + 15)
+constexpr int kPatchBytes = kPatchRows * kRowBytes;          // 2368: TMA box of the blurred level (rows y - 18 .. y + 18)
+constexpr int kPatchBuf = (kPatchBytes + 127) & ~127;        // ring buffers stay 128-byte aligned
+#ifndef ORBX_DESC_CTAS
+#define ORBX_DESC_CTAS 5
+#endif
 
 // Three phases per CTA of 32 keypoint slots:
-//   1. IC_Angle, one warp per keypoint: the 31 x 31 disc is read as aligned 32-bit words (9 per row, lanes
-//      over (row, word)), each byte weighted by its column offset u and masked by |u| <= umax[|v|].
+//   1. IC_Angle, one warp per keypoint: the 31 x 31 disc is read as aligned 32-bit words (lanes over (row, word)),
+//      each byte weighted by its column offset u and masked by |u| <= umax[|v|].
 //   2. cos/sin of the 32 angles, one THREAD per keypoint (the double-precision libm calls are the longest
 //      instruction stream of the kernel; a warp per keypoint would run them 32x redundantly).
-//   3. steered BRIEF, one warp per keypoint: the 37 x 37 blurred patch is staged into shared memory with
-//      coalesced word loads, then lane = descriptor byte gathers its 16 samples from shared memory.
-__global__ void __launch_bounds__(kWarpsPerCta * 32, 6) k_describe(const __grid_constant__ Params P) {
+//   3. steered BRIEF, one warp per keypoint: lane = descriptor byte gathers its 16 samples from the blurred patch.
+// Both phases read the keypoint's neighbourhood from shared memory, where ONE TMA box copy per keypoint and image put it
+// (cp.async.bulk.tensor.3d, 16 words x 31 or 37 rows, issued by one lane into the warp's two-deep ring, completion on the
+// buffer's mbarrier): the kernel is bound by L1 wavefronts and load latency, and the box copies use neither the LSU pipe
+// nor registers.  A warp's copies form one sequence -- the unblurred discs of its (up to 4) keypoints, then the blurred
+// patches -- and copy i + 2 is issued as soon as buffer i has been consumed, so the blurred patches of its first two
+// keypoints are in flight while the CTA is at the barriers around phase 2.
+__global__ void __launch_bounds__(kWarpsPerCta * 32, ORBX_DESC_CTAS) k_describe(const __grid_constant__ Params P, const __grid_constant__ PatchMaps M) {
+  __shared__ __align__(128) u32 sPatch[kWarpsPerCta][2][kPatchBuf / 4];
   __shared__ float4 sPat[256];  // pattern pair (x0, y0, x1, y1) as floats, [i * 32 + byte]: conflict-free for lane = byte
-  __shared__ u32 sMask[4][31 * 9];  // IC_Angle's disc as byte masks: [x & 3][row][word], 0xff where |u| <= umax[|v|]
-  __shared__ u32 sPatch[kWarpsPerCta][kPatchRows * kPatchWords];
+  __shared__ __align__(8) u64 sBar[kWarpsPerCta][2];
+  __shared__ u32 sDD[32];       // per disc row: 0x80808080 | umax[|v|] * 0x01010101 (byte-wise column limit of IC_Angle)
   __shared__ float sAngle[kKpPerCta], sCos[kKpPerCta], sSin[kKpPerCta];
   __shared__ u32 sXY[kKpPerCta];
   __shared__ signed char sLevel[kKpPerCta];  // -1: empty slot
@@ -59,15 +71,13 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 6) k_describe(const __grid_
     const int b = tid & 31, i = tid >> 5;  // 256 threads: pair (b, i) -> pattern row 8b + i
     const signed char* p = c_pattern + 4 * (8 * b + i);
     sPat[i * 32 + b] = make_float4((float)p[0], (float)p[1], (float)p[2], (float)p[3]);
-    // word w of a row starts at column offset u = 4 w - 15 - ((x + 1) & 3) from the keypoint (x - 15 = xa + ((x + 1) & 3))
-    for (int i = tid; i < 4 * 31 * 9; i += kWarpsPerCta * 32) {
-      const int a = i / (31 * 9), rw = i - a * (31 * 9), r = rw / 9, w = rw - 9 * r;
-      const int d = P.umax[r < kHalfPatch ? kHalfPatch - r : r - kHalfPatch], u0 = 4 * w - kHalfPatch - ((a + 1) & 3);
-      u32 m = 0;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) m |= (abs(u0 + j) <= d ? 0xffu : 0u) << (8 * j);
-      sMask[a][rw] = m;
-    }
+    if (tid < 31) sDD[tid] = 0x80808080u | ((u32)P.umax[tid < kHalfPatch ? kHalfPatch - tid : tid - kHalfPatch] * 0x01010101u);
+  }
+  if (lane == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&sBar[warp][0])));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(&sBar[warp][1])));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
   const int slot = blockIdx.y;
   const int gBase = blockIdx.x * kKpPerCta;
@@ -87,31 +97,67 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 6) k_describe(const __grid_
   }
   __syncthreads();
 
+  // the warp's occupied keypoint slots (k = warp + 8 j), one per byte of kk
+  u32 kk = 0;
+  int nv = 0;
+#pragma unroll
+  for (int j = 0; j < kKpPerCta / kWarpsPerCta; ++j) {
+    const int k = warp + kWarpsPerCta * j;
+    if (sLevel[k] >= 0) { kk |= (u32)k << (8 * nv); ++nv; }
+  }
+  // copy i of the warp's sequence into buffer i & 1: the disc of keypoint i (i < nv) or the blurred patch of keypoint i - nv
+  auto issue = [&](int i) {
+    if (lane == 0) {
+      const bool blurred = i >= nv;
+      const int k = (int)(kk >> (8 * (blurred ? i - nv : i))) & 31;
+      const int l = sLevel[k];
+      const u32 xy = sXY[k];
+      const int x = (int)(xy & 0xffff), y = (int)(xy >> 16);
+      const u32 bar = smem_addr(&sBar[warp][i & 1]);
+      const CUtensorMap* map = blurred ? &M.blur[l] : &M.pyr[l];
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(blurred ? kPatchBytes : kDiscBytes) : "memory");
+      asm volatile(
+          "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];"
+          ::"r"(smem_addr(&sPatch[warp][i & 1][0])), "l"(reinterpret_cast<u64>(map)), "r"(((x - 18) & ~15) >> 2), "r"(blurred ? y - 18 : y - kHalfPatch),
+            "r"(slot + P.slot0), "r"(bar)
+          : "memory");
+    }
+  };
+  auto wait = [&](int i) {
+    const u32 bar = smem_addr(&sBar[warp][i & 1]), parity = (u32)(i >> 1) & 1u;
+    u32 done = 0;
+    while (!done) {
+      asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
+                   : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    }
+  };
+  if (nv > 0) { issue(0); issue(1); }  // 2 nv >= 2 copies
+
   // ---- phase 1: IC_Angle ----
-  for (int k = warp; k < kKpPerCta; k += kWarpsPerCta) {
-    const int l = sLevel[k];
-    if (l < 0) continue;
-    const LevelInfo& L = P.lv[l];
-    const u32 xy = sXY[k];
-    const int x = (int)(xy & 0xffff), y = (int)(xy >> 16);
-    const int xa = (x - kHalfPatch) & ~3;  // 9 aligned words cover [x-15, x+15]
-    const u8* __restrict__ img = level_ptr((const u8*)P.pyr, P, slot, l) + (size_t)(y - kHalfPatch) * L.pitch + xa;
-    int m10 = 0, m01 = 0;
-    // lanes 0..26 = 3 rows x 9 words; a lane keeps its word column, so its four column offsets u_j are fixed
-    // and only the row's half-width d = umax[|v|] changes: byte j counts iff |u_j| <= d
+  // lanes 0..26 = 3 rows x 9 words; the disc's columns [x - 15, x + 15] lie in 9 aligned words of the staged rows.  A lane
+  // keeps its word column, so its four column offsets u_j are fixed and only the row's half-width d = umax[|v|] changes:
+  // byte j counts iff |u_j| <= d
+  for (int i = 0; i < nv; ++i) {
+    const int k = (int)(kk >> (8 * i)) & 31;
+    const int x = (int)(sXY[k] & 0xffff);
+    const int xa = (x - 18) & ~15;                 // first staged column
+    const int w0 = (x - kHalfPatch - xa) >> 2;     // first of the disc's 9 words in a staged row
     const int lr = lane / 9, w = lane - 9 * lr;
-    const int u0 = xa + 4 * w - x;
+    const int u0 = xa + 4 * (w0 + w) - x;
+    // |u_j| per byte (< 128); byte j of a row counts iff umax >= |u_j|: bit 7 of (0x80 | umax) - |u_j| survives
+    const u32 apk = (u32)abs(u0) | ((u32)abs(u0 + 1) << 8) | ((u32)abs(u0 + 2) << 16) | ((u32)abs(u0 + 3) << 24);
     const int upk = (u0 & 255) | (((u0 + 1) & 255) << 8) | (((u0 + 2) & 255) << 16) | (((u0 + 3) & 255) << 24);  // s8 x 4
+    const u32* const pw = &sPatch[warp][i & 1][lr * kPatchWords + w0 + w];
+    int m10 = 0, m01 = 0;
+    wait(i);
     if (lane < 27) {
       // m01 = sum over rows of (r - 15) * rowsum with r = rb + lr: T = sum of the bytes, U = sum of rb * bytes (rb is a
       // compile-time byte), m01 = U + (lr - 15) * T
-      const u32* const mk = &sMask[x & 3][9 * lr + w];
-      const u8* const ip = img + (size_t)lr * L.pitch + 4 * w;
       u32 T = 0, U = 0;
 #pragma unroll
       for (int rb = 0; rb < 33; rb += 3) {
-        if (rb + lr < 31) {
-          const u32 word = __ldg(reinterpret_cast<const u32*>(ip + (size_t)rb * L.pitch)) & mk[9 * rb];
+        if (rb + lr < kDiscRows) {
+          const u32 word = pw[rb * kPatchWords] & ((((sDD[rb + lr] - apk) & 0x80808080u) >> 7) * 255u);
           asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(m10) : "r"(word), "r"(upk), "r"(m10));
           T = __dp4a(word, 0x01010101u, T);
           U = __dp4a(word, (u32)rb * 0x01010101u, U);
@@ -119,6 +165,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 6) k_describe(const __grid_
       }
       m01 = (int)U + (lr - kHalfPatch) * (int)T;
     }
+    __syncwarp();  // every lane has read buffer i & 1
+    if (i + 2 < 2 * nv) issue(i + 2);
 #pragma unroll
     for (int o = 16; o; o >>= 1) {
       m10 += __shfl_xor_sync(0xffffffffu, m10, o);
@@ -142,41 +190,27 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, 6) k_describe(const __grid_
   __syncthreads();
 
   // ---- phase 3: steered BRIEF, lane = descriptor byte ----
-  u32* const patch = sPatch[warp];
-  for (int k = warp; k < kKpPerCta; k += kWarpsPerCta) {
-    const int l = sLevel[k];
-    if (l < 0) continue;
-    const LevelInfo& L = P.lv[l];
-    const u32 xy = sXY[k];
-    const int x = (int)(xy & 0xffff), y = (int)(xy >> 16);
-    const int xa = (x - 18) & ~3;  // 10 aligned words cover [x-18, x+18]
-    const u8* __restrict__ bl = level_ptr((const u8*)P.blur, P, slot, l) + (size_t)(y - 18) * L.pitch + xa;
-    __syncwarp();
-    {  // lanes 0..29 = 3 rows x 10 words per step
-      const int lr = lane / kPatchWords, w = lane - kPatchWords * lr;
-      if (lane < 3 * kPatchWords) {
-#pragma unroll
-        for (int rb = 0; rb < 39; rb += 3) {
-          const int r = rb + lr;
-          if (r < kPatchRows) patch[r * kPatchWords + w] = __ldg(reinterpret_cast<const u32*>(bl + (size_t)r * L.pitch) + w);
-        }
-      }
-    }
-    __syncwarp();
-    const u8* centre = reinterpret_cast<const u8*>(patch) + 18 * (4 * kPatchWords) + (x - xa);
+  for (int i = 0; i < nv; ++i) {
+    const int k = (int)(kk >> (8 * i)) & 31;
+    const int x = (int)(sXY[k] & 0xffff);
+    const int xa = (x - 18) & ~15;
+    const u8* centre = reinterpret_cast<const u8*>(&sPatch[warp][(nv + i) & 1][0]) + 18 * kRowBytes + (x - xa);
     const float co = sCos[k], si = sSin[k];
+    wait(nv + i);
     u32 val = 0;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float4 q = sPat[i * 32 + lane];
+    for (int j = 0; j < 8; ++j) {
+      const float4 q = sPat[j * 32 + lane];
       const float x0 = q.x, y0 = q.y, x1 = q.z, y1 = q.w;
       const int r0 = __float2int_rn(__fadd_rn(__fmul_rn(x0, si), __fmul_rn(y0, co)));
       const int c0 = __float2int_rn(__fsub_rn(__fmul_rn(x0, co), __fmul_rn(y0, si)));
       const int r1 = __float2int_rn(__fadd_rn(__fmul_rn(x1, si), __fmul_rn(y1, co)));
       const int c1 = __float2int_rn(__fsub_rn(__fmul_rn(x1, co), __fmul_rn(y1, si)));
-      const int t0 = centre[r0 * (4 * kPatchWords) + c0], t1 = centre[r1 * (4 * kPatchWords) + c1];
-      val |= (u32)(t0 < t1) << i;
+      const int t0 = centre[r0 * kRowBytes + c0], t1 = centre[r1 * kRowBytes + c1];
+      val |= (u32)(t0 < t1) << j;
     }
+    __syncwarp();  // every lane has read buffer (nv + i) & 1
+    if (nv + i + 2 < 2 * nv) issue(nv + i + 2);
     P.lvlDesc[((size_t)slot * P.kpStride + gBase + k) * 32 + lane] = (u8)val;
   }
 }
@@ -244,9 +278,9 @@ __global__ void __launch_bounds__(PK) k_pack(const __grid_constant__ Params P, i
   if (tid == 0) { P.outN[slot] = total; P.outMono[slot] = total - nLap; }
 }
 
-int launch_describe(const Params& P, int nSlots, int lap0, int lap1, cudaStream_t st) {
+int launch_describe(const Params& P, const PatchMaps& M, int nSlots, int lap0, int lap1, cudaStream_t st) {
   dim3 grid((P.kpStride + kKpPerCta - 1) / kKpPerCta, nSlots);
-  k_describe<<<grid, kWarpsPerCta * 32, 0, st>>>(P);
+  k_describe<<<grid, kWarpsPerCta * 32, 0, st>>>(P, M);
   k_pack<<<nSlots, PK, 0, st>>>(P, lap0, lap1);
   return 2;
 }

@@ -86,7 +86,6 @@ __device__ __forceinline__ u32 word_at(u32 wl, u32 wc, u32 wr) {
   return __funnelshift_r(wl, wc, 32 + 8 * DX);
 }
 
-__device__ __forceinline__ u32 smem_addr(const void* p) { return (u32)__cvta_generic_to_shared(p); }
 
 struct Row3 { u32 l, c, r; };  // words g-1, g, g+1 of one staged row
 __device__ __forceinline__ Row3 load3(const u32* __restrict__ row, int g) { return Row3{row[g - 1], row[g], row[g + 1]}; }

@@ -60,6 +60,15 @@ static int build_tensor_maps(orbx_ctx* c, int policy = 0) {
                                 CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                                 CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { c->err = "cuTensorMapEncodeTiled failed: " + std::to_string((int)r); return ORBX_ERR_CUDA; }
+    if (policy == 0) {  // k_describe's patch boxes over the pyramid and the blurred pyramid (independent of the keypoint policy)
+      for (int b = 0; b < 2; ++b) {
+        cuuint32_t pbox[3] = {(cuuint32_t)kPatchWords, (cuuint32_t)(b ? kPatchRows : kDiscRows), 1};
+        r = ((EncodeFn)fn)(b ? &c->patchMaps.blur[l] : &c->patchMaps.pyr[l], CU_TENSOR_MAP_DATA_TYPE_UINT32, 3, (b ? P.blur : P.pyr) + L.imgOff, dims,
+                           strides, pbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) { c->err = "cuTensorMapEncodeTiled (patch) failed: " + std::to_string((int)r); return ORBX_ERR_CUDA; }
+      }
+    }
   }
   return ORBX_OK;
 }

@@ -82,7 +82,7 @@ int enqueue_extract(orbx_ctx* c, const Params& P, int n, int lap0, int lap1, cud
   else c->launches += launch_blur(P, n, st);
   mark(c, 4);
   if (beforeOut) CU(c, cudaStreamWaitEvent(st, beforeOut, 0));
-  c->launches += launch_describe(P, n, lap0, lap1, st);
+  c->launches += launch_describe(P, c->patchMaps, n, lap0, lap1, st);
   mark(c, 5);
   CU(c, cudaGetLastError());
   c->lastBatch = n;
