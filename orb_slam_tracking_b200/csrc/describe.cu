@@ -49,8 +49,9 @@ constexpr int kPatchBuf = (kPatchBytes + 127) & ~127;        // ring buffers sta
 // Three phases per CTA of 32 keypoint slots:
 //   1. IC_Angle, one warp per keypoint: the 31 x 31 disc is read as aligned 32-bit words (lanes over (row, word)),
 //      each byte weighted by its column offset u and masked by |u| <= umax[|v|].
-//   2. cos/sin of the 32 angles, one THREAD per keypoint (the double-precision libm calls are the longest
-//      instruction stream of the kernel; a warp per keypoint would run them 32x redundantly).
+//   2. fastAtan2 and cos/sin, one LANE per keypoint of the warp (the double-precision libm calls are the longest
+//      instruction stream of the kernel: the warp runs them once for its up to 4 keypoints; no CTA barrier -- after the
+//      set-up a warp never waits for another).
 //   3. steered BRIEF, one warp per keypoint: lane = descriptor byte gathers its 16 samples from the blurred patch.
 // Both phases read the keypoint's neighbourhood from shared memory, where ONE TMA box copy per keypoint and image put it
 // (cp.async.bulk.tensor.3d, 16 words x 31 or 37 rows, issued by one lane into the warp's two-deep ring, completion on the
@@ -63,7 +64,6 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, ORBX_DESC_CTAS) k_describe(
   __shared__ float4 sPat[256];  // pattern pair (x0, y0, x1, y1) as floats, [i * 32 + byte]: conflict-free for lane = byte
   __shared__ __align__(8) u64 sBar[kWarpsPerCta][2];
   __shared__ u32 sDD[32];       // per disc row: 0x80808080 | umax[|v|] * 0x01010101 (byte-wise column limit of IC_Angle)
-  __shared__ float sAngle[kKpPerCta], sCos[kKpPerCta], sSin[kKpPerCta];
   __shared__ u32 sXY[kKpPerCta];
   __shared__ signed char sLevel[kKpPerCta];  // -1: empty slot
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -137,6 +137,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, ORBX_DESC_CTAS) k_describe(
   // lanes 0..26 = 3 rows x 9 words; the disc's columns [x - 15, x + 15] lie in 9 aligned words of the staged rows.  A lane
   // keeps its word column, so its four column offsets u_j are fixed and only the row's half-width d = umax[|v|] changes:
   // byte j counts iff |u_j| <= d
+  int k10 = 0, k01 = 0;  // lane i: the moments of the warp's keypoint i
   for (int i = 0; i < nv; ++i) {
     const int k = (int)(kk >> (8 * i)) & 31;
     const int x = (int)(sXY[k] & 0xffff);
@@ -172,22 +173,19 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, ORBX_DESC_CTAS) k_describe(
       m10 += __shfl_xor_sync(0xffffffffu, m10, o);
       m01 += __shfl_xor_sync(0xffffffffu, m01, o);
     }
-    if (lane == 0) sAngle[k] = fast_atan2_deg((float)m01, (float)m10);
+    if (lane == i) { k10 = m10; k01 = m01; }
   }
-  __syncthreads();
 
-  // ---- phase 2: one thread per keypoint ----
-  if (tid < kKpPerCta && sLevel[tid] >= 0) {
-    const float angle = sAngle[tid];
+  // ---- phase 2: one lane per keypoint of the warp ----
+  float myCos = 0.f, mySin = 0.f;
+  if (lane < nv) {
+    const float angle = fast_atan2_deg((float)k01, (float)k10);
     const float a = __fmul_rn(angle, (float)(3.1415926535897932384626433832795 / 180.f));
-    float co, si;
-    if (P.trigMode == 0) { co = (float)cos((double)a); si = (float)sin((double)a); }
-    else { co = cosf(a); si = sinf(a); }
-    sCos[tid] = co;
-    sSin[tid] = si;
-    P.lvlAngle[(size_t)slot * P.kpStride + gBase + tid] = angle;
+    if (P.trigMode == 0) { myCos = (float)cos((double)a); mySin = (float)sin((double)a); }
+    else { myCos = cosf(a); mySin = sinf(a); }
+    P.lvlAngle[(size_t)slot * P.kpStride + gBase + ((kk >> (8 * lane)) & 31)] = angle;
   }
-  __syncthreads();
+  __syncwarp();
 
   // ---- phase 3: steered BRIEF, lane = descriptor byte ----
   for (int i = 0; i < nv; ++i) {
@@ -195,7 +193,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, ORBX_DESC_CTAS) k_describe(
     const int x = (int)(sXY[k] & 0xffff);
     const int xa = (x - 18) & ~15;
     const u8* centre = reinterpret_cast<const u8*>(&sPatch[warp][(nv + i) & 1][0]) + 18 * kRowBytes + (x - xa);
-    const float co = sCos[k], si = sSin[k];
+    const float co = __shfl_sync(0xffffffffu, myCos, i), si = __shfl_sync(0xffffffffu, mySin, i);
     wait(nv + i);
     u32 val = 0;
 #pragma unroll
