@@ -76,8 +76,12 @@ orbx_ctx* orbx_create(int device, int width, int height, int nfeatures, float sc
                       int ini_th_fast, int min_th_fast, int max_batch, int* status);
 void orbx_destroy(orbx_ctx* ctx);
 const char* orbx_last_error(const orbx_ctx* ctx); /* never NULL */
-/* 0: (float)cos((double)a) [default, pinned by the oracle]; 1: cosf(a).  See DESIGN.md. */
+/* cos / sin of the keypoint angle in computeOrbDescriptor (Features/ORBextractor.cpp:173-174: the float overloads, glibc's
+ * cosf / sinf).  2 [default]: glibc's algorithm restated on the device, bit-equal to the host libm on every float of
+ * [0, 2 pi]; 0: (float)cos((double)a); 1: CUDA's cosf(a).  See DESIGN.md section 5. */
 int orbx_set_trig_mode(orbx_ctx* ctx, int mode);
+/* Test hook: sin / cos of n host floats computed exactly as trig mode 2 does on the device (host buffers in and out). */
+int orbx_sincosf_probe(orbx_ctx* ctx, const float* y, long long n, float* sin_out, float* cos_out);
 /* Keypoint selection policy of the context: 0 = ComputeKeyPointsOctTree (default; what the reference's operator() calls,
  * Features/ORBextractor.cpp:1552), 1 = ComputeKeyPointsOld (:1207-1496, the alternative the reference keeps behind a
  * commented-out call, :1555): its own cell grid, the minThFAST retry for cells with at most 3 keypoints, per-cell quotas

@@ -424,14 +424,47 @@ static float ic_angle(const u8* img, size_t step, float px, float py, const std:
 
 // =====================================================================================
 // Steered BRIEF -- computeOrbDescriptor, Features/ORBextractor.cpp:169-228
-// trigMode 0: (float)cos((double)a)  [pinned]   1: cosf(a)  [variant for the mismatch report]
+// `cos(angle)` / `sin(angle)` at :174 take a float under <cmath> + `using namespace std`: the float overloads, i.e. glibc's
+// cosf / sinf.  glibc is not part of /root/reference, so its published algorithm is restated here (glibc >= 2.28,
+// sysdeps/ieee754/flt-32/{s_sincosf.h,s_sinf.c,s_cosf.c}: the ARM optimized-routines sincosf -- reduction by one multiply with
+// 2/pi * 2^24, a degree-7 sine / degree-8 cosine polynomial in double, one rounding to float) and pinned against the libm of
+// the machine: tools/probe/glibc_sincosf_check.c compares it on EVERY float of [0, 2 pi] (and up to 119.9), bit for bit;
+// tests/test_trig_port.py repeats a sample.  On x86-64 the ifunc-selected __cosf_fma / __sinf_fma contract every a * b + c;
+// in the angle range the contracted and the plain form round to the same float everywhere (same check).
+// trigMode 2: this restatement [default, pinned]   0: (float)cos((double)a)   1: the machine's cosf(a) / sinf(a)
 // =====================================================================================
+static inline double fma_d(double a, double b, double c) { return __builtin_fma(a, b, c); }
+static void glibc_sincosf_port(float y, float* sn, float* cs) {
+  static const double C[5] = {0x1p0, -0x1.ffffffd0c621cp-2, 0x1.55553e1068f19p-5, -0x1.6c087e89a359dp-10, 0x1.99343027bf8c3p-16};
+  static const double S[3] = {-0x1.555545995a603p-3, 0x1.1107605230bc4p-7, -0x1.994eb3774cf24p-13};
+  uint32_t bits;
+  std::memcpy(&bits, &y, 4);
+  const uint32_t top = (bits >> 20) & 0x7ff;               // abstop12
+  if (top >= 0x42f) { *sn = sinf(y); *cs = cosf(y); return; }  // |y| >= 120, inf, nan: not restated (an angle in radians is <= 2 pi)
+  if (top < 0x398) { *sn = y; *cs = 1.0f; return; }   // |y| < 2^-12
+  double x = y;
+  int n = 0;
+  if (top >= 0x3f4) {                                 // |y| >= pi / 4 (float): reduce_fast
+    const double r = x * 0x1.45F306DC9C883p+23;
+    n = ((int32_t)r + 0x800000) >> 24;
+    x = fma_d(-(double)n, 0x1.921FB54442D18p0, x);
+  }
+  const double sg = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0, ng = (n & 2) ? -1.0 : 1.0;
+  const double xs = x * sg, x2 = x * x;
+  const double x3 = xs * x2, s1 = fma_d(x2, S[2], S[1]), x7 = x3 * x2, s = fma_d(x3, S[0], xs);
+  const float sp = (float)fma_d(x7, s1, s);           // sinf_poly, even quadrant
+  const double x4 = x2 * x2, c2 = fma_d(x2, ng * C[4], ng * C[3]), c1 = fma_d(x2, ng * C[1], ng * C[0]), x6 = x4 * x2;
+  const double c = fma_d(x4, ng * C[2], c1);
+  const float cp = (float)fma_d(x6, c2, c);           // sinf_poly, odd quadrant (second table when n & 2)
+  if (n & 1) { *sn = cp; *cs = sp; } else { *sn = sp; *cs = cp; }
+}
 static void brief256(const u8* img, size_t step, const KeyPoint& kp, int trigMode, u8* desc) {
   const float factorPI = (float)(3.1415926535897932384626433832795 / 180.f);
   float angle = kp.angle * factorPI;
   float co, si;
   if (trigMode == 0) { co = (float)std::cos((double)angle); si = (float)std::sin((double)angle); }
-  else { co = cosf(angle); si = sinf(angle); }
+  else if (trigMode == 1) { co = cosf(angle); si = sinf(angle); }
+  else glibc_sincosf_port(angle, &si, &co);
   const u8* c = img + (ptrdiff_t)cv_round(kp.y) * (ptrdiff_t)step + cv_round(kp.x);
   const int* p = kPatternTable;
   for (int i = 0; i < 32; ++i) {
@@ -727,13 +760,30 @@ int orc_descriptor_distance(const u8* a, const u8* b) { return hamming256(a, b);
 void* orc_extractor_create(int nfeatures, float scaleFactor, int nlevels, int iniTh, int minTh) {
   Extractor* e = new Extractor();
   e->t = make_tables(nfeatures, scaleFactor, nlevels, iniTh, minTh);
-  e->trigMode = 0;
+  e->trigMode = 2;
   e->policy = 0;
   if (e->t.status) { delete e; return 0; }
   return e;
 }
 void orc_extractor_destroy(void* h) { delete (Extractor*)h; }
 void orc_extractor_set_trig_mode(void* h, int m) { ((Extractor*)h)->trigMode = m; }
+// cv::KeyPointsFilter::retainBest as restated in cv_prims.hpp, on n responses: idx_out receives the indices of the kept
+// elements in their final order; returns how many
+int orc_retain_best(const float* response, int n, int n_points, int* idx_out) {
+  struct KP { float response; int idx; };
+  std::vector<KP> k((size_t)n);
+  for (int i = 0; i < n; ++i) k[i] = KP{response[i], i};
+  retain_best(k, n_points);
+  for (size_t i = 0; i < k.size(); ++i) idx_out[i] = k[i].idx;
+  return (int)k.size();
+}
+// the restated glibc sinf / cosf (which = 0) or the machine's libm (which = 1) on n floats
+void orc_sincosf(int which, const float* y, long long n, float* sn, float* cs) {
+  for (long long i = 0; i < n; ++i) {
+    if (which == 0) glibc_sincosf_port(y[i], sn + i, cs + i);
+    else { sn[i] = sinf(y[i]); cs[i] = cosf(y[i]); }
+  }
+}
 void orc_extractor_set_policy(void* h, int p) { ((Extractor*)h)->policy = p; }
 int orc_extractor_tables(void* h, float* scale, float* invScale, float* sigma2, float* invSigma2,
                          int* perLevel, int* umax16) {
@@ -861,7 +911,7 @@ long long orc_run_stream(const u8* imgs, int nframes, int W, int H, int nfeature
   auto worker = [&]() {
     Extractor E;
     E.t = make_tables(nfeatures, scaleFactor, nlevels, iniTh, minTh);
-    E.trigMode = 0;
+    E.trigMode = 2;
     E.policy = 0;
     const int lap[2] = {0, 0};
     for (;;) {

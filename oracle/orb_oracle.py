@@ -42,6 +42,8 @@ def lib():
         L.orc_extractor_destroy.argtypes = [vp]
         L.orc_extractor_set_trig_mode.argtypes = [vp, C.c_int]
         L.orc_extractor_set_policy.argtypes = [vp, C.c_int]
+        L.orc_retain_best.argtypes = [vp, C.c_int, C.c_int, vp]
+        L.orc_sincosf.argtypes = [C.c_int, vp, C.c_longlong, vp, vp]
         L.orc_extractor_tables.argtypes = [vp, vp, vp, vp, vp, vp, vp]
         L.orc_extract.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, vp, vp, vp, C.c_int, vp]
         L.orc_level_size.argtypes = [vp, C.c_int, vp, vp]
@@ -158,7 +160,7 @@ def image_bounds(W, H, K4, D4):
 class Extractor:
     """Mirror of ORB_SLAM_Tracking::ORBextractor (reference Features/ORBextractor.hpp:55-158)."""
 
-    def __init__(self, nfeatures, scale_factor, nlevels, ini_th, min_th, trig_mode=0, policy=0):
+    def __init__(self, nfeatures, scale_factor, nlevels, ini_th, min_th, trig_mode=2, policy=0):
         """policy 0: ComputeKeyPointsOctTree (the reference's operator()); 1: ComputeKeyPointsOld (its commented-out alternative)."""
         self.nfeatures, self.nlevels = nfeatures, nlevels
         self._h = lib().orc_extractor_create(nfeatures, scale_factor, nlevels, ini_th, min_th)
@@ -311,3 +313,19 @@ def check_fundamental(kps1_un, kps2_un, matches12, F21, sigma=1.0):
 def ransac_best(scores):
     s = np.ascontiguousarray(scores, np.float32)
     return int(lib().orc_ransac_best(_p(s), len(s)))
+
+
+def sincosf(y, which=0):
+    """sin / cos of float32 values by the restated glibc sinf / cosf (which=0) or by the machine's libm (which=1)."""
+    y = np.ascontiguousarray(y, np.float32)
+    sn, cs = np.empty_like(y), np.empty_like(y)
+    lib().orc_sincosf(which, y.ctypes.data, y.size, sn.ctypes.data, cs.ctypes.data)
+    return sn, cs
+
+
+def retain_best(response, n_points):
+    """Indices kept by cv::KeyPointsFilter::retainBest (restated, cv_prims.hpp) in their final order."""
+    r = np.ascontiguousarray(response, np.float32)
+    idx = np.empty(len(r), np.int32)
+    n = lib().orc_retain_best(r.ctypes.data, len(r), int(n_points), idx.ctypes.data)
+    return idx[:n].copy()

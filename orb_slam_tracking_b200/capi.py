@@ -39,6 +39,7 @@ SIGNATURES = {
     "orbx_destroy": (None, [vp]),
     "orbx_last_error": (C.c_char_p, [vp]),
     "orbx_set_trig_mode": (ci, [vp, ci]),
+    "orbx_sincosf_probe": (ci, [vp, vp, C.c_longlong, vp, vp]),
     "orbx_set_option": (ci, [vp, C.c_char_p, ci]),
     "orbx_set_keypoint_policy": (ci, [vp, ci]),
     "orbx_get_level_tables": (ci, [vp, vp, vp, vp, vp, vp, vp]),

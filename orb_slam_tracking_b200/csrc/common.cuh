@@ -192,6 +192,7 @@ int launch_fast(const Params& P, const TmaMaps& M, int nSlots, cudaStream_t st);
 int launch_quadtree(const Params& P, int nSlots, cudaStream_t st);
 int launch_retain_old(const Params& P, int nSlots, cudaStream_t st);
 int launch_describe(const Params& P, const PatchMaps& M, int nSlots, int lap0, int lap1, cudaStream_t st);
+void launch_sincosf_probe(const float* y, long long n, float* sn, float* cs, cudaStream_t st);
 int launch_glue(const Params& P, int nSlots, cudaStream_t st);
 // scratch of the brute-force matcher (match_bf.cu), per pair; topk == nullptr: not available
 struct BfScratch {

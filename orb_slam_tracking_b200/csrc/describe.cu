@@ -36,6 +36,34 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
   return a;
 }
 
+// cos / sin of the keypoint angle.  The reference's `cos(angle)` / `sin(angle)` (:174) take a float under <cmath> and
+// `using namespace std`, i.e. glibc's cosf / sinf.  glibc is no part of the reference tree; its algorithm (glibc >= 2.28,
+// sysdeps/ieee754/flt-32/s_sincosf.h: one multiply by 2/pi * 2^24 gives the quadrant, the reduced argument and two short
+// polynomials run in double, ONE rounding to float) is restated here with explicit fused multiply-adds where the x86-64
+// __cosf_fma / __sinf_fma builds contract them.  The same restatement in the oracle equals the libm of the test machine on
+// every float of [0, 2 pi] (tools/probe/glibc_sincosf_check.c), and this one equals the oracle's (tests/test_trig_port.py).
+__device__ __forceinline__ void glibc_sincosf(float y, float& sn, float& cs) {
+  const u32 top = (__float_as_uint(y) >> 20) & 0x7ffu;
+  if (top >= 0x42fu) { sn = sinf(y); cs = cosf(y); return; }  // |y| >= 120, inf, nan: outside the restated range (an angle is <= 2 pi)
+  if (top < 0x398u) { sn = y; cs = 1.0f; return; }            // |y| < 2^-12
+  double x = (double)y;
+  int n = 0;
+  if (top >= 0x3f4u) {                                        // |y| >= pi / 4
+    n = (__double2int_rz(__dmul_rn(x, 0x1.45F306DC9C883p+23)) + 0x800000) >> 24;
+    x = __fma_rn(-(double)n, 0x1.921FB54442D18p0, x);
+  }
+  const double x2 = __dmul_rn(x, x);
+  const double xs = ((n + 1) & 2) ? -x : x;                   // sign of the sine in quadrants 0..3: + - - +
+  const double x3 = __dmul_rn(xs, x2), s1 = __fma_rn(x2, -0x1.994eb3774cf24p-13, 0x1.1107605230bc4p-7), x7 = __dmul_rn(x3, x2);
+  const float sp = __double2float_rn(__fma_rn(x7, s1, __fma_rn(x3, -0x1.555545995a603p-3, xs)));
+  // second table (n & 2): the cosine polynomial with every coefficient negated = the negated result (rounding is symmetric)
+  const double x4 = __dmul_rn(x2, x2), c2 = __fma_rn(x2, 0x1.99343027bf8c3p-16, -0x1.6c087e89a359dp-10);
+  const double c1 = __fma_rn(x2, -0x1.ffffffd0c621cp-2, 1.0), x6 = __dmul_rn(x4, x2);
+  const float cq = __double2float_rn(__fma_rn(x6, c2, __fma_rn(x4, 0x1.55553e1068f19p-5, c1)));
+  const float cp = (n & 2) ? -cq : cq;
+  if (n & 1) { sn = cp; cs = sp; } else { sn = sp; cs = cp; }
+}
+
 constexpr int kWarpsPerCta = 8;
 constexpr int kKpPerCta = 32;           // keypoint slots per CTA: 4 per warp, one per thread of warp 0 for the trigonometry
 constexpr int kRowBytes = 4 * kPatchWords;                   // 64: a staged patch row
@@ -181,7 +209,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, ORBX_DESC_CTAS) k_describe(
   if (lane < nv) {
     const float angle = fast_atan2_deg((float)k01, (float)k10);
     const float a = __fmul_rn(angle, (float)(3.1415926535897932384626433832795 / 180.f));
-    if (P.trigMode == 0) { myCos = (float)cos((double)a); mySin = (float)sin((double)a); }
+    if (P.trigMode == 2) glibc_sincosf(a, mySin, myCos);
+    else if (P.trigMode == 0) { myCos = (float)cos((double)a); mySin = (float)sin((double)a); }
     else { myCos = cosf(a); mySin = sinf(a); }
     P.lvlAngle[(size_t)slot * P.kpStride + gBase + ((kk >> (8 * lane)) & 31)] = angle;
   }
@@ -274,6 +303,14 @@ __global__ void __launch_bounds__(PK) k_pack(const __grid_constant__ Params P, i
     }
   }
   if (tid == 0) { P.outN[slot] = total; P.outMono[slot] = total - nLap; }
+}
+
+// the restated cosf / sinf on n floats (orbx_sincosf_probe: test hook for tests/test_trig_port.py)
+__global__ void k_sincosf_probe(const float* __restrict__ y, long long n, float* __restrict__ sn, float* __restrict__ cs) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) glibc_sincosf(y[i], sn[i], cs[i]);
+}
+void launch_sincosf_probe(const float* y, long long n, float* sn, float* cs, cudaStream_t st) {
+  k_sincosf_probe<<<1184, 256, 0, st>>>(y, n, sn, cs);
 }
 
 int launch_describe(const Params& P, const PatchMaps& M, int nSlots, int lap0, int lap1, cudaStream_t st) {

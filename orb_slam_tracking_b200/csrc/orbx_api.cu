@@ -81,7 +81,7 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   Params& P = c->P;
   std::memset(&P, 0, sizeof(P));
   P.W = width; P.H = height; P.nlevels = nlevels; P.nfeatures = nfeatures;
-  P.iniTh = iniTh; P.minTh = minTh; P.maxBatch = maxBatch; P.trigMode = 0;
+  P.iniTh = iniTh; P.minTh = minTh; P.maxBatch = maxBatch; P.trigMode = 2;
   // the only place the environment is read: schedule options of this context
   auto env_int = [](const char* name, int dflt) {
     const char* v = std::getenv(name);
@@ -267,7 +267,7 @@ extern "C" void orbx_destroy(orbx_ctx* c) {
 
 extern "C" const char* orbx_last_error(const orbx_ctx* c) { return c ? c->err.c_str() : "null context"; }
 extern "C" int orbx_set_trig_mode(orbx_ctx* c, int mode) {
-  if (!c || (mode != 0 && mode != 1)) return ORBX_ERR_ARG;
+  if (!c || mode < 0 || mode > 2) return ORBX_ERR_ARG;
   c->P.trigMode = mode;
   ++c->graphEpoch;
   return ORBX_OK;

@@ -324,6 +324,23 @@ extern "C" int orbx_descriptor_distance_batch(orbx_ctx* c, const uint8_t* a, con
   return rc;
 }
 
+// cos / sin of n float angles exactly as k_describe computes them in trig mode 2 (test hook of the restated glibc cosf / sinf)
+extern "C" int orbx_sincosf_probe(orbx_ctx* c, const float* y, long long n, float* sn, float* cs) {
+  if (!c || n < 0 || (n > 0 && (!y || !sn || !cs))) return ORBX_ERR_ARG;
+  if (n == 0) return ORBX_OK;
+  CU(c, cudaSetDevice(c->device));
+  float* d = nullptr;
+  CU(c, cudaMalloc(&d, (size_t)n * 3 * sizeof(float)));
+  cudaMemcpyAsync(d, y, (size_t)n * sizeof(float), cudaMemcpyHostToDevice, c->stream);
+  launch_sincosf_probe(d, n, d + n, d + 2 * n, c->stream);
+  cudaMemcpyAsync(sn, d + n, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, c->stream);
+  cudaMemcpyAsync(cs, d + 2 * n, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, c->stream);
+  const cudaError_t e = cudaStreamSynchronize(c->stream);
+  cudaFree(d);
+  if (e != cudaSuccess) { c->err = cudaGetErrorString(e); return ORBX_ERR_CUDA; }
+  return ORBX_OK;
+}
+
 // ---- Initializer scoring -------------------------------------------------------------
 static int score_reserve(orbx_ctx* c, size_t bytes) {
   if (bytes <= c->scoreBytes) return ORBX_OK;

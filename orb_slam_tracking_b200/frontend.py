@@ -53,6 +53,13 @@ class ORBextractor:
     def set_trig_mode(self, mode):
         check(lib().orbx_set_trig_mode(self._h, mode), self._h)
 
+    def sincosf_probe(self, y):
+        """sin / cos of float32 angles as the descriptor kernel computes them in trig mode 2 (orbx_sincosf_probe)."""
+        y = np.ascontiguousarray(y, np.float32)
+        sn, cs = np.empty_like(y), np.empty_like(y)
+        check(lib().orbx_sincosf_probe(self._h, ptr(y), y.size, ptr(sn), ptr(cs)), self._h)
+        return sn, cs
+
     def set_keypoint_policy(self, policy):
         """0: ComputeKeyPointsOctTree (default), 1: ComputeKeyPointsOld (Features/ORBextractor.cpp:1207-1496)."""
         check(lib().orbx_set_keypoint_policy(self._h, int(policy)), self._h)

@@ -125,3 +125,27 @@ def test_descriptor_distance(oracle):
         b = rng.integers(0, 256, 32, dtype=np.uint8)
         assert oracle.descriptor_distance(a, b) == int(np.unpackbits(a ^ b).sum())
         assert oracle.descriptor_distance(a, b) == int(cv2.norm(a, b, cv2.NORM_HAMMING))
+
+
+def test_retain_best_selection_and_order():
+    """cv::KeyPointsFilter::retainBest (ComputeKeyPointsOld, Features/ORBextractor.cpp:1452,1482) is not exposed by the wheel, but
+    cv::ORB runs it: with one level and FAST_SCORE, ORB::detect returns retainBest(runByImageBorder(FAST keypoints), nfeatures)
+    untouched (modules/features2d/src/orb.cpp, computeKeyPoints).  The restated retain_best (oracle/cv_prims.hpp: nth_element by
+    response, the ties of the n-th kept, libstdc++ element order) must reproduce that list: same keypoints, same ORDER."""
+    from oracle import orb_oracle as orc
+    rng = np.random.default_rng(0)
+    for trial in range(6):
+        h, w = [(240, 320), (480, 640), (200, 500)][trial % 3]
+        img = rng.integers(0, 256, (h, w), dtype=np.uint8)
+        img = cv2.normalize(cv2.GaussianBlur(img, (0, 0), 1.0 + 0.3 * trial), None, 0, 255, cv2.NORM_MINMAX)
+        t = [20, 7, 12][trial % 3]
+        b = 31
+        kb = [kp for kp in cv2.FastFeatureDetector_create(t, True).detect(img) if b <= kp.pt[0] < w - b and b <= kp.pt[1] < h - b]
+        resp = np.array([kp.response for kp in kb], np.float32)
+        assert len(kb) > 500
+        for n in (1, 7, 50, 200, 1000, len(kb) - 1, len(kb), len(kb) + 5):
+            orb = cv2.ORB_create(nfeatures=n, scaleFactor=1.2, nlevels=1, edgeThreshold=b, firstLevel=0, WTA_K=2,
+                                 scoreType=cv2.ORB_FAST_SCORE, patchSize=31, fastThreshold=t)
+            ref = [(kp.pt[0], kp.pt[1], kp.response) for kp in orb.detect(img)]
+            got = [(kb[i].pt[0], kb[i].pt[1], kb[i].response) for i in orc.retain_best(resp, n)]
+            assert got == ref, (trial, n)
