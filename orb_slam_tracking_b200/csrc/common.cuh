@@ -168,6 +168,7 @@ struct Params {
   int optMatchPath;      // 0 = choose by window and capacity, 1 = k_match_cta, 2 = k_match, 3 = brute force (match_bf.cu)
   int optFastTileBudget; // bytes of one staged k_fast tile (creation time only)
   int optFrameGraph;     // single-frame calls run through a CUDA graph (default 1)
+  int optQtTight;        // test hook: k_quadtree squeezes its node table at the smallest size its bound allows (results unchanged)
 };
 
 __device__ __forceinline__ const u8* level_ptr(const u8* base, const Params& P, int slot, int l) {

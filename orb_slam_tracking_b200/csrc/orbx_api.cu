@@ -318,6 +318,7 @@ extern "C" int orbx_set_option(orbx_ctx* c, const char* name, int value) {
   else if (n == "match_serial") c->P.optMatchSerial = value != 0;
   else if (n == "match_path") c->P.optMatchPath = value;
   else if (n == "frame_graph") c->P.optFrameGraph = value != 0;
+  else if (n == "qt_tight") c->P.optQtTight = value != 0;
   else return ORBX_ERR_ARG;
   ++c->graphEpoch;
   return ORBX_OK;

@@ -73,6 +73,8 @@ __global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params 
   const int l = blockIdx.x, slot = blockIdx.y, tid = threadIdx.x;
   const LevelInfo& L = P.lv[l];
   const int N = L.quota;
+  // test hook (orbx_set_option "qt_tight"): the smallest table the bound above allows, so that the squeeze runs on ordinary scenes
+  const int nodeCap = P.optQtTight ? min(L.nodeCap, 5 * N + 4 * L.nIni + 8) : L.nodeCap;
   int* lvlCount = P.lvlCount + (size_t)slot * kMaxLevels + l;
   const int M = min((int)P.candCount[(size_t)slot * kMaxLevels + l], L.candCap);
   if (M == 0 || L.nIni < 1) {
@@ -116,7 +118,39 @@ __global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params 
 
   bool phase2 = false;
   for (;;) {
-    const int prevSize = S.size, gen0 = S.gen0, gen1 = S.gen1, G = gen1 - gen0, nNodes = S.nNodes;
+    const int prevSize = S.size, G = S.gen1 - S.gen0;
+    int gen0 = S.gen0, gen1 = S.gen1, nNodes = S.nNodes;
+    // A pass creates at most 4 children per node of the last generation.  If they might not fit into the node table, the
+    // erased nodes are squeezed out first: list order is "alive nodes by descending index", so a renumbering that keeps the
+    // relative order changes nothing, and the last generation (all alive) stays the top of the table.  Afterwards
+    // nNodes == |L| < N and G <= |L|, so nNodes + 4 G < 5 N <= nodeCap (tables.cu): the table cannot overflow, however
+    // slowly a clustered scene lets the list grow.
+    if (gen0 > 0 && nNodes + 4 * G > nodeCap) {
+      for (int i = tid; i < nNodes; i += QT) scan[i] = nCount[i] > 0;
+      __syncthreads();
+      const int alive = cta_scan<QT>(scan, nNodes, S.part);
+      for (int k = tid; k < M; k += QT) cNode[k] = (u32)(scan[cNode[k]] - 1);
+      for (int i = tid; i < nNodes; i += QT) {  // boxes and counts move through the aux table (4 ints per node)
+        const int c = nCount[i];
+        if (c > 0) {
+          const int q = scan[i] - 1;
+          const short4 b = nBox[i];
+          aux[4 * q] = (int)((u32)(unsigned short)b.x | ((u32)(unsigned short)b.y << 16));
+          aux[4 * q + 1] = (int)((u32)(unsigned short)b.z | ((u32)(unsigned short)b.w << 16));
+          aux[4 * q + 2] = c;
+        }
+      }
+      __syncthreads();
+      for (int q = tid; q < alive; q += QT) {
+        const u32 lo = (u32)aux[4 * q], hi = (u32)aux[4 * q + 1];
+        nBox[q] = make_short4((short)(lo & 0xffff), (short)(lo >> 16), (short)(hi & 0xffff), (short)(hi >> 16));
+        nCount[q] = aux[4 * q + 2];
+        nSlot[q] = -1;
+      }
+      if (tid == 0) { S.nNodes = alive; S.gen1 = alive; S.gen0 = alive - G; }
+      __syncthreads();
+      nNodes = alive; gen1 = alive; gen0 = alive - G;
+    }
     // ---- A. nodes to split, in visiting order ----
     int nS;
     if (!phase2) {
@@ -179,7 +213,7 @@ __global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params 
     }
     const int nProc = S.cut + 1;
     const int nNew = scan[nProc - 1];
-    if (nNodes + nNew > L.nodeCap) {
+    if (nNodes + nNew > L.nodeCap) {  // unreachable after the squeeze above; kept as a guard
       if (tid == 0) { atomicMin(P.status + slot, ORBX_ERR_CAPACITY); *lvlCount = 0; }
       return;
     }

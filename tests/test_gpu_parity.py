@@ -292,3 +292,32 @@ def test_clustered_corners_quadtree_capacity(fe, oracle):
         rk, rd, _ = R(im)
         assert len(k) == len(rk) and np.array_equal(k.view(np.uint8), rk.view(np.uint8)) and np.array_equal(d, rd), (nf, patch, len(k), len(rk))
         E.close()
+
+
+@pytest.mark.gpu
+def test_quadtree_node_table_squeeze(fe, oracle):
+    """k_quadtree renumbers its alive nodes when the children of a pass might not fit into the node table (the proven bound of
+    ADVICE r01: afterwards nNodes + 4 G < 5 quota).  With the "qt_tight" option the table is treated as 5 quota + 4 nIni + 8 nodes,
+    so the squeeze runs on ordinary and on clustered scenes, several times per level; the selection and its order must not change."""
+    from orb_slam_tracking_b200 import synth
+    W, H = 640, 480
+    rng = np.random.default_rng(23)
+    ims = [synth.frames(2, W, H)[1], rng.integers(0, 256, (H, W), dtype=np.uint8)]
+    im = np.full((H, W), 120, np.uint8)
+    yy, xx = np.mgrid[0:300, 0:300]
+    board = (((xx // 4) + (yy // 4)) & 1).astype(np.uint8) * 110 + 60
+    im[30:330, 40:340] = np.clip(board.astype(np.int16) + rng.integers(-6, 7, board.shape), 0, 255).astype(np.uint8)
+    im[H - 60:H - 40, W - 70:W - 40] = 30
+    ims.append(im)
+    for nf, (ini, mn) in ((1000, (20, 7)), (300, (20, 7)), (2000, (0, 0))):
+        E = fe.ORBextractor(nf, 1.2, 8, ini, mn, W, H)
+        R = oracle.Extractor(nf, 1.2, 8, ini, mn)
+        for im in ims:
+            E.set_option("qt_tight", 0)
+            k0, d0, _ = E(im)
+            E.set_option("qt_tight", 1)
+            k1, d1, _ = E(im)
+            rk, rd, _ = R(im)
+            assert len(k1) == len(rk) and np.array_equal(k1.view(np.uint8), rk.view(np.uint8)) and np.array_equal(d1, rd), (nf, ini)
+            assert np.array_equal(k0.view(np.uint8), k1.view(np.uint8)) and np.array_equal(d0, d1)
+        E.close()
