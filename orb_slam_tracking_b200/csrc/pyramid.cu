@@ -37,7 +37,7 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
   const int2* __restrict__ ytab = reinterpret_cast<const int2*>(tab + 2 * D.w);  // the table base is 256-byte aligned
   // lane constants
   int a0[4], a1[4], e0[4], e1[4];
-  u32 acoef[4], sel[4];
+  u32 acoef[4];
   int sx0 = 0;
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
@@ -47,11 +47,16 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
     a0[k] = (short)(ac & 0xffff); a1[k] = ac >> 16;
     e0[k] = sx - sx0; e1[k] = min(sx + 1, S.w - 1) - sx0;
     acoef[k] = (u32)ac;                                        // a0 | a1 << 16: the two 16-bit operands of dp2a
-    sel[k] = 0x4400u | (u32)(e0[k] & 7) | ((u32)(e1[k] & 7) << 4);  // bytes (S[sx], S[sx + 1], 0, 0) out of the 8-byte window
   }
+  // one byte permute per PAIR of pixels: bytes (S[sx_k], S[sx_k + 1], S[sx_k+1], S[sx_k+1 + 1]) out of the 8-byte window; dp2a.lo
+  // takes the first two, dp2a.hi the other two
+  u32 sel[2];
+#pragma unroll
+  for (int k = 0; k < 2; ++k)
+    sel[k] = (u32)(e0[2 * k] & 7) | ((u32)(e1[2 * k] & 7) << 4) | ((u32)(e0[2 * k + 1] & 7) << 8) | ((u32)(e1[2 * k + 1] & 7) << 12);
+
   const int A = sx0 & ~3, sh = 8 * (sx0 & 3);
   const bool need3 = (sx0 & 3) + e1[3] >= 8;
-  const u8* __restrict__ colp = src + A;
 
   // WIDE: scale factors above 2 spread a lane's taps over more than the 8 bytes the permutes can reach -> byte loads
   // horizontally interpolated row r, pre-shifted: (S[sx] * a0 + S[sx + 1] * a1) >> 4; the two taps are adjacent source
@@ -63,14 +68,16 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
       for (int k = 0; k < 4; ++k) hs[k] = ((u32)__ldg(rowp + e0[k]) * (u32)a0[k] + (u32)__ldg(rowp + e1[k]) * (u32)a1[k]) >> 4;
       return;
     }
-    const u32* rp = reinterpret_cast<const u32*>(colp + r * S.pitch);
+    const u32* rp = reinterpret_cast<const u32*>(src + (u32)(A + r * S.pitch));  // uniform base + 32-bit offset
     const u32 w0 = __ldg(rp), w1 = __ldg(rp + 1), w2 = need3 ? __ldg(rp + 2) : 0u;
     const u32 q0 = __funnelshift_r(w0, w1, sh), q1 = __funnelshift_r(w1, w2, sh);
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      u32 d;
-      asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(acoef[k]), "r"(__byte_perm(q0, q1, sel[k])), "r"(0u));
-      hs[k] = d >> 4;
+    for (int k = 0; k < 2; ++k) {
+      const u32 taps = __byte_perm(q0, q1, sel[k]);
+      u32 d0, d1;
+      asm("dp2a.lo.u32.u32 %0, %1, %2, %3;" : "=r"(d0) : "r"(acoef[2 * k]), "r"(taps), "r"(0u));
+      asm("dp2a.hi.u32.u32 %0, %1, %2, %3;" : "=r"(d1) : "r"(acoef[2 * k + 1]), "r"(taps), "r"(0u));
+      hs[2 * k] = d0 >> 4; hs[2 * k + 1] = d1 >> 4;
     }
   };
 
@@ -101,10 +108,16 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
     const u32 B0 = (u32)yt.y << 16, B1 = (u32)yt.y & 0xffff0000u;
     if (r0 != rHave) hrow(r0, hHave);
     hrow(r1, hNew);  // r1 == r0 only where the row loop clips (never when shrinking): the row is simply interpolated again
-    u32 v[4];
+    // (umulhi(B0, h0) + umulhi(B1, h1) + 2) >> 2 per pixel (<= 255): the products (<= 1020) of two pixels are put side by side in
+    // 16-bit halves first, so one add and one shift serve a pixel pair and the final permute picks bytes 0 and 2 of each pair
+    u32 s[2];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) v[k] = (__umulhi(B0, hHave[k]) + __umulhi(B1, hNew[k]) + 2u) >> 2;  // <= 255
-    *reinterpret_cast<u32*>(dp) = __byte_perm(__byte_perm(v[0], v[1], 0x0040), __byte_perm(v[2], v[3], 0x0040), 0x5410);
+    for (int k = 0; k < 2; ++k) {
+      const u32 x = __byte_perm(__umulhi(B0, hHave[2 * k]), __umulhi(B0, hHave[2 * k + 1]), 0x5410);
+      const u32 y = __byte_perm(__umulhi(B1, hNew[2 * k]), __umulhi(B1, hNew[2 * k + 1]), 0x5410);
+      s[k] = (x + y + 0x00020002u) >> 2;
+    }
+    *reinterpret_cast<u32*>(dp) = __byte_perm(s[0], s[1], 0x6420);
     dp += D.pitch;
     rHave = r1;
   };
