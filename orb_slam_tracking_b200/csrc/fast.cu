@@ -87,6 +87,24 @@ __device__ __forceinline__ u32 word_at(u32 wl, u32 wc, u32 wr) {
 }
 
 
+// ballot over "x & m != 0": one LOP3 with a predicate result in front of the vote
+__device__ __forceinline__ u32 ballot_bits(u32 x, u32 m) {
+  u32 b;
+  asm volatile("{\n .reg .pred p;\n .reg .b32 t;\n and.b32 t, %1, %2;\n setp.ne.u32 p, t, 0;\n vote.sync.ballot.b32 %0, p, 0xffffffff;\n}\n"
+               : "=r"(b) : "r"(x), "r"(m));
+  return b;
+}
+
+// A shared-memory pointer the compiler must keep in a register: without this it recomputes list bases such as
+// warp * segment length + offset (a constant-bank load, a multiply and an add) in front of every access in the chunk loops.
+template <typename T>
+__device__ __forceinline__ T* keep_shared(T* p) {
+  u32 a = (u32)__cvta_generic_to_shared(p);
+  asm volatile("" : "+r"(a));
+  return reinterpret_cast<T*>(__cvta_shared_to_generic((size_t)a));
+}
+__device__ __forceinline__ int keep(int v) { asm volatile("" : "+r"(v)); return v; }
+
 struct Row3 { u32 l, c, r; };  // words g-1, g, g+1 of one staged row
 __device__ __forceinline__ Row3 load3(const u32* __restrict__ row, int g) { return Row3{row[g - 1], row[g], row[g + 1]}; }
 
@@ -224,22 +242,24 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
       }
     }
     __syncwarp();
-    // append the alive pixels: one ballot per byte position
-    const u32 b0 = __ballot_sync(0xffffffffu, alive & 0x80u), b1 = __ballot_sync(0xffffffffu, alive & 0x8000u);
-    const u32 b2 = __ballot_sync(0xffffffffu, alive & 0x800000u), b3 = __ballot_sync(0xffffffffu, alive & 0x80000000u);
-    const int n0 = nP + __popc(b0), n1 = n0 + __popc(b1), n2 = n1 + __popc(b2);
+    // append the alive pixels: a lane's pixels (0..4) take consecutive entries; the lane offsets are the prefix sum of the
+    // counts, from three ballots over the bits of the count
+    const int c = __popc(alive);  // alive holds bits 7, 15, 23, 31 only
+    const u32 c0 = ballot_bits((u32)c, 1u), c1 = ballot_bits((u32)c, 2u), c2 = ballot_bits((u32)c, 4u);
+    unsigned short* q = S.segP + (nP + __popc(c0 & lt) + 2 * __popc(c1 & lt) + 4 * __popc(c2 & lt));
+    nP += __popc(c0) + 2 * __popc(c1) + 4 * __popc(c2);
     const u32 pe = ((e & 0x7f00u) << 1) | ((e & 0x7fu) << 2);  // row << 9 | 4 * word
-    if (alive & 0x80u) S.segP[nP + __popc(b0 & lt)] = (unsigned short)pe;
-    if (alive & 0x8000u) S.segP[n0 + __popc(b1 & lt)] = (unsigned short)(pe + 1);
-    if (alive & 0x800000u) S.segP[n1 + __popc(b2 & lt)] = (unsigned short)(pe + 2);
-    if (alive & 0x80000000u) S.segP[n2 + __popc(b3 & lt)] = (unsigned short)(pe + 3);
-    nP = n2 + __popc(b3);
+    if (alive & 0x80u) *q++ = (unsigned short)pe;
+    if (alive & 0x8000u) *q++ = (unsigned short)(pe + 1);
+    if (alive & 0x800000u) *q++ = (unsigned short)(pe + 2);
+    if (alive & 0x80000000u) *q = (unsigned short)(pe + 3);
   }
   __syncwarp();
   // ---- phase P2: exact segment-test value of the surviving pixels (ring offsets in cv::FAST order).  The pixel list is
   // compacted IN PLACE to the corners (m > t; a chunk's survivors land at or before the chunk): only they own an m-map entry,
   // so only they take part in the maximum search and in the clearing ----
   const u8* sImg = reinterpret_cast<const u8*>(S.imgW);
+  const int SB1 = keep(SB), SB2 = keep(2 * SB), SB3 = keep(3 * SB);  // row offsets of the ring, held in registers over the chunk loop
   int nC = 0;
   for (int i0 = 0; i0 < nP; i0 += 32) {
     const int i = i0 + lane;
@@ -251,10 +271,11 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
       const u8* p = sImg + ry * SB + b;
       const u32 vb = ((256u - (u32)p[0]) << 16) | ((u32)p[0] + 256u);
       u32 x[16];
-      x[0] = ring_pack(vb, p[3 * SB]); x[1] = ring_pack(vb, p[3 * SB + 1]); x[2] = ring_pack(vb, p[2 * SB + 2]); x[3] = ring_pack(vb, p[SB + 3]);
-      x[4] = ring_pack(vb, p[3]); x[5] = ring_pack(vb, p[-SB + 3]); x[6] = ring_pack(vb, p[-2 * SB + 2]); x[7] = ring_pack(vb, p[-3 * SB + 1]);
-      x[8] = ring_pack(vb, p[-3 * SB]); x[9] = ring_pack(vb, p[-3 * SB - 1]); x[10] = ring_pack(vb, p[-2 * SB - 2]); x[11] = ring_pack(vb, p[-SB - 3]);
-      x[12] = ring_pack(vb, p[-3]); x[13] = ring_pack(vb, p[SB - 3]); x[14] = ring_pack(vb, p[2 * SB - 2]); x[15] = ring_pack(vb, p[3 * SB - 1]);
+      const u8 *pa1 = p + SB1, *pa2 = p + SB2, *pa3 = p + SB3, *pb1 = p - SB1, *pb2 = p - SB2, *pb3 = p - SB3;
+      x[0] = ring_pack(vb, pa3[0]); x[1] = ring_pack(vb, pa3[1]); x[2] = ring_pack(vb, pa2[2]); x[3] = ring_pack(vb, pa1[3]);
+      x[4] = ring_pack(vb, p[3]); x[5] = ring_pack(vb, pb1[3]); x[6] = ring_pack(vb, pb2[2]); x[7] = ring_pack(vb, pb3[1]);
+      x[8] = ring_pack(vb, pb3[0]); x[9] = ring_pack(vb, pb3[-1]); x[10] = ring_pack(vb, pb2[-2]); x[11] = ring_pack(vb, pb1[-3]);
+      x[12] = ring_pack(vb, p[-3]); x[13] = ring_pack(vb, pa1[-3]); x[14] = ring_pack(vb, pa2[-2]); x[15] = ring_pack(vb, pa3[-1]);
       const int m = arc_value(x);
       corner = m > t;
       if (corner) S.mm[ry * SB + b] = (u8)m;
@@ -363,9 +384,10 @@ __global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k_fast(const __g
   __shared__ __align__(8) u64 sBar[2];
   __shared__ int sCellIni[32];
   const int tid = threadIdx.x;
-  u8* const sMm = smem + kFastStages * P.fastTileMax;
-  u32* const sSegW = reinterpret_cast<u32*>(sMm + P.fastTileMax) + (tid >> 5) * P.fastSegW;
-  unsigned short* const sSegP = reinterpret_cast<unsigned short*>(reinterpret_cast<u32*>(sMm + P.fastTileMax) + kFastWarps * P.fastSegW) + (tid >> 5) * P.fastSegP;
+  u8* const sMm = keep_shared(smem + kFastStages * P.fastTileMax);
+  u32* const sSegW = keep_shared(reinterpret_cast<u32*>(sMm + P.fastTileMax) + (tid >> 5) * P.fastSegW);
+  unsigned short* const sSegP =
+      keep_shared(reinterpret_cast<unsigned short*>(reinterpret_cast<u32*>(sMm + P.fastTileMax) + kFastWarps * P.fastSegW) + (tid >> 5) * P.fastSegP);
 
   {
     uint4* z = reinterpret_cast<uint4*>(sMm);  // the m-map starts out zero and every run leaves it zero
@@ -410,7 +432,7 @@ __global__ void __launch_bounds__(kFastThreads, kFastCtasPerSm) k_fast(const __g
     if (tid < 32) sCellIni[tid] = 0;
     const StripDesc d = load_desc(strip);
     StripCtx S;
-    S.imgW = reinterpret_cast<const u32*>(smem + buf * P.fastTileMax);
+    S.imgW = keep_shared(reinterpret_cast<const u32*>(smem + buf * P.fastTileMax));
     S.mm = sMm; S.segW = sSegW; S.segP = sSegP; S.cellIni = sCellIni;
     S.SB = d.SB; S.SW = S.SB >> 2;
     S.bLo = d.bLo; S.bHi = d.bHi; S.nR = d.nR;
