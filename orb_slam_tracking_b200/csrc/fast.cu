@@ -73,10 +73,15 @@ __device__ __forceinline__ u32 ring_pack(u32 base, u32 p) { return p * 0xFFFFu +
 // the exact segment-test value, whose comparison with t decides.
 //   t < 128  (HI = 0): K = (127 - t) * 0x01010101; (x & 0x7f) + K carries into bit 7 iff (x & 0x7f) > t, and x >= 128 > t.
 //   t >= 128 (HI = 1): K = (255 - t) * 0x01010101; x > t iff bit 7 of x is set and (x & 0x7f) + K carries.
+// Three instructions, spelled out as lop3 so that they stay three: (a | b) & 0x7f.., + K, and the combination with a | b.
 template <int HI>
 __device__ __forceinline__ u32 any_gt(u32 a, u32 b, u32 K) {
-  const u32 s = ((a | b) & 0x7f7f7f7fu) + K;
-  return HI ? s & (a | b) : s | a | b;
+  u32 x, r;
+  asm("lop3.b32 %0, %1, %2, 0x7f7f7f7f, 0xa8;" : "=r"(x) : "r"(a), "r"(b));            // (a | b) & 0x7f7f7f7f
+  const u32 s = x + K;
+  if (HI) asm("lop3.b32 %0, %1, %2, %3, 0xa8;" : "=r"(r) : "r"(a), "r"(b), "r"(s));    // (a | b) & s
+  else asm("lop3.b32 %0, %1, %2, %3, 0xfe;" : "=r"(r) : "r"(a), "r"(b), "r"(s));       // a | b | s
+  return r;
 }
 // 4 bytes starting at byte offset 4g + DX (DX in [-3, 3]) given the words g-1, g, g+1 of a staged row
 template <int DX>
@@ -195,13 +200,16 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
       u32 m0 = interior_mask(g, S.bLo, S.bHi), m1 = interior_mask(g + 1, S.bLo, S.bHi);
       if (RETRY) { m0 &= cell_mask(S, g, cells); m1 &= cell_mask(S, g + 1, cells); }
       const bool act = (m0 | m1) != 0;
-      for (int r = warp; r < S.nR; r += kFastWarps) {
+      // one pointer and one list-entry stem walk down the warp's rows: e = row << 8 | word (a word index is below 128)
+      const u32* p = S.imgW + (warp + 3) * SW + g;
+      const int pStep = keep(kFastWarps * SW), o3 = keep(3 * SW);
+      u32 e = ((u32)(warp + 3) << 8) + (u32)g;
+      for (int r = warp; r < S.nR; r += kFastWarps, p += pStep, e += (u32)kFastWarps << 8) {
         u32 a0 = 0, a1 = 0;
         if (act) {
-          const u32* p = S.imgW + (r + 3) * SW + g;
           const uint2 c = *reinterpret_cast<const uint2*>(p);
-          const uint2 n = *reinterpret_cast<const uint2*>(p - 3 * SW);
-          const uint2 s = *reinterpret_cast<const uint2*>(p + 3 * SW);
+          const uint2 n = *reinterpret_cast<const uint2*>(p - o3);
+          const uint2 s = *reinterpret_cast<const uint2*>(p + o3);
           const u32 l = p[-1], q = p[2];
           a0 = m0 & any_gt<MODE>(__vabsdiffu4(c.x, n.x), __vabsdiffu4(c.x, s.x), K);
           a1 = m1 & any_gt<MODE>(__vabsdiffu4(c.y, n.y), __vabsdiffu4(c.y, s.y), K);
@@ -209,7 +217,6 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
           a1 &= any_gt<MODE>(__vabsdiffu4(c.y, word_at<3>(c.x, c.y, q)), __vabsdiffu4(c.y, word_at<-3>(c.x, c.y, q)), K);
         }
         const u32 b0 = __ballot_sync(0xffffffffu, a0 != 0), b1 = __ballot_sync(0xffffffffu, a1 != 0);
-        const u32 e = ((u32)(r + 3) << 8) | (u32)g;
         if (a0) S.segW[nW + __popc(b0 & lt)] = a0 | e;
         nW += __popc(b0);
         if (a1) S.segW[nW + __popc(b1 & lt)] = a1 | (e + 1);
@@ -320,8 +327,17 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
   // ---- phase P4: the keypoints of this run go to the level's candidate list ----
   // ComputeKeyPointsOld drops the iniThFAST keypoints of a cell that has at most retryMax of them: its emission waits for
   // the cell counts of all warps (after the barrier) and compacts the warp's peak list first.
+  // The warp's keypoints take consecutive slots of the candidate list: ONE global atomic per warp.  It is issued before the
+  // barrier and its result is used after it, so the round trip to L2 (about a microsecond) runs beside the barrier wait; the
+  // keypoints are written after the barrier -- a warp's peaks come from its own pixel list, whose m-map entries only this warp
+  // clears (below), so they are still in place.
   const bool deferred = S.retryMax > 0 && !RETRY;
-  auto emit = [&]() {
+  u32 k0 = 0;
+  auto reserve = [&]() {
+    if (nK > 0 && lane == 0) k0 = atomicAdd(P.candCount + (size_t)S.slot * kMaxLevels + S.level, (u32)nK);
+  };
+  if (!deferred) reserve();
+  __syncthreads();  // every neighbour read of the m-map is done
   if (deferred) {
     int kept = 0;
     for (int i0 = 0; i0 < nK; i0 += 32) {
@@ -340,12 +356,11 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
       __syncwarp();
     }
     nK = kept;
+    reserve();
   }
   if (nK > 0) {
     const size_t co = (size_t)S.slot * P.candTotal + S.candOff;
     const u8* rootTab = P.rootTab + S.rootTabOff;
-    u32 k0 = 0;  // one global atomic per warp: its keypoints take consecutive slots
-    if (lane == 0) k0 = atomicAdd(P.candCount + (size_t)S.slot * kMaxLevels + S.level, (u32)nK);
     k0 = __shfl_sync(0xffffffffu, k0, 0);
     if (k0 + (u32)nK > (u32)S.candCap) {
       if (lane == 0) atomicMin(P.status + S.slot, ORBX_ERR_CAPACITY);
@@ -364,10 +379,7 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
       }
     }
   }
-  };
-  if (!deferred) emit();
-  __syncthreads();  // every neighbour read of the m-map is done
-  if (deferred) emit();
+  __syncwarp();
   for (int i = lane; i < nP; i += 32) {  // the m-map entries of this run are cleared
     const int e = S.segP[i];
     S.mm[(e >> 9) * SB + (e & 511)] = 0;
