@@ -159,13 +159,13 @@ struct StripCtx {
   int orderBits;          // bits per coordinate of the emission-order key
 };
 
-// bytes of word g (bit 7 each) that lie inside [bLo, bHi)
+// bytes of word g (bit 7 each) that lie inside [bLo, bHi): the low max(bLo - 4g, 0) and the high max(4g + 4 - bHi, 0) bytes are cut
+// off by two shifts (PTX shifts by 32 or more give 0, which is what a word outside the interval needs)
 __device__ __forceinline__ u32 interior_mask(int g, int bLo, int bHi) {
-  u32 m = 0x80808080u;
-  if (4 * g + 4 <= bLo || 4 * g >= bHi) return 0u;
-  if (4 * g < bLo) m &= 0xffffffffu << (8 * (bLo - 4 * g));
-  if (4 * g + 4 > bHi) m &= 0xffffffffu >> (8 * (4 * g + 4 - bHi));
-  return m;
+  u32 lo, hi;
+  asm("shl.b32 %0, %1, %2;" : "=r"(lo) : "r"(0x80808080u), "r"((u32)max(8 * bLo - 32 * g, 0)));
+  asm("shr.u32 %0, %1, %2;" : "=r"(hi) : "r"(0x80808080u), "r"((u32)max(32 * g + 32 - 8 * bHi, 0)));
+  return lo & hi;
 }
 // bytes of word g (any bits) whose cell is in `cells` (retry run); a word spans at most two cells
 __device__ __forceinline__ u32 cell_mask(const StripCtx& S, int g, u32 cells) {

@@ -36,25 +36,33 @@ struct PackedLess {
   __device__ __forceinline__ bool operator()(const u64& a, const u64& b) const { return (a >> 24) < (b >> 24); }
 };
 
-// In-place inclusive scan of a[0..n) by the whole CTA.  Returns the total to every thread.
+// In-place inclusive scan of a[0..n) by the whole CTA.  Returns the total to every thread.  Each thread sums a run of consecutive
+// elements; the per-thread sums are scanned with shuffles inside each warp and the warp totals (at most 16) through part[]:
+// two CTA barriers per scan.
 template <int QT>
 __device__ int cta_scan(int* a, int n, int* part) {
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const int chunk = (n + QT - 1) / QT;
   const int b = min(tid * chunk, n), e = min(b + chunk, n);
   int s = 0;
   for (int i = b; i < e; ++i) s += a[i];
-  part[tid] = s;
-  __syncthreads();
-  for (int off = 1; off < QT; off <<= 1) {
-    const int v = tid >= off ? part[tid - off] : 0;
-    __syncthreads();
-    part[tid] += v;
-    __syncthreads();
+  int v = s;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += t;
   }
-  int run = tid ? part[tid - 1] : 0;
+  if (lane == 31) part[w] = v;
+  __syncthreads();
+  int base = 0, total = 0;
+#pragma unroll
+  for (int i = 0; i < QT / 32; ++i) {
+    const int p = part[i];
+    if (i < w) base += p;
+    total += p;
+  }
+  int run = base + v - s;
   for (int i = b; i < e; ++i) { run += a[i]; a[i] = run; }
-  const int total = part[QT - 1];
   __syncthreads();
   return total;
 }
