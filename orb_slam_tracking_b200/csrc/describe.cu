@@ -186,7 +186,10 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, ORBX_DESC_CTAS) k_describe(
 #pragma unroll
       for (int rb = 0; rb < 33; rb += 3) {
         if (rb + lr < kDiscRows) {
-          const u32 word = pw[rb * kPatchWords] & ((((sDD[rb + lr] - apk) & 0x80808080u) >> 7) * 255u);
+          // bit 7 of each byte of (0x80 | umax) - |u| says "inside the disc"; the byte permute in sign-replication mode widens it to 0xff / 0x00
+          u32 inside;  // (__byte_perm ignores the replication bit of the selector nibbles: PTX prmt spelled out)
+          asm("prmt.b32 %0, %1, 0, 0xba98;" : "=r"(inside) : "r"(sDD[rb + lr] - apk));
+          const u32 word = pw[rb * kPatchWords] & inside;
           asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(m10) : "r"(word), "r"(upk), "r"(m10));
           T = __dp4a(word, 0x01010101u, T);
           U = __dp4a(word, (u32)rb * 0x01010101u, U);
