@@ -66,15 +66,20 @@ __global__ void __launch_bounds__(kBlurWarps * 32) k_blur(const __grid_constant_
 #pragma unroll
   for (int k = 0; k < 5; ++k) { pr[k][0] = pr[k][1] = pr[k][2] = pr[k][3] = 0; }
   hl[0] = hl[1] = hl[2] = hl[3] = 0;
-  const u8* __restrict__ colp = src + A;
+  // The lane's column of the source and of the destination as pointers the compiler has to keep (and walk down the rows):
+  // left alone it rebuilds every row address from the parameter block (a constant-bank load and two 64-bit additions per row).
+  const u8* colp = src + A;
+  u8* dcol = dst + xw;
+  int pitch = L.pitch;
+  asm volatile("" : "+l"(colp), "+l"(dcol), "+r"(pitch));
   for (int rb = 0; rb < kTH + 6; rb += kRB) {
     if (t.y0 + rb - 6 >= L.h) break;  // nothing left to emit in this strip
     u32 v0[kRB], v1[kRB];
     const int yb = t.y0 + rb - 3;
     if (yb >= 0 && yb + kRB <= L.h) {  // all rows of the block inside the level: one pointer walks down
-      const u8* rp = colp + yb * L.pitch;
+      const u8* rp = colp + yb * pitch;
 #pragma unroll
-      for (int k = 0; k < kRB; ++k, rp += L.pitch) {
+      for (int k = 0; k < kRB; ++k, rp += pitch) {
         v0[k] = __ldg(reinterpret_cast<const u32*>(rp));
         v1[k] = two ? __ldg(reinterpret_cast<const u32*>(rp) + 1) : 0u;
       }
@@ -85,13 +90,13 @@ __global__ void __launch_bounds__(kBlurWarps * 32) k_blur(const __grid_constant_
         y = y < 0 ? -y : y;
         y = y >= L.h ? 2 * (L.h - 1) - y : y;
         y = max(y, 0);  // rows beyond the halo of the last strip are never used
-        const u32* rp = reinterpret_cast<const u32*>(colp + y * L.pitch);
+        const u32* rp = reinterpret_cast<const u32*>(colp + y * pitch);
         v0[k] = __ldg(rp);
         v1[k] = two ? __ldg(rp + 1) : 0u;
       }
     }
     const int nEmit = emit ? L.h - (t.y0 + rb - 6) : 0;  // rows k < nEmit of the block are inside the level
-    u8* dp = dst + (t.y0 + rb - 6) * L.pitch + xw;
+    u8* dp = dcol + (t.y0 + rb - 6) * pitch;
 #pragma unroll
     for (int k = 0; k < kRB; ++k) {
       const u32 w1 = __byte_perm(v0[k], v1[k], S);
@@ -116,9 +121,9 @@ __global__ void __launch_bounds__(kBlurWarps * 32) k_blur(const __grid_constant_
         hl[j] = nn[j];
       }
       if (k < nEmit && (k >= 6 || rb > 0)) {
-        *reinterpret_cast<u32*>(dp) = __byte_perm(__byte_perm(px[0], px[1], 0x0062), __byte_perm(px[2], px[3], 0x0062), 0x5410);
+        __stcg(reinterpret_cast<u32*>(dp), __byte_perm(__byte_perm(px[0], px[1], 0x0062), __byte_perm(px[2], px[3], 0x0062), 0x5410));
       }
-      dp += L.pitch;
+      dp += pitch;
     }
   }
 }
