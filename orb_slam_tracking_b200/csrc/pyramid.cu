@@ -30,8 +30,11 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
   const int dy0 = (blockIdx.y * kResizeWarps + threadIdx.y) * rows;
   const int dx0 = (blockIdx.x * 32 + lane) * 4;
   if (dy0 >= D.h) return;
-  const u8* __restrict__ src = level_ptr((const u8*)P.pyr, P, slot, l - 1);
+  const u8* src = level_ptr((const u8*)P.pyr, P, slot, l - 1);
   u8* dst = level_ptr(P.pyr, P, slot, l);
+  // bases and pitches the compiler has to keep in registers (it reloaded them from the parameter block for every row)
+  int sPitch = S.pitch, dPitch = D.pitch;
+  asm volatile("" : "+l"(src), "+l"(dst), "+r"(sPitch), "+r"(dPitch));
   const int* xofs = tab;
   const int* xcoef = tab + D.w;
   const int2* __restrict__ ytab = reinterpret_cast<const int2*>(tab + 2 * D.w);  // the table base is 256-byte aligned
@@ -63,12 +66,12 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
   // bytes, so one byte permute puts them side by side and one dp2a (2 x u16 . 2 x u8) is the whole interpolation
   auto hrow = [&](int r, u32 (&hs)[4]) {
     if (WIDE) {
-      const u8* rowp = src + r * S.pitch + sx0;
+      const u8* rowp = src + r * sPitch + sx0;
 #pragma unroll
       for (int k = 0; k < 4; ++k) hs[k] = ((u32)__ldg(rowp + e0[k]) * (u32)a0[k] + (u32)__ldg(rowp + e1[k]) * (u32)a1[k]) >> 4;
       return;
     }
-    const u32* rp = reinterpret_cast<const u32*>(src + (u32)(A + r * S.pitch));  // uniform base + 32-bit offset
+    const u32* rp = reinterpret_cast<const u32*>(src + (u32)(A + r * sPitch));  // base + 32-bit offset
     const u32 w0 = __ldg(rp), w1 = __ldg(rp + 1), w2 = need3 ? __ldg(rp + 2) : 0u;
     const u32 q0 = __funnelshift_r(w0, w1, sh), q1 = __funnelshift_r(w1, w2, sh);
 #pragma unroll
@@ -91,7 +94,7 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
     const int total = (rLast - rFirst + 1) * nLines;
     for (int i = lane; i < total; i += 32) {
       const int r = i / nLines, ln = i - r * nLines;
-      asm volatile("prefetch.global.L2 [%0];" ::"l"(src + (size_t)(rFirst + r) * S.pitch + xb + 128 * ln));
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(src + (size_t)(rFirst + r) * sPitch + xb + 128 * ln));
     }
   }
   // Output row dy from the horizontally interpolated source rows r0, r1.  At scale 1.2 row r1 of dy is row r0 of dy + 1 five
@@ -100,7 +103,7 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
   int rHave = -1;
   // pitch = width rounded up to 128 and a warp covers 128 columns: every lane's 4-pixel group is inside the row allocation,
   // lanes beyond the level's width write row padding that nothing reads
-  u8* dp = dst + (size_t)dy0 * D.pitch + dx0;
+  u8* dp = dst + (size_t)dy0 * dPitch + dx0;
   auto out_row = [&](int dy, u32 (&hHave)[4], u32 (&hNew)[4]) {
     const int2 yt = __ldg(ytab + dy);
     const int r0 = yt.x & 0xffff, r1 = (int)((u32)yt.x >> 16);
@@ -117,8 +120,8 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
       const u32 y = __byte_perm(__umulhi(B1, hNew[2 * k]), __umulhi(B1, hNew[2 * k + 1]), 0x5410);
       s[k] = (x + y + 0x00020002u) >> 2;
     }
-    *reinterpret_cast<u32*>(dp) = __byte_perm(s[0], s[1], 0x6420);
-    dp += D.pitch;
+    __stcg(reinterpret_cast<u32*>(dp), __byte_perm(s[0], s[1], 0x6420));
+    dp += dPitch;
     rHave = r1;
   };
   u32 hA[4] = {0, 0, 0, 0}, hB[4] = {0, 0, 0, 0};
