@@ -34,7 +34,10 @@ constexpr int kGridCols = ORBX_GRID_COLS, kGridRows = ORBX_GRID_ROWS, kGridCells
 #define ORBX_BLUR_TH 124
 #endif
 constexpr int kBlurTW = 120, kBlurTH = ORBX_BLUR_TH;  // k_blur: output columns x rows per warp strip
-constexpr int kFastWarps = 8;   // warps of a k_fast CTA (its per-warp list segments are sized on the host)
+#ifndef ORBX_FAST_WARPS
+#define ORBX_FAST_WARPS 8
+#endif
+constexpr int kFastWarps = ORBX_FAST_WARPS;   // warps of a k_fast CTA (its per-warp list segments are sized on the host)
 constexpr int kMaxCellDim = 80;  // cell ROI (wCell + 6) is < 76 for every image size
 
 struct LevelInfo {
