@@ -90,10 +90,11 @@ int orbx_sincosf_probe(orbx_ctx* ctx, const float* y, long long n, float* sin_ou
  * whose cells are wider than 480 tested columns. */
 int orbx_set_keypoint_policy(orbx_ctx* ctx, int policy);
 /* Schedule options of a context (they never change results).  The environment is read ONCE, in orbx_create
- * (ORBX_SINGLE_STREAM, ORBX_RUN_PARTS, ORBX_LANES, ORBX_RESIZE_ROWS, ORBX_MATCH_SERIAL, ORBX_FAST_TILE); this call
+ * (ORBX_SINGLE_STREAM, ORBX_RUN_PARTS, ORBX_LANES, ORBX_RESIZE_ROWS, ORBX_MATCH_SERIAL, ORBX_FAST_TILE, ORBX_PYRAMID_CHAIN); this call
  * changes an option of a live context: name = "single_stream" | "run_parts" | "lanes" | "resize_rows" | "match_serial" |
  * "match_path" (0 auto, 1 k_match_cta, 2 k_match, 3 brute force) | "frame_graph" (1: single-frame calls use a CUDA graph) |
- * "qt_tight" (test hook: the quadtree squeezes erased nodes out of its table at the smallest size its bound allows).
+ * "qt_tight" (test hook: the quadtree squeezes erased nodes out of its table at the smallest size its bound allows) |
+ * "pyramid_chain" (1, default: batches of at most 2 frames build their pyramids in one launch with a grid barrier between levels).
  * No launch path reads the environment.  Returns ORBX_ERR_ARG for an unknown name. */
 int orbx_set_option(orbx_ctx* ctx, const char* name, int value);
 

@@ -147,6 +147,8 @@ struct Params {
   u8* lvlDesc;         // 32 bytes each
   int* lvlCount;       // [slot][kMaxLevels]
   int* status;         // [slot]  sticky error flags of the slot (ORBX_ERR_*), 0 = ok
+  u32* gridBar;        // arrival counter of k_pyramid_chain's grid barrier
+  int smCount;         // SMs of the context's device
   // packed outputs [slot][nfeatures]
   orbx_keypoint* outKp;
   u8* outDesc;
@@ -171,6 +173,7 @@ struct Params {
   int optMatchPath;      // 0 = choose by window and capacity, 1 = k_match_cta, 2 = k_match, 3 = brute force (match_bf.cu)
   int optFastTileBudget; // bytes of one staged k_fast tile (creation time only)
   int optFrameGraph;     // single-frame calls run through a CUDA graph (default 1)
+  int optPyramidChain;   // batches of at most 2 frames build the pyramid in one launch (default 1)
   int optQtTight;        // test hook: k_quadtree squeezes its node table at the smallest size its bound allows (results unchanged)
 };
 

@@ -95,6 +95,7 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   P.optMatchSerial = env_int("ORBX_MATCH_SERIAL", 0) != 0;
   P.optMatchPath = env_int("ORBX_MATCH_PATH", 0);
   P.optFrameGraph = env_int("ORBX_FRAME_GRAPH", 1) != 0;
+  P.optPyramidChain = env_int("ORBX_PYRAMID_CHAIN", 1) != 0;
   P.optFastTileBudget = std::max(4096, env_int("ORBX_FAST_TILE", 15360));
   std::memcpy(P.umax, c->T.umax, sizeof(P.umax));
   std::vector<StripDesc> strips;
@@ -166,6 +167,8 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   if ((rc = dalloc(c, &P.lvlDesc, K * 32))) return rc;
   if ((rc = dalloc(c, &P.lvlCount, B * kMaxLevels))) return rc;
   if ((rc = dalloc(c, &P.status, B))) return rc;
+  if ((rc = dalloc(c, &P.gridBar, 1))) return rc;
+  if (cudaDeviceGetAttribute(&P.smCount, cudaDevAttrMultiProcessorCount, device) != cudaSuccess) return ORBX_ERR_CUDA;
   if ((rc = dalloc(c, &P.outKp, K))) return rc;
   if ((rc = dalloc(c, &P.outDesc, K * 32))) return rc;
   if ((rc = dalloc(c, &P.outN, B))) return rc;
@@ -319,6 +322,7 @@ extern "C" int orbx_set_option(orbx_ctx* c, const char* name, int value) {
   else if (n == "match_path") c->P.optMatchPath = value;
   else if (n == "frame_graph") c->P.optFrameGraph = value != 0;
   else if (n == "qt_tight") c->P.optQtTight = value != 0;
+  else if (n == "pyramid_chain") c->P.optPyramidChain = value != 0;
   else return ORBX_ERR_ARG;
   ++c->graphEpoch;
   return ORBX_OK;

@@ -20,15 +20,23 @@
 namespace orbx {
 
 constexpr int kResizeRows = 16, kResizeWarps = 4;
+constexpr int kChainMaxSlots = 2;  // batches up to this size build their pyramids in one launch (k_pyramid_chain)
 
 // tab: xofs[dw] | xcoef[dw] (a0 | a1 << 16) | per output row { r0 | r1 << 16, b0 | b1 << 16 }
-template <bool WIDE>
-__global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_constant__ Params P, int l, const int* __restrict__ tab, int rows) {
+// source words of the row pass: read-only for the whole launch in k_resize (non-coherent path); in k_pyramid_chain the source level
+// was written earlier in the SAME launch by other CTAs, so its loads go to L2 (ld.global.cg), where those stores are
+template <bool CHAIN>
+__device__ __forceinline__ u32 ld_src(const u32* p) { return CHAIN ? __ldcg(p) : __ldg(p); }
+template <bool CHAIN>
+__device__ __forceinline__ u32 ld_src(const u8* p) { return CHAIN ? (u32)__ldcg(p) : (u32)__ldg(p); }
+
+// One warp: the strip of `rows` output rows from dy0 and 128 output columns from 128 * bx of level l of `slot`.
+template <bool WIDE, bool CHAIN>
+__device__ __forceinline__ void resize_strip(const Params& P, int l, const int* __restrict__ tab, int rows, int bx, int dy0, int slot) {
   const LevelInfo& D = P.lv[l];
   const LevelInfo& S = P.lv[l - 1];
-  const int slot = blockIdx.z, lane = threadIdx.x;
-  const int dy0 = (blockIdx.y * kResizeWarps + threadIdx.y) * rows;
-  const int dx0 = (blockIdx.x * 32 + lane) * 4;
+  const int lane = threadIdx.x;
+  const int dx0 = (bx * 32 + lane) * 4;
   if (dy0 >= D.h) return;
   const u8* src = level_ptr((const u8*)P.pyr, P, slot, l - 1);
   u8* dst = level_ptr(P.pyr, P, slot, l);
@@ -64,16 +72,12 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
   // WIDE: scale factors above 2 spread a lane's taps over more than the 8 bytes the permutes can reach -> byte loads
   // horizontally interpolated row r, pre-shifted: (S[sx] * a0 + S[sx + 1] * a1) >> 4; the two taps are adjacent source
   // bytes, so one byte permute puts them side by side and one dp2a (2 x u16 . 2 x u8) is the whole interpolation
-  auto hrow = [&](int r, u32 (&hs)[4]) {
-    if (WIDE) {
-      const u8* rowp = src + r * sPitch + sx0;
-#pragma unroll
-      for (int k = 0; k < 4; ++k) hs[k] = ((u32)__ldg(rowp + e0[k]) * (u32)a0[k] + (u32)__ldg(rowp + e1[k]) * (u32)a1[k]) >> 4;
-      return;
-    }
+  auto hload = [&](int r, u32 (&w)[3]) {  // the 2 (3) aligned words of source row r that hold this lane's taps
     const u32* rp = reinterpret_cast<const u32*>(src + (u32)(A + r * sPitch));  // base + 32-bit offset
-    const u32 w0 = __ldg(rp), w1 = __ldg(rp + 1), w2 = need3 ? __ldg(rp + 2) : 0u;
-    const u32 q0 = __funnelshift_r(w0, w1, sh), q1 = __funnelshift_r(w1, w2, sh);
+    w[0] = ld_src<CHAIN>(rp); w[1] = ld_src<CHAIN>(rp + 1); w[2] = need3 ? ld_src<CHAIN>(rp + 2) : 0u;
+  };
+  auto hcalc = [&](const u32 (&w)[3], u32 (&hs)[4]) {
+    const u32 q0 = __funnelshift_r(w[0], w[1], sh), q1 = __funnelshift_r(w[1], w[2], sh);
 #pragma unroll
     for (int k = 0; k < 2; ++k) {
       const u32 taps = __byte_perm(q0, q1, sel[k]);
@@ -83,8 +87,48 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
       hs[2 * k] = d0 >> 4; hs[2 * k + 1] = d1 >> 4;
     }
   };
+  auto hrow = [&](int r, u32 (&hs)[4]) {
+    if (WIDE) {
+      const u8* rowp = src + r * sPitch + sx0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) hs[k] = (ld_src<CHAIN>(rowp + e0[k]) * (u32)a0[k] + ld_src<CHAIN>(rowp + e1[k]) * (u32)a1[k]) >> 4;
+      return;
+    }
+    u32 w[3];
+    hload(r, w);
+    hcalc(w, hs);
+  };
 
   const int dyEnd = min(dy0 + rows, D.h);
+  if (CHAIN && !WIDE && rows == 4) {
+    // latency form (k_pyramid_chain): the walk below is a chain of dependent loads per row (row table entry, then source
+    // words); here all four table entries and then all eight source rows are requested before anything is used
+    int2 yt[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) yt[k] = __ldg(ytab + min(dy0 + k, D.h - 1));
+    u32 wa[4][3], wb[4][3];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { hload(yt[k].x & 0xffff, wa[k]); hload((int)((u32)yt[k].x >> 16), wb[k]); }
+    u8* dq = dst + (size_t)dy0 * dPitch + dx0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (dy0 + k < D.h) {
+        u32 h0[4], h1[4], t[2];
+        hcalc(wa[k], h0);
+        hcalc(wb[k], h1);
+        const u32 B0 = (u32)yt[k].y << 16, B1 = (u32)yt[k].y & 0xffff0000u;
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const u32 x = __byte_perm(__umulhi(B0, h0[2 * j]), __umulhi(B0, h0[2 * j + 1]), 0x5410);
+          const u32 y = __byte_perm(__umulhi(B1, h1[2 * j]), __umulhi(B1, h1[2 * j + 1]), 0x5410);
+          t[j] = (x + y + 0x00020002u) >> 2;
+        }
+        __stcg(reinterpret_cast<u32*>(dq), __byte_perm(t[0], t[1], 0x6420));
+      }
+      dq += dPitch;
+    }
+    return;
+  }
   {
     // the strip's source rows are consumed one after the other (a dependent chain of loads per lane): pull its
     // 128-byte lines into L2 up front, one line per lane and round
@@ -129,6 +173,43 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_const
     out_row(dy, hA, hB);
     if (dy + 1 >= dyEnd) break;
     out_row(dy + 1, hB, hA);
+  }
+}
+
+template <bool WIDE>
+__global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_constant__ Params P, int l, const int* __restrict__ tab, int rows) {
+  resize_strip<WIDE, false>(P, l, tab, rows, blockIdx.x, (blockIdx.y * kResizeWarps + threadIdx.y) * rows, blockIdx.z);
+}
+
+// The whole pyramid of a few frames in ONE launch (single-frame latency path): seven dependent launches cost about 10 us each
+// for a frame, most of it launch latency and the short dependent load chain of a nearly empty GPU.  All CTAs are co-resident (the
+// grid is at most one CTA per SM); a level is finished by a grid-wide barrier -- an arrival counter in global memory that the host
+// zeroes in front of the launch -- before the next level reads it.
+struct ResizeTabs { const int* t[kMaxLevels]; };
+__global__ void __launch_bounds__(32 * kResizeWarps) k_pyramid_chain(const __grid_constant__ Params P, const __grid_constant__ ResizeTabs T, int rows,
+                                                                     int nSlots, u32* __restrict__ arrive) {
+  const int warpsTotal = (int)gridDim.x * kResizeWarps, warp0 = (int)blockIdx.x * kResizeWarps + (int)threadIdx.y;
+  for (int l = 1; l < P.nlevels; ++l) {
+    const int nbx = (P.lv[l].w + 127) / 128, nwy = (P.lv[l].h + rows - 1) / rows, perSlot = nbx * nwy;
+    const bool wide = P.lv[l - 1].w > 2 * P.lv[l].w + 1;
+    for (int it = warp0; it < perSlot * nSlots; it += warpsTotal) {
+      const int slot = it / perSlot, r = it - slot * perSlot, wy = r / nbx, bx = r - wy * nbx;
+      if (wide) resize_strip<true, true>(P, l, T.t[l], rows, bx, wy * rows, slot);
+      else resize_strip<false, true>(P, l, T.t[l], rows, bx, wy * rows, slot);
+    }
+    if (l + 1 < P.nlevels) {  // grid barrier: every store of level l is in L2 before any CTA starts level l + 1
+      __syncthreads();
+      if (threadIdx.x == 0 && threadIdx.y == 0) {
+        __threadfence();
+        atomicAdd(arrive, 1u);
+        const u32 want = (u32)l * gridDim.x;
+        u32 seen;
+        do {
+          asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(arrive) : "memory");
+        } while (seen < want);
+      }
+      __syncthreads();
+    }
   }
 }
 
@@ -205,6 +286,18 @@ int launch_ingest(const Params& P, const u8* dense, int nSlots, cudaStream_t st)
 
 int launch_pyramid(const Params& P, const int* const* dTabs, int nSlots, cudaStream_t st) {
   int n = 0;
+  if (nSlots <= kChainMaxSlots && P.optPyramidChain && P.gridBar) {
+    // few frames: one launch for all levels (k_pyramid_chain).  4 rows per warp keep the dependent load chain short; the grid is
+    // what level 1 needs, capped at one CTA per SM so that every CTA is resident (the barrier spins)
+    const int rows = P.optResizeRows > 0 ? P.optResizeRows : 4;
+    const int items = ((P.lv[1].w + 127) / 128) * ((P.lv[1].h + rows - 1) / rows) * nSlots;
+    const int grid = std::max(1, std::min(P.smCount, (items + kResizeWarps - 1) / kResizeWarps));
+    ResizeTabs T;
+    for (int l = 0; l < kMaxLevels; ++l) T.t[l] = l < P.nlevels ? dTabs[l] : nullptr;
+    cudaMemsetAsync(P.gridBar, 0, sizeof(u32), st);
+    k_pyramid_chain<<<grid, dim3(32, kResizeWarps), 0, st>>>(P, T, rows, nSlots, P.gridBar);
+    return 1;
+  }
   for (int l = 1; l < P.nlevels; ++l) {
     dim3 block(32, kResizeWarps);
     // a warp walks its rows one after the other (a dependent chain of loads): with whole batches the SMs are full anyway and

@@ -321,3 +321,30 @@ def test_quadtree_node_table_squeeze(fe, oracle):
             assert len(k1) == len(rk) and np.array_equal(k1.view(np.uint8), rk.view(np.uint8)) and np.array_equal(d1, rd), (nf, ini)
             assert np.array_equal(k0.view(np.uint8), k1.view(np.uint8)) and np.array_equal(d0, d1)
         E.close()
+
+
+@pytest.mark.gpu
+def test_pyramid_chain_equals_levelwise(fe, oracle, synth):
+    """Batches of at most 2 frames build the pyramid in ONE launch (k_pyramid_chain: grid barrier between the levels); larger batches
+    run one k_resize launch per level.  Both must give the oracle's levels, also for scale factors above 2 (the byte-load form of the
+    row pass) and for a batch of 2."""
+    for W, H, sf, nl in ((640, 480, 1.2, 8), (752, 480, 1.2, 8), (611, 403, 1.33, 6), (800, 600, 2.5, 3), (1241, 376, 1.2, 8)):
+        E = fe.ORBextractor(500, sf, nl, 20, 7, W, H, max_batch=2)
+        R = oracle.Extractor(500, sf, nl, 20, 7)
+        imgs = synth.frames(2, W, H, first_pair=5)
+        R(imgs[0])
+        ref = [R.level(l) for l in range(nl)]
+        for chain in (1, 0, 1):
+            E.set_option("pyramid_chain", chain)
+            k, d, _ = E(imgs[0])
+            for l in range(nl):
+                assert np.array_equal(E.pyramid_level(l), ref[l]), (W, H, sf, chain, l)
+        rk, rd, _ = R(imgs[0])
+        assert np.array_equal(k.view(np.uint8), rk.view(np.uint8)) and np.array_equal(d, rd)
+        # a batch of 2 through the chain: slot 1 holds the second image's levels
+        E.set_option("pyramid_chain", 1)
+        out = E.extract_batch(imgs)
+        R(imgs[1])
+        for l in range(nl):
+            assert np.array_equal(E.pyramid_level(l, slot=1), R.level(l)), (W, H, sf, "batch", l)
+        E.close()
