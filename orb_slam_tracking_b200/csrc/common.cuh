@@ -104,6 +104,30 @@ struct PatchMaps {
 };
 __device__ __forceinline__ u32 smem_addr(const void* p) { return (u32)__cvta_generic_to_shared(p); }
 
+// Inclusive prefix sum of one value per thread over a CTA of NT threads (a multiple of 32, at most 1024): shuffles inside the
+// warps, the warp totals through part[NT / 32]; two CTA barriers.  *total receives the sum over the CTA.
+template <int NT>
+__device__ __forceinline__ int cta_prefix_sum(int v, int* part, int* total) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int t = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane >= o) v += t;
+  }
+  if (lane == 31) part[w] = v;
+  __syncthreads();
+  int base = 0, sum = 0;
+#pragma unroll
+  for (int i = 0; i < NT / 32; ++i) {
+    const int p = part[i];
+    if (i < w) base += p;
+    sum += p;
+  }
+  __syncthreads();  // part[] may be reused
+  *total = sum;
+  return base + v;
+}
+
 struct Params {
   int W, H, nlevels, nfeatures, iniTh, minTh, maxBatch;
   int kpStride;        // keypoint slots per frame = max(nfeatures, sum of quotas)

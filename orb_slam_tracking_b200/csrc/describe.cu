@@ -246,9 +246,11 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, ORBX_DESC_CTAS) k_describe(
 }
 
 // ---- output packing: one CTA per slot ----
-constexpr int PK = 256;
+// CTA size PK: 256 threads for whole batches, 1024 for a few frames (a keypoint per thread: the kernel is a chain of dependent
+// loads per keypoint, and a single frame's kernel time is its latency)
+template <int PK>
 __global__ void __launch_bounds__(PK) k_pack(const __grid_constant__ Params P, int lap0, int lap1) {
-  __shared__ int sPart[PK];
+  __shared__ int sPart[PK / 32];
   __shared__ int sOff[kMaxLevels + 1];
   const int slot = blockIdx.x, tid = threadIdx.x;
   if (tid == 0) {
@@ -274,16 +276,9 @@ __global__ void __launch_bounds__(PK) k_pack(const __grid_constant__ Params P, i
       nl += (x >= fl0 && x <= fl1);
     }
   }
-  sPart[tid] = nl;
-  __syncthreads();
-  for (int off = 1; off < PK; off <<= 1) {
-    const int v = tid >= off ? sPart[tid - off] : 0;
-    __syncthreads();
-    sPart[tid] += v;
-    __syncthreads();
-  }
-  int lapBefore = tid ? sPart[tid - 1] : 0;
-  const int nLap = sPart[PK - 1];
+  int nLap;
+  const int lapIncl = cta_prefix_sum<PK>(nl, sPart, &nLap);
+  int lapBefore = lapIncl - nl;
   // pass 2: write
   {
     int l = 0;
@@ -319,7 +314,8 @@ void launch_sincosf_probe(const float* y, long long n, float* sn, float* cs, cud
 int launch_describe(const Params& P, const PatchMaps& M, int nSlots, int lap0, int lap1, cudaStream_t st) {
   dim3 grid((P.kpStride + kKpPerCta - 1) / kKpPerCta, nSlots);
   k_describe<<<grid, kWarpsPerCta * 32, 0, st>>>(P, M);
-  k_pack<<<nSlots, PK, 0, st>>>(P, lap0, lap1);
+  if (nSlots <= 8) k_pack<1024><<<nSlots, 1024, 0, st>>>(P, lap0, lap1);
+  else k_pack<256><<<nSlots, 256, 0, st>>>(P, lap0, lap1);
   return 2;
 }
 

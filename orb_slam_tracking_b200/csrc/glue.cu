@@ -30,12 +30,15 @@ __device__ __forceinline__ void undistort_point(const Params& P, float u, float 
   *ov = (float)__dadd_rn(__dmul_rn(y, fy), cy);
 }
 
-constexpr int GT = 256;
-constexpr int kCellsPerThread = kGridCells / GT;  // 12
+// CTA size GT: 256 threads for whole batches (several CTAs per SM), 1024 for a few frames -- a keypoint per thread for the usual
+// 1000, because the undistortion is a long dependent chain in double and a single frame's kernel time is its latency
 
+template <int GT>
 __global__ void __launch_bounds__(GT) k_glue(const __grid_constant__ Params P) {
+  constexpr int kCellsPerThread = kGridCells / GT;
+  static_assert(kGridCells % GT == 0, "cells per thread");
   __shared__ int sCnt[kGridCells];
-  __shared__ int sPart[GT];
+  __shared__ int sPart[GT / 32];
   const int slot = blockIdx.x, tid = threadIdx.x;
   const int n = P.outN[slot];
   const size_t base = (size_t)slot * P.kpStride;
@@ -59,15 +62,8 @@ __global__ void __launch_bounds__(GT) k_glue(const __grid_constant__ Params P) {
   int loc[kCellsPerThread], s = 0;
 #pragma unroll
   for (int j = 0; j < kCellsPerThread; ++j) { loc[j] = sCnt[tid * kCellsPerThread + j]; s += loc[j]; }
-  sPart[tid] = s;
-  __syncthreads();
-  for (int off = 1; off < GT; off <<= 1) {
-    const int v = tid >= off ? sPart[tid - off] : 0;
-    __syncthreads();
-    sPart[tid] += v;
-    __syncthreads();
-  }
-  int run = tid ? sPart[tid - 1] : 0;
+  int all;
+  int run = cta_prefix_sum<GT>(s, sPart, &all) - s;
 #pragma unroll
   for (int j = 0; j < kCellsPerThread; ++j) {
     const int c = tid * kCellsPerThread + j;
@@ -98,7 +94,8 @@ __global__ void __launch_bounds__(GT) k_glue(const __grid_constant__ Params P) {
 }
 
 int launch_glue(const Params& P, int nSlots, cudaStream_t st) {
-  k_glue<<<nSlots, GT, 0, st>>>(P);
+  if (nSlots <= 8) k_glue<1024><<<nSlots, 1024, 0, st>>>(P);
+  else k_glue<256><<<nSlots, 256, 0, st>>>(P);
   return 1;
 }
 
