@@ -204,23 +204,35 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
       const u32* p = S.imgW + (warp + 3) * SW + g;
       const int pStep = keep(kFastWarps * SW), o3 = keep(3 * SW);
       u32 e = ((u32)(warp + 3) << 8) + (u32)g;
-      for (int r = warp; r < S.nR; r += kFastWarps, p += pStep, e += (u32)kFastWarps << 8) {
-        u32 a0 = 0, a1 = 0;
-        if (act) {
-          const uint2 c = *reinterpret_cast<const uint2*>(p);
-          const uint2 n = *reinterpret_cast<const uint2*>(p - o3);
-          const uint2 s = *reinterpret_cast<const uint2*>(p + o3);
-          const u32 l = p[-1], q = p[2];
-          a0 = m0 & any_gt<MODE>(__vabsdiffu4(c.x, n.x), __vabsdiffu4(c.x, s.x), K);
-          a1 = m1 & any_gt<MODE>(__vabsdiffu4(c.y, n.y), __vabsdiffu4(c.y, s.y), K);
-          a0 &= any_gt<MODE>(__vabsdiffu4(c.x, word_at<3>(l, c.x, c.y)), __vabsdiffu4(c.x, word_at<-3>(l, c.x, c.y)), K);
-          a1 &= any_gt<MODE>(__vabsdiffu4(c.y, word_at<3>(c.x, c.y, q)), __vabsdiffu4(c.y, word_at<-3>(c.x, c.y, q)), K);
-        }
+      // the two pair tests of one word pair of one row (loads and arithmetic only: two rows are in flight per trip of the loop)
+      auto tests = [&](const u32* pp, u32& a0, u32& a1) {
+        const uint2 c = *reinterpret_cast<const uint2*>(pp);
+        const uint2 n = *reinterpret_cast<const uint2*>(pp - o3);
+        const uint2 s = *reinterpret_cast<const uint2*>(pp + o3);
+        const u32 l = pp[-1], q = pp[2];
+        a0 = m0 & any_gt<MODE>(__vabsdiffu4(c.x, n.x), __vabsdiffu4(c.x, s.x), K);
+        a1 = m1 & any_gt<MODE>(__vabsdiffu4(c.y, n.y), __vabsdiffu4(c.y, s.y), K);
+        a0 &= any_gt<MODE>(__vabsdiffu4(c.x, word_at<3>(l, c.x, c.y)), __vabsdiffu4(c.x, word_at<-3>(l, c.x, c.y)), K);
+        a1 &= any_gt<MODE>(__vabsdiffu4(c.y, word_at<3>(c.x, c.y, q)), __vabsdiffu4(c.y, word_at<-3>(c.x, c.y, q)), K);
+      };
+      auto append = [&](u32 a0, u32 a1, u32 ee) {
         const u32 b0 = __ballot_sync(0xffffffffu, a0 != 0), b1 = __ballot_sync(0xffffffffu, a1 != 0);
-        if (a0) S.segW[nW + __popc(b0 & lt)] = a0 | e;
+        if (a0) S.segW[nW + __popc(b0 & lt)] = a0 | ee;
         nW += __popc(b0);
-        if (a1) S.segW[nW + __popc(b1 & lt)] = a1 | (e + 1);
+        if (a1) S.segW[nW + __popc(b1 & lt)] = a1 | (ee + 1);
         nW += __popc(b1);
+      };
+      int r = warp;
+      for (; r + kFastWarps < S.nR; r += 2 * kFastWarps, p += 2 * pStep, e += (u32)kFastWarps << 9) {
+        u32 a0 = 0, a1 = 0, c0 = 0, c1 = 0;
+        if (act) { tests(p, a0, a1); tests(p + pStep, c0, c1); }
+        append(a0, a1, e);
+        append(c0, c1, e + ((u32)kFastWarps << 8));
+      }
+      if (r < S.nR) {
+        u32 a0 = 0, a1 = 0;
+        if (act) tests(p, a0, a1);
+        append(a0, a1, e);
       }
     }
   }
