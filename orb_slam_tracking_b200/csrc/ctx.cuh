@@ -76,6 +76,12 @@ struct orbx_ctx {
   int* hfCounters;
   int* hfScratch;
   int hfCap;
+  // the staging store is ONE device block, inputs first (keys | desc | gridOff | gridIdx | n), then the results (nmatches | counters |
+  // matches12), with a pinned host mirror of each part: a host-frame call is one H2D copy, its kernels, one D2H copy
+  orbx::u8* hfBlock;
+  orbx::u8* hHfIn;    // pinned, hfInBytes
+  orbx::u8* hHfOut;   // pinned, hfOutBytes
+  size_t hfInBytes, hfOutBytes;
   // Initializer scoring scratch (grown on demand): hypotheses, scores, best, list lengths, inlier flags
   orbx::u8* dScore;
   size_t scoreBytes;

@@ -193,14 +193,26 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   if ((rc = bf_alloc(c->hfBf, 1, (size_t)P.kpStride))) return rc;
   // host-frame staging (2 frames)
   c->hfCap = P.kpStride;
-  if ((rc = dalloc(c, &c->hfKeys, 2 * (size_t)c->hfCap))) return rc;
-  if ((rc = dalloc(c, &c->hfDesc, 2 * (size_t)c->hfCap * 32))) return rc;
-  if ((rc = dalloc(c, &c->hfGridOff, 2 * (size_t)(kGridCells + 1)))) return rc;
-  if ((rc = dalloc(c, &c->hfGridIdx, 2 * (size_t)c->hfCap))) return rc;
-  if ((rc = dalloc(c, &c->hfN, 2))) return rc;
-  if ((rc = dalloc(c, &c->hfMatches, (size_t)c->hfCap))) return rc;
-  if ((rc = dalloc(c, &c->hfNMatches, 1))) return rc;
-  if ((rc = dalloc(c, &c->hfCounters, 3))) return rc;
+  {
+    const size_t cap = (size_t)c->hfCap;
+    auto up = [](size_t b) { return (b + 255) & ~(size_t)255; };
+    const size_t oKeys = 0, oDesc = oKeys + up(2 * cap * sizeof(orbx_keypoint)), oOff = oDesc + up(2 * cap * 32),
+                 oIdx = oOff + up(2 * (size_t)(kGridCells + 1) * 4), oN = oIdx + up(2 * cap * 4), inBytes = oN + 256;
+    const size_t oNM = inBytes, oCnt = oNM + 4, oM = oNM + 16, outBytes = 16 + cap * 4;
+    if ((rc = dalloc(c, &c->hfBlock, inBytes + outBytes))) return rc;
+    c->hfKeys = reinterpret_cast<orbx_keypoint*>(c->hfBlock + oKeys);
+    c->hfDesc = c->hfBlock + oDesc;
+    c->hfGridOff = reinterpret_cast<u32*>(c->hfBlock + oOff);
+    c->hfGridIdx = reinterpret_cast<u32*>(c->hfBlock + oIdx);
+    c->hfN = reinterpret_cast<int*>(c->hfBlock + oN);
+    c->hfNMatches = reinterpret_cast<int*>(c->hfBlock + oNM);
+    c->hfCounters = reinterpret_cast<int*>(c->hfBlock + oCnt);
+    c->hfMatches = reinterpret_cast<int*>(c->hfBlock + oM);
+    c->hfInBytes = inBytes; c->hfOutBytes = outBytes;
+    CU(c, cudaHostAlloc((void**)&c->hHfIn, inBytes, cudaHostAllocDefault));
+    CU(c, cudaHostAlloc((void**)&c->hHfOut, outBytes, cudaHostAllocDefault));
+    std::memset(c->hHfIn, 0, inBytes);
+  }
   if ((rc = dalloc(c, &c->hfScratch, 3 * (size_t)c->hfCap))) return rc;
   if ((rc = dalloc(c, &c->dIngest, B * (size_t)width * height))) return rc;
   if ((rc = build_tensor_maps(c))) return rc;
@@ -226,7 +238,7 @@ extern "C" orbx_ctx* orbx_create(int device, int width, int height, int nfeature
   for (int i = 0; i < 2; ++i) { c->flight[i].active = 0; c->flight[i].n = 0; c->flight[i].chunk = 0; c->flight[i].status = 0; c->evDone[i] = nullptr; }
   c->nextTicket = 0;
   for (int i = 0; i < 2; ++i) { c->fg[i].exec = nullptr; c->fg[i].epoch = -1; }
-  c->graphEpoch = 0; c->hFrameIn = nullptr; c->hFrameOut = nullptr;
+  c->graphEpoch = 0; c->hFrameIn = nullptr; c->hFrameOut = nullptr; c->hHfIn = nullptr; c->hHfOut = nullptr; c->hfBlock = nullptr;
   c->stageTiming = 0; c->evStart = c->evStop = nullptr;
   for (int i = 0; i < 10; ++i) c->evStage[i] = nullptr;
   std::memset(c->stageMs, 0, sizeof(c->stageMs));
@@ -253,6 +265,8 @@ extern "C" void orbx_destroy(orbx_ctx* c) {
   for (int i = 0; i < 2; ++i) if (c->fg[i].exec) cudaGraphExecDestroy(c->fg[i].exec);
   if (c->hFrameIn) cudaFreeHost(c->hFrameIn);
   if (c->hFrameOut) cudaFreeHost(c->hFrameOut);
+  if (c->hHfIn) cudaFreeHost(c->hHfIn);
+  if (c->hHfOut) cudaFreeHost(c->hHfOut);
   for (int i = 0; i < 2; ++i) if (c->evDone[i]) cudaEventDestroy(c->evDone[i]);
   for (int i = 0; i < orbx_ctx::kLanes; ++i) {
     if (c->sSide[i]) cudaStreamDestroy(c->sSide[i]);

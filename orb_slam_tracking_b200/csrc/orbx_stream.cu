@@ -90,24 +90,39 @@ extern "C" int orbx_frame_glue(orbx_ctx* c, const orbx_keypoint* kps, int n, orb
   return ORBX_OK;
 }
 
-// copies a host frame into staging slot s (0 or 1)
+// copies a host frame into staging slot s (0 or 1) of the PINNED mirror of the staging store; stage_commit() sends the mirror to
+// the device in one copy (the caller's vectors are pageable: one asynchronous copy per array cost ~10 us each, ten per pair)
 static int stage_frame(orbx_ctx* c, const orbx_frame* F, int s) {
   if (!F || F->n < 0) return ORBX_ERR_ARG;
   if (F->n > c->hfCap) return ORBX_ERR_CAPACITY;
   if (F->n > 0 && (!F->keys_un || !F->desc || !F->grid_indices)) return ORBX_ERR_ARG;
   if (!F->grid_offsets) return ORBX_ERR_ARG;
-  cudaStream_t st = c->stream;
   const size_t cap = (size_t)c->hfCap;
+  u8* const h = c->hHfIn;
+  auto at = [&](const void* dev) { return h + (reinterpret_cast<const u8*>(dev) - c->hfBlock); };
   if (F->n) {
-    CU(c, cudaMemcpyAsync(c->hfKeys + s * cap, F->keys_un, (size_t)F->n * sizeof(orbx_keypoint), cudaMemcpyHostToDevice, st));
-    CU(c, cudaMemcpyAsync(c->hfDesc + s * cap * 32, F->desc, (size_t)F->n * 32, cudaMemcpyHostToDevice, st));
     const u32 nIdx = F->grid_offsets[kGridCells];
     if (nIdx > (u32)F->n) return ORBX_ERR_ARG;
-    if (nIdx) CU(c, cudaMemcpyAsync(c->hfGridIdx + s * cap, F->grid_indices, nIdx * sizeof(u32), cudaMemcpyHostToDevice, st));
+    std::memcpy(at(c->hfKeys + s * cap), F->keys_un, (size_t)F->n * sizeof(orbx_keypoint));
+    std::memcpy(at(c->hfDesc + s * cap * 32), F->desc, (size_t)F->n * 32);
+    if (nIdx) std::memcpy(at(c->hfGridIdx + s * cap), F->grid_indices, nIdx * sizeof(u32));
   }
-  CU(c, cudaMemcpyAsync(c->hfGridOff + (size_t)s * (kGridCells + 1), F->grid_offsets, (kGridCells + 1) * sizeof(u32),
-                        cudaMemcpyHostToDevice, st));
-  CU(c, cudaMemcpyAsync(c->hfN + s, &F->n, sizeof(int), cudaMemcpyHostToDevice, st));
+  std::memcpy(at(c->hfGridOff + (size_t)s * (kGridCells + 1)), F->grid_offsets, (kGridCells + 1) * sizeof(u32));
+  std::memcpy(at(c->hfN + s), &F->n, sizeof(int));
+  return ORBX_OK;
+}
+static int stage_commit(orbx_ctx* c) {
+  CU(c, cudaMemcpyAsync(c->hfBlock, c->hHfIn, c->hfInBytes, cudaMemcpyHostToDevice, c->stream));
+  return ORBX_OK;
+}
+// the results of a host-frame matcher call (nmatches | counters | matches12[n1]) through the pinned mirror: one D2H copy, one sync
+static int fetch_match_results(orbx_ctx* c, int n1, int* matches12, int* nmatches, int* counters) {
+  const size_t bytes = 16 + (matches12 ? (size_t)n1 * sizeof(int) : 0);
+  CU(c, cudaMemcpyAsync(c->hHfOut, c->hfBlock + c->hfInBytes, bytes, cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  if (nmatches) std::memcpy(nmatches, c->hHfOut, sizeof(int));
+  if (counters) std::memcpy(counters, c->hHfOut + 4, 3 * sizeof(int));
+  if (matches12 && n1) std::memcpy(matches12, c->hHfOut + 16, (size_t)n1 * sizeof(int));
   return ORBX_OK;
 }
 
@@ -118,7 +133,7 @@ extern "C" int orbx_features_in_area(orbx_ctx* c, const orbx_frame* F, float x, 
   CU(c, cudaSetDevice(c->device));
   int rc = drain_flights(c);
   if (rc) return rc;
-  if ((rc = stage_frame(c, F, 0))) return rc;
+  if ((rc = stage_frame(c, F, 0)) || (rc = stage_commit(c))) return rc;
   const int dcap = std::min(cap, c->hfCap);
   launch_features_in_area(c->P, c->hfKeys, c->hfGridOff, c->hfGridIdx, x, y, r, min_level, max_level, c->hfMatches,
                           dcap, c->hfNMatches, c->stream);
@@ -172,7 +187,7 @@ extern "C" int orbx_search_for_initialization(orbx_ctx* c, const orbx_frame* F1,
   int rc = drain_flights(c);
   if (rc) return rc;
   if ((rc = stage_frame(c, F1, 0))) return rc;
-  if ((rc = stage_frame(c, F2, 1))) return rc;
+  if ((rc = stage_frame(c, F2, 1)) || (rc = stage_commit(c))) return rc;
   MatchArgs A;
   A.keysUn = c->hfKeys; A.desc = c->hfDesc; A.gridOff = c->hfGridOff; A.gridIdx = c->hfGridIdx; A.n = c->hfN;
   A.stride = c->hfCap; A.matches12 = c->hfMatches; A.nmatches = c->hfNMatches; A.counters = c->hfCounters;
@@ -180,15 +195,7 @@ extern "C" int orbx_search_for_initialization(orbx_ctx* c, const orbx_frame* F1,
   A.bf = c->hfBf;
   c->launches = launch_match(c->P, A, 1, 2, nnratio, check_orientation, window_size, c->stream);
   CU(c, cudaGetLastError());
-  int nm = 0, cnt[3] = {0, 0, 0};
-  if (matches12 && F1->n)
-    CU(c, cudaMemcpyAsync(matches12, c->hfMatches, (size_t)F1->n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  CU(c, cudaMemcpyAsync(&nm, c->hfNMatches, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  CU(c, cudaMemcpyAsync(cnt, c->hfCounters, 3 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  CU(c, cudaStreamSynchronize(c->stream));
-  if (nmatches) *nmatches = nm;
-  if (counters) std::memcpy(counters, cnt, sizeof(cnt));
-  return ORBX_OK;
+  return fetch_match_results(c, F1->n, matches12, nmatches, counters);
 }
 
 // ---- the distance matrix of one pair sharded by query rows (multi-GPU brute-force matching) ------------------------
@@ -209,7 +216,7 @@ extern "C" int orbx_match_rows(orbx_ctx* c, const orbx_frame* F1, const orbx_fra
   CU(c, cudaSetDevice(c->device));
   int rc = stage_frame(c, F1, 0);
   if (rc) return rc;
-  if ((rc = stage_frame(c, F2, 1))) return rc;
+  if ((rc = stage_frame(c, F2, 1)) || (rc = stage_commit(c))) return rc;
   const MatchArgs A = host_pair_args(c);
   c->launches = launch_bf_prep(c->P, A, A.bf, 1, 2, c->stream);
   int cnt[4] = {0, 0, 0, 0};
@@ -236,7 +243,7 @@ extern "C" int orbx_match_resolve(orbx_ctx* c, const orbx_frame* F1, const orbx_
   CU(c, cudaSetDevice(c->device));
   int rc = stage_frame(c, F1, 0);
   if (rc) return rc;
-  if ((rc = stage_frame(c, F2, 1))) return rc;
+  if ((rc = stage_frame(c, F2, 1)) || (rc = stage_commit(c))) return rc;
   const MatchArgs A = host_pair_args(c);
   c->launches = launch_bf_prep(c->P, A, A.bf, 1, 2, c->stream);
   if (n_queries) CU(c, cudaMemcpyAsync(A.bf.topk, rows, (size_t)n_queries * 8 * sizeof(u32), cudaMemcpyHostToDevice, c->stream));
@@ -246,15 +253,7 @@ extern "C" int orbx_match_resolve(orbx_ctx* c, const orbx_frame* F1, const orbx_
   if (cnt[1] != n_queries) return ORBX_ERR_ARG;  // the row table does not belong to this pair
   c->launches += launch_bf_resolve(c->P, A, A.bf, 1, 2, nnratio, check_orientation, window_size, c->stream);
   CU(c, cudaGetLastError());
-  int nm = 0, cn[3] = {0, 0, 0};
-  if (matches12 && F1->n)
-    CU(c, cudaMemcpyAsync(matches12, c->hfMatches, (size_t)F1->n * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  CU(c, cudaMemcpyAsync(&nm, c->hfNMatches, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  CU(c, cudaMemcpyAsync(cn, c->hfCounters, 3 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-  CU(c, cudaStreamSynchronize(c->stream));
-  if (nmatches) *nmatches = nm;
-  if (counters) std::memcpy(counters, cn, sizeof(cn));
-  return ORBX_OK;
+  return fetch_match_results(c, F1->n, matches12, nmatches, counters);
 }
 
 // Raw all-pairs Hamming best / second best (micro-benchmark of the brute-force configuration; DescriptorDistance over a matrix)
