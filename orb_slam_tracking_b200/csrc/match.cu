@@ -197,9 +197,10 @@ constexpr int kChunkQ = 128;            // queries per chunk (segment table size
 constexpr u32 kInvalid = 0xffffffffu;   // entry of a cell-rectangle key outside the window
 
 struct MatchSmem {  // byte offsets into dynamic shared memory
-  int off0, cx, cy, ci, md, m21, q, bin, touch, ent, total;
-  int entCap;
+  int off0, cx, cy, ci, md, m21, q, bin, touch, ent, d2, qd, qk, total;
+  int entCap, descCap;
 };
+constexpr int kDescStage = 1024;  // level-0 keys of F2 whose descriptors are staged in shared memory (the rest is read from global memory)
 __host__ __device__ inline MatchSmem match_smem_layout(int stride) {
   MatchSmem L;
   int o = 0;
@@ -215,6 +216,12 @@ __host__ __device__ inline MatchSmem match_smem_layout(int stride) {
   L.touch = take(stride * 4);
   L.entCap = stride > 8192 ? stride : 8192;
   L.ent = take(L.entCap * 4);
+  // descriptors next to the work: F2's level-0 keys in CSR order (the first descCap of them) and the queries of the running chunk.
+  // Without them a warp's fill is a chain of dependent global loads per query (keypoint, its descriptor, the candidates' descriptors).
+  L.descCap = stride < kDescStage ? stride : kDescStage;
+  L.d2 = take(L.descCap * 32);
+  L.qd = take(kChunkQ * 32);
+  L.qk = take(kChunkQ * 8);
   L.total = o;
   return L;
 }
@@ -239,6 +246,9 @@ __global__ void __launch_bounds__(MT) k_match_cta(const __grid_constant__ Params
   u8* const sBin = dsm + LY.bin;
   u32* const sTouch = reinterpret_cast<u32*>(dsm + LY.touch);  // per key of F2: the first query (lane) of the running batch that takes it
   u32* const sEnt = reinterpret_cast<u32*>(dsm + LY.ent);
+  uint4* const sD2 = reinterpret_cast<uint4*>(dsm + LY.d2);   // [p][2]: descriptor of the level-0 key at CSR position p < descCap
+  uint4* const sQd = reinterpret_cast<uint4*>(dsm + LY.qd);   // [query of the chunk][2]
+  float2* const sQk = reinterpret_cast<float2*>(dsm + LY.qk); // [query of the chunk]: undistorted position
 
   const int pair = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int s1 = pair * pairStep, s2 = s1 + 1;
@@ -256,59 +266,71 @@ __global__ void __launch_bounds__(MT) k_match_cta(const __grid_constant__ Params
   if (tid < HISTO_LENGTH) sHist[tid] = 0;
 
   // ---- S1: level-0 CSR of F2 (thread t owns cells [12 t, 12 t + 12)) ----
+  // The grid entries of F2 (index -> keypoint: two dependent global loads each) are fetched by all threads side by side into a
+  // scratch view of the entry table (x, y, index; index 0xffffffff for other octaves) when they fit there; the per-cell walks
+  // below then read shared memory.  Otherwise they walk global memory as before.
+  const int nE = (int)gOff[kGridCells];
+  const bool staged = (size_t)nE * 12 <= (size_t)LY.entCap * 4;
+  float* const tX = reinterpret_cast<float*>(sEnt);
+  float* const tY = tX + nE;
+  u32* const tI = reinterpret_cast<u32*>(tY + nE);
+  if (staged) {
+    for (int e = tid; e < nE; e += MT) {
+      const int i2 = (int)gIdx[e];
+      const orbx_keypoint k = k2[i2];
+      tX[e] = k.x; tY[e] = k.y; tI[e] = k.octave == 0 ? (u32)i2 : 0xffffffffu;
+    }
+    __syncthreads();
+  }
   constexpr int CPT = kGridCells / MT;
   int cnt[CPT], tot = 0;
+  u32 eb[CPT + 1];
   {
     const int c0 = tid * CPT;
-    u32 e = gOff[c0];
+#pragma unroll
+    for (int j = 0; j <= CPT; ++j) eb[j] = gOff[c0 + j];
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
-      const u32 e1 = gOff[c0 + j + 1];
       int n = 0;
-      for (; e < e1; ++e) n += (k2[gIdx[e]].octave == 0);
+      if (staged) { for (u32 e = eb[j]; e < eb[j + 1]; ++e) n += (tI[e] != 0xffffffffu); }
+      else { for (u32 e = eb[j]; e < eb[j + 1]; ++e) n += (k2[gIdx[e]].octave == 0); }
       cnt[j] = n;
       tot += n;
     }
   }
-  sPart[tid] = tot;
-  __syncthreads();
-  for (int o = 1; o < MT; o <<= 1) {
-    const int v = tid >= o ? sPart[tid - o] : 0;
-    __syncthreads();
-    sPart[tid] += v;
-    __syncthreads();
-  }
+  int total0;
+  int run0 = cta_prefix_sum<MT>(tot, sPart, &total0) - tot;
   {
-    int run = tid ? sPart[tid - 1] : 0;
+    int run = run0;
     const int c0 = tid * CPT;
-    u32 e = gOff[c0];
 #pragma unroll
     for (int j = 0; j < CPT; ++j) {
       sOff0[c0 + j] = (unsigned short)run;
-      const u32 e1 = gOff[c0 + j + 1];
-      for (; e < e1; ++e) {
-        const int i2 = (int)gIdx[e];
-        const orbx_keypoint k = k2[i2];
-        if (k.octave == 0) { sCx[run] = k.x; sCy[run] = k.y; sCi[run] = (unsigned short)i2; ++run; }
+      for (u32 e = eb[j]; e < eb[j + 1]; ++e) {
+        if (staged) {
+          const u32 i2 = tI[e];
+          if (i2 != 0xffffffffu) { sCx[run] = tX[e]; sCy[run] = tY[e]; sCi[run] = (unsigned short)i2; ++run; }
+        } else {
+          const int i2 = (int)gIdx[e];
+          const orbx_keypoint k = k2[i2];
+          if (k.octave == 0) { sCx[run] = k.x; sCy[run] = k.y; sCi[run] = (unsigned short)i2; ++run; }
+        }
       }
     }
     if (tid == MT - 1) sOff0[kGridCells] = (unsigned short)run;
   }
   __syncthreads();
+  {  // descriptors of F2's level-0 keys, CSR order (visible after the barriers of S2)
+    const int n0 = min((int)sOff0[kGridCells], LY.descCap);
+    for (int i = tid; i < 2 * n0; i += MT) sD2[i] = __ldg(reinterpret_cast<const uint4*>(d2 + (size_t)sCi[i >> 1] * 32) + (i & 1));
+  }
   // ---- S2: level-0 queries of F1, ascending i1 (:36-39) ----
   {
     const int per = (n1 + MT - 1) / MT, b = min(tid * per, n1), e = min(b + per, n1);
     int c = 0;
     for (int i = b; i < e; ++i) c += !(k1[i].octave > 0);
-    sPart[tid] = c;
-    __syncthreads();
-    for (int o = 1; o < MT; o <<= 1) {
-      const int v = tid >= o ? sPart[tid - o] : 0;
-      __syncthreads();
-      sPart[tid] += v;
-      __syncthreads();
-    }
-    int run = tid ? sPart[tid - 1] : 0;
+    int totalQ;
+    int run = cta_prefix_sum<MT>(c, sPart, &totalQ) - c;
     for (int i = b; i < e; ++i)
       if (!(k1[i].octave > 0)) { sQ[run] = (unsigned short)i; sBin[run] = 0xff; ++run; }
     if (tid == MT - 1) sNQ = run;
@@ -326,7 +348,11 @@ __global__ void __launch_bounds__(MT) k_match_cta(const __grid_constant__ Params
     if (tid < kChunkQ) {
       int sz = 0;
       if (tid < nCand) {
-        const orbx_keypoint kp1 = k1[sQ[qs + tid]];
+        const int i1 = sQ[qs + tid];
+        const orbx_keypoint kp1 = k1[i1];
+        sQk[tid] = make_float2(kp1.x, kp1.y);
+        sQd[2 * tid] = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i1 * 32));
+        sQd[2 * tid + 1] = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i1 * 32) + 1);
         int a, b, c, d;
         if (cell_rect(P, kp1.x, kp1.y, r, a, b, c, d))
           for (int ix = a; ix <= b; ++ix) sz += (int)sOff0[ix * kGridRows + d + 1] - (int)sOff0[ix * kGridRows + c];
@@ -363,8 +389,7 @@ __global__ void __launch_bounds__(MT) k_match_cta(const __grid_constant__ Params
     for (int qi = warp; qi < nq; qi += MW) {
       const int segB = sSeg[qi], segN = sSeg[qi + 1] - segB;
       if (segN == 0) continue;
-      const int i1 = sQ[qs + qi];
-      const orbx_keypoint kp1 = k1[i1];
+      const float2 kp1 = sQk[qi];
       int minCX, maxCX, minCY, maxCY;
       cell_rect(P, kp1.x, kp1.y, r, minCX, maxCX, minCY, maxCY);
       const int nCols = maxCX - minCX + 1;
@@ -392,8 +417,7 @@ __global__ void __launch_bounds__(MT) k_match_cta(const __grid_constant__ Params
       cs[lane + 32] = tot0 + p1 - c1; cb[lane + 32] = b1;
       if (lane == 0) cs[kGridCols] = segN;
       __syncwarp();
-      const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i1 * 32));
-      const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(d1 + (size_t)i1 * 32) + 1);
+      const uint4 a0 = sQd[2 * qi], a1 = sQd[2 * qi + 1];
       for (int t = lane; t < segN; t += 32) {
         int lo = 0, hi = kGridCols;  // column of flattened position t: last c with cs[c] <= t
 #pragma unroll
@@ -406,7 +430,15 @@ __global__ void __launch_bounds__(MT) k_match_cta(const __grid_constant__ Params
         u32 en = kInvalid;
         if (fabsf(dx) < r && fabsf(dy) < r) {  // Frame.cpp:196-199
           const int i2 = sCi[p];
-          en = ((u32)hamming256(a0, a1, d2 + (size_t)i2 * 32) << 16) | (u32)i2;
+          int dist;
+          if (p < LY.descCap) {
+            const uint4 b0 = sD2[2 * p], b1 = sD2[2 * p + 1];
+            dist = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+                   __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+          } else {
+            dist = hamming256(a0, a1, d2 + (size_t)i2 * 32);
+          }
+          en = ((u32)dist << 16) | (u32)i2;
         }
         sEnt[segB + t] = en;
       }
