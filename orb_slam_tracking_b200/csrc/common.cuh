@@ -221,6 +221,7 @@ int launch_pyramid(const Params& P, const int* const* dTabs, int nSlots, cudaStr
 int launch_blur(const Params& P, int nSlots, cudaStream_t st);
 int launch_fast(const Params& P, const TmaMaps& M, int nSlots, cudaStream_t st);
 int launch_quadtree(const Params& P, int nSlots, cudaStream_t st);
+int configure_quadtree();
 int launch_retain_old(const Params& P, int nSlots, cudaStream_t st);
 int launch_describe(const Params& P, const PatchMaps& M, int nSlots, int lap0, int lap1, cudaStream_t st);
 void launch_sincosf_probe(const float* y, long long n, float* sn, float* cs, cudaStream_t st);

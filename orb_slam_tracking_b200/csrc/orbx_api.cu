@@ -217,6 +217,7 @@ static int create_impl(orbx_ctx* c, int device, int width, int height, int nfeat
   if ((rc = dalloc(c, &c->dIngest, B * (size_t)width * height))) return rc;
   if ((rc = build_tensor_maps(c))) return rc;
   if ((rc = configure_fast(P))) { c->err = "k_fast: shared memory / occupancy configuration failed"; return rc; }
+  if ((rc = configure_quadtree())) { c->err = "k_quadtree: shared memory configuration failed"; return rc; }
   c->fastSet[0].strips = P.strips; c->fastSet[0].nStrips = P.nStrips; c->fastSet[0].tileMax = P.fastTileMax;
   c->fastSet[0].segW = P.fastSegW; c->fastSet[0].segP = P.fastSegP; c->fastSet[0].grid = P.fastGrid; c->fastSet[0].tma = c->tma;
   c->fastSet[0].ready = 1; c->fastSet[1].ready = 0;

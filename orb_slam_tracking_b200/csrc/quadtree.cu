@@ -74,8 +74,11 @@ __device__ __forceinline__ int quadrant(const short4 b, const u32 xy) {
   return (x >= midx ? 1 : 0) + (y >= midy ? 2 : 0);  // n1, n2, n3, n4
 }
 
-template <int QT>
-__global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params P, int sortCap) {
+// SM (single-frame path, launch_quadtree): the node tables and the candidates' node ids / positions live in shared memory (smNodeCap
+// nodes, smCandCap candidates, behind the sort words).  A pass is a handful of dependent steps over those tables -- counts by atomics,
+// prefix sums, child boxes, key moves -- and with one frame on the GPU each step's global round trip is the kernel's latency.
+template <int QT, bool SM>
+__global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params P, int sortCap, int smNodeCap, int smCandCap) {
   __shared__ QtS<QT> S;
   extern __shared__ __align__(8) u64 sSrt[];  // sortCap packed sort words (launch_quadtree sizes it from the largest quota)
   const int l = blockIdx.x, slot = blockIdx.y, tid = threadIdx.x;
@@ -106,6 +109,24 @@ __global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params 
   int* scan = P.nodeScan + no;
   SortElem* srt = P.nodeSort + no;
   const int* edges = P.rootEdges + L.rootEdgeOff;
+  if (SM) {
+    u8* sm = reinterpret_cast<u8*>(sSrt + sortCap);
+    auto take = [&](size_t bytes) { u8* r = sm; sm += (bytes + 15) & ~(size_t)15; return r; };
+    nBest = reinterpret_cast<u64*>(take((size_t)smNodeCap * 8));
+    nBox = reinterpret_cast<short4*>(take((size_t)smNodeCap * 8));
+    aux = reinterpret_cast<int*>(take((size_t)smNodeCap * 16));
+    nCount = reinterpret_cast<int*>(take((size_t)smNodeCap * 4));
+    nSlot = reinterpret_cast<int*>(take((size_t)smNodeCap * 4));
+    list = reinterpret_cast<int*>(take((size_t)smNodeCap * 4));
+    scan = reinterpret_cast<int*>(take((size_t)smNodeCap * 4));
+    u32* sNode = reinterpret_cast<u32*>(take((size_t)smCandCap * 4));
+    u32* sXY = reinterpret_cast<u32*>(take((size_t)smCandCap * 4));
+    if (M <= smCandCap) {  // the usual few thousand candidates; beyond the budget they stay in global memory
+      for (int k = tid; k < M; k += QT) { sNode[k] = cNode[k]; sXY[k] = cXY[k]; }
+      cNode = sNode; cXY = sXY;
+    }
+    __syncthreads();
+  }
 
   // roots (:706-768)
   for (int i = tid; i < L.nIni; i += QT) {
@@ -296,16 +317,30 @@ __global__ void __launch_bounds__(QT) k_quadtree(const __grid_constant__ Params 
 int launch_quadtree(const Params& P, int nSlots, cudaStream_t st) {
   dim3 grid(P.nlevels, nSlots);
   // a generation has at most ~quota divisible nodes; beyond sortCap the kernel sorts in global memory
-  int q = 0;
-  for (int l = 0; l < P.nlevels; ++l) q = q > P.lv[l].quota ? q : P.lv[l].quota;
+  int q = 0, nodeCap = 0, candCap = 0;
+  for (int l = 0; l < P.nlevels; ++l) {
+    q = std::max(q, P.lv[l].quota); nodeCap = std::max(nodeCap, P.lv[l].nodeCap); candCap = std::max(candCap, P.lv[l].candCap);
+  }
   const int sortCap = 2 * q < 256 ? 256 : (2 * q > 4096 ? 4096 : 2 * q);
   const size_t smem = (size_t)sortCap * sizeof(u64);
+  // a few frames (the latency path): everything a pass touches in shared memory, if it fits
+  candCap = std::min(candCap, 8192);
+  const size_t smemSM = smem + (size_t)nodeCap * 48 + (size_t)candCap * 8 + 256;
+  if (nSlots <= 8 && q < 1000 && smemSM <= 200 * 1024) {
+    k_quadtree<256, true><<<grid, 256, smemSM, st>>>(P, sortCap, nodeCap, candCap);
+    return 1;
+  }
   // small quotas: 64-thread CTAs give the best throughput when thousands of them share the GPU (whole batches); a chunk of
   // the pipelined host path has few CTAs and waits for the slowest one (level 0), where 256 threads cut the latency by a third
-  if (q < 400 && nSlots > 128) k_quadtree<64><<<grid, 64, smem, st>>>(P, sortCap);
-  else if (q < 1000) k_quadtree<256><<<grid, 256, smem, st>>>(P, sortCap);
-  else k_quadtree<512><<<grid, 512, smem, st>>>(P, sortCap);
+  if (q < 400 && nSlots > 128) k_quadtree<64, false><<<grid, 64, smem, st>>>(P, sortCap, 0, 0);
+  else if (q < 1000) k_quadtree<256, false><<<grid, 256, smem, st>>>(P, sortCap, 0, 0);
+  else k_quadtree<512, false><<<grid, 512, smem, st>>>(P, sortCap, 0, 0);
   return 1;
+}
+
+// Called once per context (after cudaSetDevice): the shared-memory form of k_quadtree opts into its dynamic shared memory.
+int configure_quadtree() {
+  return cudaFuncSetAttribute(k_quadtree<256, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) == cudaSuccess ? ORBX_OK : ORBX_ERR_CUDA;
 }
 
 }  // namespace orbx
