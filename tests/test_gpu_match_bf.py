@@ -34,7 +34,8 @@ def _frames(fe, oracle, synth, W, H, nf, ini, mn, pair_index):
     return E, G, O
 
 
-@pytest.mark.parametrize("cfg", [(640, 480, 1000, 20, 7), (752, 480, 2000, 0, 0), (1241, 376, 2000, 20, 7)])
+# the 3200-feature case: more grid entries than k_match_cta's scratch view of them holds (its set-up walks global memory instead)
+@pytest.mark.parametrize("cfg", [(640, 480, 1000, 20, 7), (752, 480, 2000, 0, 0), (1241, 376, 2000, 20, 7), (1241, 376, 3200, 0, 0)])
 def test_every_matcher_path_agrees_with_the_oracle(fe, oracle, synth, cfg):
     W, H, nf, ini, mn = cfg
     E, G, O = _frames(fe, oracle, synth, W, H, nf, ini, mn, 33)
