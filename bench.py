@@ -193,12 +193,13 @@ def opencv_primitives(wl, n_frames=8):
     return out
 
 
-def cpu_baseline(wl, n_frames, threads, target_s=12.0, repeats=None):
+def cpu_baseline(wl, n_frames, threads, target_s=12.0, repeats=None, frames=None):
     """The reference's CPU path on a bounded sample of the same workload (about `target_s` seconds of
     work, or exactly `repeats` passes).  Only the processing is timed (images are generated before)."""
     from orb_slam_tracking_b200 import synth
     impl, kind = cpu_impl()
-    imgs = synth.frames_parallel(n_frames, wl["W"], wl["H"])   # the first n_frames of the same stream, all distinct
+    # the first n_frames of the same stream, all distinct (run_ours hands over its own batch: no second process pool)
+    imgs = frames[:n_frames] if frames is not None and len(frames) >= n_frames else synth.frames_parallel(n_frames, wl["W"], wl["H"])
     K4, D4 = synth.camera_for(wl["W"], wl["H"])
     a = (wl["nfeatures"], 1.2, 8, wl["ini"], wl["mn"], K4, D4, wl.get("window", WINDOW), NNRATIO, threads)
     t = time.perf_counter()
@@ -273,27 +274,27 @@ def run_ours(args, wl):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
     use_dist = world > 1
+    B = args.batch or wl["batch"]
+    B -= B % 2
+    W, H, nf = wl["W"], wl["H"], wl["nfeatures"]
+    # synthetic frames: every frame of the batch is DISTINCT (pair p of the stream is generated from seed p; rounds 1 and 2 up to
+    # r02o timed 16 distinct pairs tiled to the batch, which now is the variant "tiled_16_pairs").  The job is a stream of
+    # world * B/2 pairs; this rank owns one contiguous block of it (shard.py), no collective.  Generated first: the process
+    # pool forks, and that is done before this process owns a CUDA context or NCCL threads.
+    pair_lo, pair_hi = shard.shard_pairs(world * (B // 2), world, rank)
+    assert pair_hi - pair_lo == B // 2
+    imgs = synth.frames_parallel(B, W, H, first_pair=pair_lo)
     torch.cuda.set_device(local)
     binding = bind_near_gpu(local) if world > 1 and not os.environ.get("ORBX_BENCH_NO_BIND") else "not bound"
     if use_dist:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    B = args.batch or wl["batch"]
-    B -= B % 2
     WINDOW = wl.get("window", 100)
-    W, H, nf = wl["W"], wl["H"], wl["nfeatures"]
     L = capi.lib()
     E = fe.ORBextractor(nf, 1.2, 8, wl["ini"], wl["mn"], W, H, max_batch=B, device=local)
     K4, D4 = synth.camera_for(W, H)
     E.set_camera(K4, D4)
     S = fe.Stream(E, NNRATIO, True, WINDOW)
-    # synthetic frames: every frame of the batch is DISTINCT (pair p of the stream is generated from seed p; rounds 1 and 2 up to
-    # r02o timed 16 distinct pairs tiled to the batch, which now is the variant "tiled_16_pairs": FAST, quadtree and matcher
-    # costs depend on the scene, and those 16 happen to be ~14 % cheaper than the average of the stream)
-    # the job is a stream of world * B/2 pairs; this rank owns one contiguous block of it (shard.py), no collective
-    pair_lo, pair_hi = shard.shard_pairs(world * (B // 2), world, rank)
-    assert pair_hi - pair_lo == B // 2
-    imgs = synth.frames_parallel(B, W, H, first_pair=pair_lo)
     nbytes_in = imgs.nbytes
     wc = bool(os.environ.get("ORBX_BENCH_WC"))   # experiment: write-combined upload buffer (bench-side switch, not a library option)
     hp = L.orbx_host_alloc_ex(nbytes_in, 1) if wc else L.orbx_host_alloc(nbytes_in)
@@ -569,7 +570,7 @@ def run_ours(args, wl):
         if world == 1 and not args.no_cpu:
             threads = host_threads()
             n_cpu = cpu_sample_frames(wl, threads)
-            v, dt, reps, kind = cpu_baseline(wl, n_cpu, threads)
+            v, dt, reps, kind = cpu_baseline(wl, n_cpu, threads, frames=imgs if pair_lo == 0 else None)
             try:
                 line["cpu_opencv_primitives"] = opencv_primitives(wl)
             except Exception as e:   # no cv2 on the box: the reference-source arm below is the baseline
