@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_pyramid_chain(const __gri
   const int warpsTotal = (int)gridDim.x * kResizeWarps, warp0 = (int)blockIdx.x * kResizeWarps + (int)threadIdx.y;
   for (int l = 1; l < P.nlevels; ++l) {
     const int nbx = (P.lv[l].w + 127) / 128, nwy = (P.lv[l].h + rows - 1) / rows, perSlot = nbx * nwy;
-    const bool wide = P.lv[l - 1].w > 2 * P.lv[l].w + 1;
+    const bool wide = P.lv[l - 1].w > 2 * P.lv[l].w;  // horizontal scale above 2 (by however little: 309 -> 154 columns)
     for (int it = warp0; it < perSlot * nSlots; it += warpsTotal) {
       const int slot = it / perSlot, r = it - slot * perSlot, wy = r / nbx, bx = r - wy * nbx;
       if (wide) resize_strip<true, true>(P, l, T.t[l], rows, bx, wy * rows, slot);
@@ -305,7 +305,9 @@ int launch_pyramid(const Params& P, const int* const* dTabs, int nSlots, cudaStr
     const int rows = P.optResizeRows > 0 ? P.optResizeRows : nSlots >= 64 ? kResizeRows : nSlots >= 8 ? 8 : 4;
     dim3 grid((P.lv[l].w + 127) / 128, (P.lv[l].h + rows * kResizeWarps - 1) / (rows * kResizeWarps), nSlots);
     // taps of 4 adjacent output columns span 3 * scale + 2 source bytes
-    if (P.lv[l - 1].w > 2 * P.lv[l].w + 1) k_resize<true><<<grid, block, 0, st>>>(P, l, dTabs[l], rows);
+    // the permutes reach 8 bytes = the taps of 4 columns up to a horizontal scale of exactly 2; anything above (309 -> 154 columns is
+    // 2.006) takes the byte-load form
+    if (P.lv[l - 1].w > 2 * P.lv[l].w) k_resize<true><<<grid, block, 0, st>>>(P, l, dTabs[l], rows);
     else k_resize<false><<<grid, block, 0, st>>>(P, l, dTabs[l], rows);
     ++n;
   }

@@ -328,7 +328,9 @@ def test_pyramid_chain_equals_levelwise(fe, oracle, synth):
     """Batches of at most 2 frames build the pyramid in ONE launch (k_pyramid_chain: grid barrier between the levels); larger batches
     run one k_resize launch per level.  Both must give the oracle's levels, also for scale factors above 2 (the byte-load form of the
     row pass) and for a batch of 2."""
-    for W, H, sf, nl in ((640, 480, 1.2, 8), (752, 480, 1.2, 8), (611, 403, 1.33, 6), (800, 600, 2.5, 3), (1241, 376, 1.2, 8)):
+    # 309 -> 154 and 885 -> 442 columns: a horizontal scale a hair above 2 (found by the wider fuzz run, tools/gpu/fuzz_more.py)
+    for W, H, sf, nl in ((640, 480, 1.2, 8), (752, 480, 1.2, 8), (611, 403, 1.33, 6), (800, 600, 2.5, 3), (1241, 376, 1.2, 8),
+                         (309, 164, 2.0, 2), (885, 309, 2.0, 3), (640, 480, 2.0, 3)):
         E = fe.ORBextractor(500, sf, nl, 20, 7, W, H, max_batch=2)
         R = oracle.Extractor(500, sf, nl, 20, 7)
         imgs = synth.frames(2, W, H, first_pair=5)
