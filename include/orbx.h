@@ -86,8 +86,10 @@ int orbx_sincosf_probe(orbx_ctx* ctx, const float* y, long long n, float* sin_ou
  * Features/ORBextractor.cpp:1552), 1 = ComputeKeyPointsOld (:1207-1496, the alternative the reference keeps behind a
  * commented-out call, :1555): its own cell grid, the minThFAST retry for cells with at most 3 keypoints, per-cell quotas
  * and cv::KeyPointsFilter::retainBest (libstdc++'s std::nth_element order).  Everything else of operator() is shared.
- * Returns ORBX_ERR_ARG for shapes on which that function divides by zero (a level quota too small for one cell column) or
- * whose cells are wider than 480 tested columns. */
+ * Returns ORBX_ERR_ARG for shapes on which that function divides by zero (a level quota too small for one cell column),
+ * whose cells are wider than 480 tested columns, or whose cell grid runs past the tested region of a level (very wide or
+ * very tall images: the reference then keeps keypoints closer than 19 px to the border, whose descriptors it reads from
+ * outside the blurred level, and asserts in cv::Mat::rowRange when a cell leaves the image). */
 int orbx_set_keypoint_policy(orbx_ctx* ctx, int policy);
 /* Schedule options of a context (they never change results).  The environment is read ONCE, in orbx_create
  * (ORBX_SINGLE_STREAM, ORBX_RUN_PARTS, ORBX_LANES, ORBX_RESIZE_ROWS, ORBX_MATCH_SERIAL, ORBX_FAST_TILE, ORBX_PYRAMID_CHAIN); this call

@@ -331,6 +331,11 @@ static int keypoints_old(const Level& L, const Tables& t, int level, float image
   const int minBX = kEdge, minBY = kEdge, maxBX = L.w - kEdge, maxBY = L.h - kEdge;  // :1233-1236
   const int W = maxBX - minBX, H = maxBY - minBY;
   const int cellW = (int)std::ceil((float)W / levelCols), cellH = (int)std::ceil((float)H / levelRows);
+  // Outside the function's working range: a cell row / column other than the last ends at minB + (i + 1) * cell + 3 (:1279, :1309); when
+  // that lies beyond maxB + 3 the reference tests and keeps keypoints closer than 19 px to the level's border -- its descriptor then
+  // reads outside the blurred clone (:1598-1613, undefined values), and a cell beyond the image makes cv::Mat::rowRange assert.
+  // Reported as -8 (the CUDA path refuses the shape with ORBX_ERR_ARG).
+  if ((levelRows - 1) * cellH > H || (levelCols - 1) * cellW > W) return -8;
   const int nCells = levelRows * levelCols;
   const int nfeaturesCell = (int)std::ceil((float)nDesired / nCells);  // :1250-1251
   std::vector<std::vector<KeyPoint>> cellKeys((size_t)nCells);

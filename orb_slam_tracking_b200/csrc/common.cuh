@@ -34,6 +34,9 @@ constexpr int kGridCols = ORBX_GRID_COLS, kGridRows = ORBX_GRID_ROWS, kGridCells
 #define ORBX_BLUR_TH 124
 #endif
 constexpr int kBlurTW = 120, kBlurTH = ORBX_BLUR_TH;  // k_blur: output columns x rows per warp strip
+// cell index of an interior column by multiply and shift: exact for xb * wCell < 2^22; xb * cellMul stays below 2^32 (xb <= 244 when
+// a strip holds several cells, xb < wCell <= 480 otherwise)
+constexpr int kCellShift = 22;
 #ifndef ORBX_FAST_WARPS
 #define ORBX_FAST_WARPS 8
 #endif
@@ -76,7 +79,7 @@ struct StripDesc {    // one work item of k_fast: a run of consecutive FAST cell
   int tileBytes;          // box bytes of the level: what the tile copy delivers; bits 24..27: retryMax (a cell with at most that many
                           // keypoints at iniThFAST runs again at minThFAST: 0 in ComputeKeyPointsOctTree, 3 in ComputeKeyPointsOld);
                           // bits 28..31: bits per coordinate of the emission-order key (7 or 9)
-  u32 cellMul;            // (xb * cellMul) >> 16 == xb / wCell for every interior column xb of a strip
+  u32 cellMul;            // (xb * cellMul) >> kCellShift == xb / wCell for every interior column xb of a strip
   int index0;             // i * nCols + j0: row-major index of the strip's first cell
   u32 candOff;            // lv[level].candOff, candCap, rootTabOff
   int candCap;

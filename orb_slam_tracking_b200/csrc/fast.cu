@@ -170,7 +170,7 @@ __device__ __forceinline__ u32 interior_mask(int g, int bLo, int bHi) {
 // bytes of word g (any bits) whose cell is in `cells` (retry run); a word spans at most two cells
 __device__ __forceinline__ u32 cell_mask(const StripCtx& S, int g, u32 cells) {
   const int xa = max(4 * g - S.bLo, 0), xb = max(4 * g + 3 - S.bLo, 0);
-  const int ja = (int)(((u32)xa * S.cellMul) >> 16), jb = (int)(((u32)xb * S.cellMul) >> 16);
+  const int ja = (int)(((u32)xa * S.cellMul) >> kCellShift), jb = (int)(((u32)xb * S.cellMul) >> kCellShift);
   const u32 ka = (cells >> ja) & 1 ? 0xffffffffu : 0u, kb = (cells >> jb) & 1 ? 0xffffffffu : 0u;
   if (ja == jb) return ka;
   const int nb = jb * S.wCell + S.bLo - 4 * g;  // first byte of the word that belongs to cell jb, 1..3
@@ -320,7 +320,7 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
       const u8* q = S.mm + ry * SB + b;
       const int m = q[0];
       const int xb = b - S.bLo;
-      const int j = (int)(((u32)xb * S.cellMul) >> 16), cs = j * S.wCell;
+      const int j = (int)(((u32)xb * S.cellMul) >> kCellShift), cs = j * S.wCell;
       // the columns left of the cell's first and right of its last interior column belong to another cell: they count as 0
       const int mL = xb != cs ? max(max((int)q[-SB - 1], (int)q[-1]), (int)q[SB - 1]) : 0;
       const int mR = xb + 1 != cs + S.wCell ? max(max((int)q[-SB + 1], (int)q[1]), (int)q[SB + 1]) : 0;
@@ -359,7 +359,7 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
       if (i < nK) {
         e = segK[i];
         const int xb = (int)(e & 511) - S.bLo;
-        on = S.cellIni[(int)(((u32)xb * S.cellMul) >> 16)] > S.retryMax;
+        on = S.cellIni[(int)(((u32)xb * S.cellMul) >> kCellShift)] > S.retryMax;
       }
       const u32 bo = __ballot_sync(0xffffffffu, on);
       __syncwarp();
@@ -381,7 +381,7 @@ __device__ __forceinline__ void fast_run(const Params& P, const StripCtx& S, con
         const u32 pk = segK[i], k = k0 + (u32)i;
         const int ry = (int)(pk >> 9), b = (int)(pk & 511), xb = b - S.bLo;
         const int m = S.mm[ry * SB + b];
-        const int j = (int)(((u32)xb * S.cellMul) >> 16);
+        const int j = (int)(((u32)xb * S.cellMul) >> kCellShift);
         const int rx = xb - j * S.wCell + 3;  // ROI-relative column in the pixel's cell; the reference shifts by the cell origin (:1134-1135)
         const int x = xb + 3 + S.sx, y = ry + S.sy;  // relative to (16,16)
         const u32 order = ((u32)(S.index0 + j) << (2 * S.orderBits)) | ((u32)ry << S.orderBits) | (u32)rx;

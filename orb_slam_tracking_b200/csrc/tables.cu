@@ -120,7 +120,7 @@ int build_geometry(Params& P, const HostTables& T, int fastTileBudget, std::vect
     L.wCell = (int)std::ceil(width / L.nCols);
     L.hCell = (int)std::ceil(height / L.nRows);
     if (L.wCell + 6 > kMaxCellDim || L.hCell + 6 > kMaxCellDim) return ORBX_ERR_ARG;
-    const u32 cellMul = 65535u / (u32)L.wCell + 1;  // exact floor(xb / wCell) for xb * wCell < 65536 (strip interiors are < 1024 wide)
+    const u32 cellMul = ((1u << kCellShift) - 1) / (u32)L.wCell + 1;  // exact floor(xb / wCell) for xb * wCell < 2^22 (strip interiors are < 1024 wide)
     // The cells of a cell row that cv::FAST can find anything in are j = 0 .. nValid - 1 (the skipped and the
     // degenerate ones are at the end, :1101); their tested interiors tile [19, maxBX - 3) without gaps.
     int nValid = 0, lastMaxX = 0;
@@ -258,6 +258,11 @@ int build_strips_old(Params& P, const HostTables& T, int fastTileBudget, std::ve
     L.oCellH = (int)std::ceil((float)H / L.oRows);
     L.oNfCell = (int)std::ceil((float)nDesired / (L.oCols * L.oRows));
     if (L.oCellW > 480 || L.oCellH + 6 > 127) return ORBX_ERR_ARG;  // a cell is one strip at least: 9-bit byte columns, 7-bit rows
+    // A cell row / column other than the last ends at minB + (i + 1) * cell + 3 (:1279, :1309).  Beyond maxB + 3 the reference tests and
+    // keeps keypoints closer than 19 px to the level's border: IC_Angle then needs the 19-px frame (not stored here), the descriptor
+    // reads outside the blurred level (undefined in the reference), and a cell beyond the image makes cv::Mat::rowRange assert.
+    // Those shapes (very wide or very tall levels with many small cells) are outside the function's working range and are refused.
+    if ((L.oRows - 1) * L.oCellH > H || (L.oCols - 1) * L.oCellW > W) return ORBX_ERR_ARG;
     cellTotal += L.oCols * L.oRows;
     // columns with something to test: ROI [16 + j cellW, 16 + j cellW + hX), hX = cellW + 6 or (last column) w - 16 - iniX
     int nValid = 0, lastX1 = 0;
@@ -269,7 +274,9 @@ int build_strips_old(Params& P, const HostTables& T, int fastTileBudget, std::ve
       nValid = j + 1;
       lastX1 = iniX + hX;
     }
-    const u32 cellMul = 65535u / (u32)L.oCellW + 1;
+    // (a 16-bit reciprocal is exact only for xb * cellW < 65536: the last column of a 343-px cell of ComputeKeyPointsOld landed in
+    // the next cell -- found by tools/gpu/fuzz_stream.py)
+    const u32 cellMul = ((1u << kCellShift) - 1) / (u32)L.oCellW + 1;
     int nSplit = 1, perStrip = nValid;
     auto box_w = [&](int nc) {
       u32 w = align_up((u32)(nc * L.oCellW + 6 + 20), 16);
