@@ -7,9 +7,11 @@ from oracle import orb_oracle as orc
 from orb_slam_tracking_b200 import frontend as fe, synth
 from orb_slam_tracking_b200.capi import OrbxError
 N, seed = int(sys.argv[1]), int(sys.argv[2])
+BIG = float(sys.argv[3]) if len(sys.argv) > 3 else 1.0   # scales the shapes (and triples the feature counts): large levels, quotas >= 1000
 bad = 0
 for cfg in T._configs(N, seed):
     W, H, nf, sf, nl, ini, mn, dist, idx = cfg
+    if BIG != 1.0: W, H, nf = int(W * BIG), int(H * BIG), nf * 3
     R = orc.Extractor(nf, sf, nl, ini, mn)
     try:
         E = fe.ORBextractor(nf, sf, nl, ini, mn, W, H, max_batch=4)
