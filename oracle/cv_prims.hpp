@@ -281,6 +281,11 @@ static inline void undistort_point(float u, float v, const float K[4], const flo
   for (int j = 0; j < 5; ++j) {
     double r2 = x * x + y * y;
     double icdist = 1. / (1 + ((0 * r2 + k2) * r2 + k1) * r2);
+    if (icdist < 0) {  // OpenCV 4.x (regression test 14583): a negative radial factor -- far outside the model's range -- gives up
+      x = ((double)u - cx) * ifx;
+      y = ((double)v - cy) * ify;
+      break;
+    }
     double dx = 2 * p1 * x * y + p2 * (r2 + 2 * x * x);
     double dy = p1 * (r2 + 2 * y * y) + 2 * p2 * x * y;
     x = (x0 - dx) * icdist;

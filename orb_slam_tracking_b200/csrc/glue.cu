@@ -19,6 +19,10 @@ __device__ __forceinline__ void undistort_point(const Params& P, float u, float 
     // 1 / (1 + ((k3*r2 + k2)*r2 + k1)*r2), k3 = 0
     const double poly = __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(0.0, r2), k2), r2), k1), r2);
     const double icdist = 1. / __dadd_rn(1.0, poly);
+    if (icdist < 0) {  // OpenCV 4.x: a negative radial factor (a point far outside the model's range) ends the iteration at the start value
+      x = x0; y = y0;
+      break;
+    }
     const double dx = __dadd_rn(__dmul_rn(__dmul_rn(__dmul_rn(2.0, p1), x), y),
                                 __dmul_rn(p2, __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, x), x))));
     const double dy = __dadd_rn(__dmul_rn(p1, __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, y), y))),

@@ -30,6 +30,7 @@ static void undistort_host(float u, float v, const float K[4], const float D[4],
   for (int j = 0; j < 5; ++j) {
     const double r2 = x * x + y * y;
     const double icdist = 1. / (1 + ((0 * r2 + k2) * r2 + k1) * r2);
+    if (icdist < 0) { x = x0; y = y0; break; }  // OpenCV 4.x: negative radial factor -> the start value
     const double dx = 2 * p1 * x * y + p2 * (r2 + 2 * x * x);
     const double dy = p1 * (r2 + 2 * y * y) + 2 * p2 * x * y;
     x = (x0 - dx) * icdist;

@@ -312,3 +312,21 @@ def test_stream_features_in_area_batched(fe, oracle, synth):
     got2, cnt2 = S.features_in_area(slots[:50], q[:50], cap=5)
     assert np.array_equal(cnt2, cnt[:50]) and all(np.array_equal(a, b[:5]) for a, b in zip(got2, got[:50]))
     E.close()
+
+
+def test_frame_glue_negative_radial_factor(fe, oracle, synth):
+    """A camera whose distortion model turns over inside the image (the radial factor goes negative towards the corners): OpenCV's
+    undistortPoints gives up on those points and keeps the start value; bounds, undistorted keys and grid must follow the oracle
+    (pinned against the OpenCV wheel in tests/test_oracle_vs_cv2.py)."""
+    W, H = 640, 480
+    K4, D4 = np.array([250, 250, 320, 240], np.float32), np.array([-0.6, 0.0, 1e-3, -1e-3], np.float32)
+    E, G, O = _pair(fe, oracle, synth, W, H, 1000, 20, 7, 23, K4, D4)
+    for g, o in zip(G, O):
+        ku = o.keys_un()
+        assert g.N == o.N and np.array_equal(g.mvKeysUn.view(np.uint8), ku.view(np.uint8))
+        off, idx = o.grid()
+        assert np.array_equal(g.grid_offsets, off) and np.array_equal(g.grid_indices, idx)
+    n, m12, cnt = fe.ORBmatcher(0.9, True).SearchForInitialization(G[0], G[1], 100)
+    rn, rm12, rcnt = oracle.search_for_initialization(O[0], O[1], 0.9, True, 100)
+    assert n == rn and np.array_equal(m12, rm12) and np.array_equal(cnt, rcnt)
+    E.close()

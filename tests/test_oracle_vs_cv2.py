@@ -149,3 +149,15 @@ def test_retain_best_selection_and_order():
             ref = [(kp.pt[0], kp.pt[1], kp.response) for kp in orb.detect(img)]
             got = [(kb[i].pt[0], kb[i].pt[1], kb[i].response) for i in orc.retain_best(resp, n)]
             assert got == ref, (trial, n)
+
+
+def test_undistort_points_negative_radial_factor(oracle):
+    """OpenCV 4.x ends the fixed-point iteration at the start value when the radial factor turns negative (points far outside the
+    distortion model's range; its regression test 14583).  Found by tools/fuzz_oracle_vs_cv2.py with random cameras."""
+    rng = np.random.default_rng(5)
+    for K4, D4 in (((250, 250, 320, 240), (-0.45, 0.0, 1e-3, -1e-3)), ((200, 300, 100, 400), (-0.4, 0.2, -2e-3, 2e-3)), ((609.2855, 609.3422, 351.4274, 237.7324), (-0.3492, 0.1363, 0, 0))):
+        K4, D4 = np.array(K4, np.float32), np.array(D4, np.float32)
+        pts = rng.uniform(-50, 900, (400, 2)).astype(np.float32)
+        K = np.array([[K4[0], 0, K4[2]], [0, K4[1], K4[3]], [0, 0, 1]], np.float32)
+        ref = cv2.undistortPoints(pts.reshape(-1, 1, 2), K, D4, None, None, K).reshape(-1, 2)
+        assert np.array_equal(ref.view(np.uint32), oracle.undistort(pts, K4, D4).view(np.uint32))
