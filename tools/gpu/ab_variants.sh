@@ -6,7 +6,7 @@ cp orb_slam_tracking_b200/liborbx.so /tmp/liborbx.keep
 for r in $(seq $rounds); do
   for v in "$@"; do
     cp "$v" orb_slam_tracking_b200/liborbx.so
-    python bench.py --steps 30 --warmup 5 2>/dev/null | python -c "
+    python bench.py --steps 30 --warmup 5 --no-cpu --no-variants 2>/dev/null | python -c "
 import json,sys
 d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$v', round(d['value']), round(d['e2e']['value']), d['stage_ms_per_step'])"
   done
