@@ -31,13 +31,18 @@ template <bool CHAIN>
 __device__ __forceinline__ u32 ld_src(const u8* p) { return CHAIN ? (u32)__ldcg(p) : (u32)__ldg(p); }
 
 // One warp: the strip of `rows` output rows from dy0 and 128 output columns from 128 * bx of level l of `slot`.
-template <bool WIDE, bool CHAIN>
-__device__ __forceinline__ void resize_strip(const Params& P, int l, const int* __restrict__ tab, int rows, int bx, int dy0, int slot) {
+// FOLD (the last column block of a level when at most 16 of its lanes have columns inside the level, e.g. 533 = 4 * 128 + 21
+// columns: 6 lanes): the warp is cut into 32 / lanesPer groups of lanesPer lanes and group g takes the rows from dyWarp + g * rows.
+// The instructions a warp issues do not depend on how many of its lanes are inside the level, so the block costs 1 / groups of
+// what it did (a sixth of all strips are such blocks at 640x480, scale 1.2).
+template <bool WIDE, bool CHAIN, bool FOLD>
+__device__ __forceinline__ void resize_strip(const Params& P, int l, const int* __restrict__ tab, int rows, int bx, int dyWarp, int slot, int lanesPer = 32) {
   const LevelInfo& D = P.lv[l];
   const LevelInfo& S = P.lv[l - 1];
-  const int lane = threadIdx.x;
+  const int lane = FOLD ? (int)threadIdx.x & (lanesPer - 1) : (int)threadIdx.x;
   const int dx0 = (bx * 32 + lane) * 4;
-  if (dy0 >= D.h) return;
+  if (dyWarp >= D.h) return;  // the whole warp
+  const int dy0 = FOLD ? dyWarp + ((int)threadIdx.x / lanesPer) * rows : dyWarp;  // groups beyond the level have no rows below
   const u8* src = level_ptr((const u8*)P.pyr, P, slot, l - 1);
   u8* dst = level_ptr(P.pyr, P, slot, l);
   // bases and pitches the compiler has to keep in registers (it reloaded them from the parameter block for every row)
@@ -132,11 +137,12 @@ __device__ __forceinline__ void resize_strip(const Params& P, int l, const int* 
   {
     // the strip's source rows are consumed one after the other (a dependent chain of loads per lane): pull its
     // 128-byte lines into L2 up front, one line per lane and round
-    const int rFirst = __ldg(&ytab[dy0].x) & 0xffff, rLast = (int)((u32)__ldg(&ytab[dyEnd - 1].x) >> 16);
+    const int dyWarpEnd = FOLD ? min(dyWarp + (32 / lanesPer) * rows, D.h) : dyEnd;  // all groups' rows
+    const int rFirst = __ldg(&ytab[dyWarp].x) & 0xffff, rLast = (int)((u32)__ldg(&ytab[dyWarpEnd - 1].x) >> 16);
     const int xb = __shfl_sync(0xffffffffu, sx0, 0) & ~127;
     const int nLines = (min(__shfl_sync(0xffffffffu, sx0 + e1[3], 31), S.pitch - 1) - xb) / 128 + 1;
     const int total = (rLast - rFirst + 1) * nLines;
-    for (int i = lane; i < total; i += 32) {
+    for (int i = threadIdx.x; i < total; i += 32) {
       const int r = i / nLines, ln = i - r * nLines;
       asm volatile("prefetch.global.L2 [%0];" ::"l"(src + (size_t)(rFirst + r) * sPitch + xb + 128 * ln));
     }
@@ -178,7 +184,17 @@ __device__ __forceinline__ void resize_strip(const Params& P, int l, const int* 
 
 template <bool WIDE>
 __global__ void __launch_bounds__(32 * kResizeWarps) k_resize(const __grid_constant__ Params P, int l, const int* __restrict__ tab, int rows) {
-  resize_strip<WIDE, false>(P, l, tab, rows, blockIdx.x, (blockIdx.y * kResizeWarps + threadIdx.y) * rows, blockIdx.z);
+  const int warp = blockIdx.y * kResizeWarps + threadIdx.y;
+  if (blockIdx.x + 1 == gridDim.x) {
+    const int nl = (P.lv[l].w - 128 * (int)blockIdx.x + 3) >> 2;  // lanes of the last column block with columns inside the level (>= 1)
+    if (nl <= 16) {
+      int lanesPer = 16;
+      while ((lanesPer >> 1) >= nl) lanesPer >>= 1;
+      resize_strip<WIDE, false, true>(P, l, tab, rows, blockIdx.x, warp * (32 / lanesPer) * rows, blockIdx.z, lanesPer);
+      return;
+    }
+  }
+  resize_strip<WIDE, false, false>(P, l, tab, rows, blockIdx.x, warp * rows, blockIdx.z);
 }
 
 // The whole pyramid of a few frames in ONE launch (single-frame latency path): seven dependent launches cost about 10 us each
@@ -194,8 +210,8 @@ __global__ void __launch_bounds__(32 * kResizeWarps) k_pyramid_chain(const __gri
     const bool wide = P.lv[l - 1].w > 2 * P.lv[l].w;  // horizontal scale above 2 (by however little: 309 -> 154 columns)
     for (int it = warp0; it < perSlot * nSlots; it += warpsTotal) {
       const int slot = it / perSlot, r = it - slot * perSlot, wy = r / nbx, bx = r - wy * nbx;
-      if (wide) resize_strip<true, true>(P, l, T.t[l], rows, bx, wy * rows, slot);
-      else resize_strip<false, true>(P, l, T.t[l], rows, bx, wy * rows, slot);
+      if (wide) resize_strip<true, true, false>(P, l, T.t[l], rows, bx, wy * rows, slot);
+      else resize_strip<false, true, false>(P, l, T.t[l], rows, bx, wy * rows, slot);
     }
     if (l + 1 < P.nlevels) {  // grid barrier: every store of level l is in L2 before any CTA starts level l + 1
       __syncthreads();
