@@ -350,3 +350,26 @@ def test_pyramid_chain_equals_levelwise(fe, oracle, synth):
         for l in range(nl):
             assert np.array_equal(E.pyramid_level(l, slot=1), R.level(l)), (W, H, sf, "batch", l)
         E.close()
+
+
+@pytest.mark.gpu
+def test_pyramid_folded_last_block(fe, oracle, synth):
+    """k_resize folds the last 128-column block of a level when at most 16 of its lanes have columns inside the level: groups of
+    16 / 8 / 4 / 2 / 1 lanes take consecutive bands of rows.  Widths whose level 1 ends 3, 8, 12, 27 and 52 columns into a block
+    give every group size; batches of 1, 8 and 64 frames give the three band heights (4, 8 and 16 rows per group)."""
+    for W, H in ((311, 200), (317, 203), (322, 240), (340, 222), (370, 240)):
+        R = oracle.Extractor(300, 1.2, 6, 20, 7)
+        imgs = synth.frames(2, W, H, first_pair=77)
+        refs = []
+        for im in imgs:
+            R(im)
+            refs.append([R.level(l) for l in range(6)])
+        for B in (1, 8, 64):
+            E = fe.ORBextractor(300, 1.2, 6, 20, 7, W, H, max_batch=B)
+            E.set_option("pyramid_chain", 0)
+            batch = np.ascontiguousarray(np.stack([imgs[i & 1] for i in range(B)]))
+            E.extract_batch(batch)
+            for slot in sorted({0, B // 2, B - 1}):
+                for l in range(6):
+                    assert np.array_equal(E.pyramid_level(l, slot=slot), refs[slot & 1][l]), (W, H, B, slot, l)
+            E.close()
