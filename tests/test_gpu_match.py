@@ -330,3 +330,36 @@ def test_frame_glue_negative_radial_factor(fe, oracle, synth):
     rn, rm12, rcnt = oracle.search_for_initialization(O[0], O[1], 0.9, True, 100)
     assert n == rn and np.array_equal(m12, rm12) and np.array_equal(cnt, rcnt)
     E.close()
+
+
+def test_stream_run_back_to_back(fe, synth):
+    """orbx_stream_run calls enqueued one after the other without a synchronisation (the batch runs as two halves on two lanes that
+    join on the context's stream), uploads in between, runs of different sizes in a row: results must be those of a single run of
+    whatever batch is resident."""
+    W, H, B = 640, 480, 128
+    K4, D4 = synth.camera_for(W, H)
+    E = fe.ORBextractor(1000, 1.2, 8, 20, 7, W, H, max_batch=B)
+    E.set_camera(K4, D4)
+    S = fe.Stream(E, 0.9, True, 100)
+    batches = [synth.frames(B, W, H, first_pair=300), synth.frames(B, W, H, first_pair=700)]
+    single = []
+    for imgs in batches:
+        S.upload(imgs)
+        S.run(B)
+        single.append(S.download(B))
+    assert not np.array_equal(single[0]["n"], single[1]["n"]) or not np.array_equal(single[0]["desc"], single[1]["desc"])
+
+    def same(a, b):
+        return all(np.array_equal(a[k].view(np.uint8), b[k].view(np.uint8)) for k in a)
+
+    for rep in range(3):
+        for j, imgs in enumerate(batches):
+            S.upload(imgs)
+            for _ in range(5 + rep):
+                S.run(B)
+            assert same(S.download(B), single[j]), (rep, j)
+    # runs of different sizes in a row, and a sync in between
+    S.upload(batches[0])
+    S.run(B); S.run(B // 2); S.run(B); S.run(B); S.sync(); S.run(B); S.run(B)
+    assert same(S.download(B), single[0])
+    E.close()
